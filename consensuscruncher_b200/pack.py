@@ -1,0 +1,220 @@
+"""Host packing: records -> the SoA batch the CUDA kernels consume.
+
+This is the part of `read_bam` (consensus_helper.py:305-480) that stays on host
+cores: region visit order, the bad-read filter (`:390-410`), mate pairing by
+query name (`:412-420,478`), barcode extraction (`:423-431`) and dictionary
+encoding of the two string-valued key fields (barcode, ordered cigar pair).
+Grouping reads into families - the dictionaries `read_dict` / `tag_dict` /
+`csn_pair_dict` of `:447-475` - is done on the GPU from the packed fields.
+
+Layout handed to the device (also described in DESIGN.md):
+
+  fields[N]   32-byte records, reads in pair-completion order (2k = first-seen
+              mate of pair k, 2k+1 = second-seen mate):
+                u32 bc     barcode dictionary id
+                u32 cig    ordered cigar-pair dictionary id
+                i32 tid, pos, mtid, mpos
+                i32 tlen ; u16 flag ; u8 mapq ; u8 rg (0xff = no RG tag)
+              The family key of `unique_tag` (`:293-301`) is the first 24 bytes
+              plus flag bits 0x10 (orientation) and 0x40/0x80 (read number).
+  payload[N]  `stride` bytes per read: lpad/2 bytes of BAM 4-bit bases (high
+              nibble first, zero padded) followed by lpad quality bytes (zero
+              padded), lpad = L rounded up to 32, stride a multiple of 64.
+  dup_bc[B]   barcode id of the complementary strand's barcode (`duplex_tag`,
+              `:629-639`), 0xffffffff when that barcode never occurs.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import keys
+from .records import Read, seq_to_codes
+
+FIELDS_DT = np.dtype([("bc", "<u4"), ("cig", "<u4"), ("tid", "<i4"), ("pos", "<i4"),
+                      ("mtid", "<i4"), ("mpos", "<i4"), ("tlen", "<i4"),
+                      ("flag", "<u2"), ("mapq", "u1"), ("rg", "u1")])
+assert FIELDS_DT.itemsize == 32
+NO_ID = 0xFFFFFFFF
+NO_RG = 0xFF
+
+
+class DomainError(ValueError):
+    """Input outside the domain the reference itself handles."""
+
+
+def row_geometry(max_len):
+    """(lpad, stride) for reads of up to `max_len` bases."""
+    lpad = max(32, (int(max_len) + 31) // 32 * 32)
+    stride = (lpad // 2 + lpad + 63) // 64 * 64
+    return lpad, stride
+
+
+def pack_row(codes, qual, lpad, out):
+    """Write one payload row (4-bit bases then qualities) into `out` (u8[stride])."""
+    n = len(codes)
+    c = np.zeros(lpad, np.uint8)
+    c[:n] = codes
+    out[:lpad // 2] = (c[0::2] << 4) | c[1::2]
+    out[lpad // 2:lpad // 2 + n] = qual
+    out[lpad // 2 + n:] = 0
+
+
+def unpack_row(row, lpad, n):
+    """Inverse of `pack_row`: (codes u8[n], qual u8[n])."""
+    s = row[:lpad // 2]
+    codes = np.empty(lpad, np.uint8)
+    codes[0::2] = s >> 4
+    codes[1::2] = s & 15
+    return codes[:n].copy(), row[lpad // 2:lpad // 2 + n].copy()
+
+
+class PackedReads:
+    """SoA batch of the good, paired reads of one stage (+ host-side bookkeeping)."""
+
+    def __init__(self, fields, payload, lpad, barcodes, dup_bc, cigar_pairs, rgs,
+                 src=None, lens=None, counters=None, bad=None, leftover=None):
+        self.fields = fields
+        self.payload = payload
+        self.lpad = int(lpad)
+        self.stride = int(payload.shape[1]) if payload.ndim == 2 else 0
+        self.barcodes = barcodes
+        self.dup_bc = dup_bc
+        self.cigar_pairs = cigar_pairs
+        self.rgs = rgs
+        self.src = src                    # index of each packed read in the input record list
+        self.lens = lens                  # query length of each packed read
+        self.counters = counters or {}
+        self.bad = bad or []              # indices of records that go to badReads.bam
+        self.leftover = leftover or []    # indices of records whose mate never showed up
+
+    @property
+    def n(self):
+        return int(self.fields.shape[0])
+
+
+def build_dup_table(barcodes):
+    idx = {b: i for i, b in enumerate(barcodes)}
+    dup = np.full(len(barcodes), NO_ID, np.uint32)
+    for i, b in enumerate(barcodes):
+        j = idx.get(keys.duplex_barcode(b))
+        if j is not None:
+            dup[i] = j
+    return dup
+
+
+def visit_order(reads, regions):
+    """Indices of `reads` in the order `read_bam` visits them.
+
+    regions None: file order (`fetch(until_eof=True)`).  Otherwise a list of
+    (tid, start, end): for each, records of that contig overlapping the
+    half-open window, kept iff start <= pos <= end (consensus_helper.py:381).
+    """
+    if regions is None:
+        return range(len(reads))
+    by_tid = {}
+    for i, r in enumerate(reads):
+        by_tid.setdefault(r.tid, []).append(i)
+    pos_of = {t: np.array([reads[i].pos for i in ix]) for t, ix in by_tid.items()}
+    out = []
+    for tid, start, end in regions:
+        ix = by_tid.get(tid)
+        if not ix:
+            continue
+        p = pos_of[tid]
+        if np.all(p[:-1] <= p[1:]):
+            lo = int(np.searchsorted(p, start, "left"))
+            hi = int(np.searchsorted(p, end, "left"))     # pos == end does not overlap [start, end)
+            out.extend(ix[lo:hi])
+        else:
+            out.extend(i for i, q in zip(ix, p) if start <= q < end)
+    return out
+
+
+def pair_reads(reads, stage="sscs", bdelim="|", regions=None):
+    """Filter + mate pairing.  Returns (pairs, barcodes_of_pairs, counters, bad, leftover).
+
+    stage "sscs": barcode is `qname.split(bdelim)[1]`, bad reads are diverted;
+    stage "dcs":  barcode is `qname.split('_')[0]`, nothing is diverted
+                  (`badRead_bam=None`, consensus_helper.py:409-412).
+    """
+    sscs = stage == "sscs"
+    counters = dict(total=0, unmapped=0, unmapped_mate=0, multiple_mapping=0, bad_spacer=0)
+    waiting = {}
+    pairs, pair_bc, bad = [], [], []
+    for i in visit_order(reads, regions):
+        r = reads[i]
+        counters["total"] += 1
+        is_bad = True
+        if sscs and bdelim not in r.qname:
+            counters["bad_spacer"] += 1
+        elif r.flag & 0x4:
+            counters["unmapped"] += 1
+            counters["total"] -= 1
+        elif r.flag in keys.MATE_UNMAPPED_FLAGS:
+            counters["unmapped_mate"] += 1
+        elif r.flag & 0x900:
+            counters["multiple_mapping"] += 1
+        else:
+            is_bad = False
+        if is_bad and sscs:
+            bad.append(i)
+            continue
+        j = waiting.pop(r.qname, None)
+        if j is None:
+            waiting[r.qname] = i
+            continue
+        q = reads[j].qname
+        pair_bc.append(q.split(bdelim)[1] if sscs else q.split("_")[0])
+        pairs.append((j, i))
+    return pairs, pair_bc, counters, bad, list(waiting.values())
+
+
+def pack_reads(reads, stage="sscs", bdelim="|", regions=None, row_source=None):
+    """Records -> PackedReads (see module docstring).
+
+    `row_source(i) -> (codes, qual)` lets a caller supply bases/qualities that
+    are already arrays; by default they come from `reads[i].seq/.qual`.
+    """
+    pairs, pair_bc, counters, bad, leftover = pair_reads(reads, stage, bdelim, regions)
+    n = 2 * len(pairs)
+    fields = np.zeros(n, FIELDS_DT)
+    bc_ids, cig_ids, rg_ids = {}, {}, {}
+    src = np.empty(n, np.int64)
+    lens = np.empty(n, np.int32)
+    max_len = 0
+    for k, (a, b) in enumerate(pairs):
+        read, mate = reads[a], reads[b]
+        for r in (read, mate):
+            if keys.which_read(r.flag) is None:
+                raise DomainError("flag %d of %s is not one of the 16 paired flags the "
+                                  "reference can key (consensus_helper.py:69-70)" % (r.flag, r.qname))
+        bc = bc_ids.setdefault(pair_bc[k], len(bc_ids))
+        cg = cig_ids.setdefault(keys.cigar_order(read, mate), len(cig_ids))
+        for j, (i, r) in enumerate(((a, read), (b, mate))):
+            f = fields[2 * k + j]
+            f["bc"], f["cig"] = bc, cg
+            f["tid"], f["pos"], f["mtid"], f["mpos"] = r.tid, r.pos, r.mtid, r.mpos
+            f["tlen"], f["flag"], f["mapq"] = r.tlen, r.flag, r.mapq
+            if r.rg is None:
+                f["rg"] = NO_RG
+            else:
+                g = rg_ids.setdefault(r.rg, len(rg_ids))
+                if g >= NO_RG:
+                    raise DomainError("more than 255 distinct read groups")
+                f["rg"] = g
+            src[2 * k + j] = i
+            lens[2 * k + j] = len(r.seq)
+            max_len = max(max_len, len(r.seq))
+    lpad, stride = row_geometry(max_len)
+    payload = np.zeros((n, stride), np.uint8)
+    for x in range(n):
+        i = int(src[x])
+        if row_source is None:
+            codes, qual = seq_to_codes(reads[i].seq), reads[i].qual
+        else:
+            codes, qual = row_source(i)
+        pack_row(codes, qual, lpad, payload[x])
+    barcodes = list(bc_ids)
+    return PackedReads(fields, payload, lpad, barcodes, build_dup_table(barcodes),
+                       list(cig_ids), list(rg_ids), src=src, lens=lens,
+                       counters=counters, bad=bad, leftover=leftover)
