@@ -1,0 +1,817 @@
+// libccgpu.so - host side of the C ABI declared in include/ccgpu.h.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include "../../include/ccgpu.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "radix.cuh"
+#include "scan.cuh"
+
+using namespace ccgpu;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct PhaseTimer {
+    std::vector<cudaEvent_t> ev;   // start/stop pairs
+    size_t used = 0;
+    double ms = 0.0;
+    uint64_t runs = 0;
+};
+
+enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_COUNT = 32 };
+
+}  // namespace
+
+struct cc_ctx {
+    int device = 0;
+    cc_params params{0.7, 1};
+    std::string err;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    // input
+    const uint4 *fields = nullptr;
+    const uint8_t *payload = nullptr;
+    const uint32_t *dup_bc = nullptr;
+    uint64_t n = 0;
+    uint32_t lpad = 0, stride = 0, n_bc = 0;
+    DevBuf in_fields, in_payload, in_dup;
+    // grouping scratch
+    DevBuf key_a, key_b, val_a, val_b, head, radix_counts, scan_status, counters, hist, stats;
+    uint32_t *perm = nullptr, *sorted_keys = nullptr, *spare_keys = nullptr, *spare_vals = nullptr;
+    uint32_t next_ticket = 0;
+    // families
+    uint32_t n_fam = 0, n_sscs = 0, n_dcs = 0, n_corr = 0, n_dcssc = 0;
+    DevBuf tmpl, c2hs, fam_start, fam_size, is_sscs, fam_mapq, fam_flag, fam_tlen, fam_rg;
+    DevBuf partner, table, f_dcs, f_corr, f_dcssc;
+    DevBuf sscs_list, dcs_list, corr_list, dcssc_list, sscs_row, dcs_row, corr_row, dcssc_row;
+    DevBuf sscs_rows, corr_rows, dcs_rows, dcssc_rows;
+    DevBuf dcs_mapq, dcs_flag, dcs_tlen, dcs_rg, dcssc_mapq, dcssc_flag, dcssc_tlen, dcssc_rg;
+    DevBuf tmp_a, tmp_b, tmp_c;   // stand-alone primitives
+    bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
+    bool read_fam_ready = false;
+    uint32_t host_ctr[CT_COUNT];
+    // bookkeeping
+    bool profile = false;
+    PhaseTimer phase[CC_PH_COUNT];
+    uint64_t launches = 0;
+    uint64_t dev_bytes = 0;
+};
+
+namespace {
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+            return CC_ERR_CUDA;                                                                    \
+        }                                                                                          \
+    } while (0)
+
+#define TRY(expr)                                                                                  \
+    do {                                                                                           \
+        int rc_ = (expr);                                                                          \
+        if (rc_ != CC_OK) return rc_;                                                              \
+    } while (0)
+
+#define LAUNCH(kernel, grid, block, ...)                                                           \
+    do {                                                                                           \
+        kernel<<<(grid), (block), 0, ctx->stream>>>(__VA_ARGS__);                                  \
+        ctx->launches++;                                                                           \
+        CK(cudaGetLastError());                                                                    \
+    } while (0)
+
+int fail(cc_ctx *ctx, int code, const char *msg)
+{
+    ctx->err = msg;
+    return code;
+}
+
+int ensure(cc_ctx *ctx, DevBuf &b, size_t bytes)
+{
+    if (bytes == 0) bytes = 256;
+    if (b.cap >= bytes) return CC_OK;
+    if (b.p) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        CK(cudaFree(b.p));
+        ctx->dev_bytes -= b.cap;
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    size_t want = (bytes + 255) & ~(size_t)255;
+    CK(cudaMalloc(&b.p, want));
+    b.cap = want;
+    ctx->dev_bytes += want;
+    return CC_OK;
+}
+
+void release(cc_ctx *ctx, DevBuf &b)
+{
+    if (b.p) cudaFree(b.p);
+    ctx->dev_bytes -= b.cap;
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+template <typename T> T *ptr(DevBuf &b) { return reinterpret_cast<T *>(b.p); }
+
+inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+
+int phase_begin(cc_ctx *ctx, int ph)
+{
+    if (!ctx->profile) return CC_OK;
+    PhaseTimer &t = ctx->phase[ph];
+    if (t.used + 2 > t.ev.size()) {
+        cudaEvent_t a, b;
+        CK(cudaEventCreate(&a));
+        CK(cudaEventCreate(&b));
+        t.ev.push_back(a);
+        t.ev.push_back(b);
+    }
+    CK(cudaEventRecord(t.ev[t.used], ctx->stream));
+    return CC_OK;
+}
+
+int phase_end(cc_ctx *ctx, int ph)
+{
+    if (!ctx->profile) return CC_OK;
+    PhaseTimer &t = ctx->phase[ph];
+    CK(cudaEventRecord(t.ev[t.used + 1], ctx->stream));
+    t.used += 2;
+    return CC_OK;
+}
+
+int collect_phases(cc_ctx *ctx)
+{
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int ph = 0; ph < CC_PH_COUNT; ph++) {
+        PhaseTimer &t = ctx->phase[ph];
+        for (size_t i = 0; i + 1 < t.used; i += 2) {
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, t.ev[i], t.ev[i + 1]));
+            t.ms += ms;
+            t.runs++;
+        }
+        t.used = 0;
+    }
+    return CC_OK;
+}
+
+// ---- prefix-sum helpers ---------------------------------------------------------------
+int scan_prepare(cc_ctx *ctx, uint64_t n, uint32_t **ticket)
+{
+    uint64_t tiles = scan_tiles(n);
+    TRY(ensure(ctx, ctx->scan_status, (tiles + 1) * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->scan_status.p, 0, (tiles + 1) * sizeof(unsigned long long), ctx->stream));
+    if (ctx->next_ticket >= CT_COUNT - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    *ticket = ptr<uint32_t>(ctx->counters) + CT_TICKET0 + ctx->next_ticket++;
+    return CC_OK;
+}
+
+int scan_exclusive(cc_ctx *ctx, const uint32_t *in, uint32_t *out, uint64_t n)
+{
+    if (n == 0) return CC_OK;
+    uint32_t *ticket;
+    TRY(scan_prepare(ctx, n, &ticket));
+    auto kernel = scan_kernel<SCAN_MODE_EXCL, uint32_t>;
+    LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, in, out, (uint32_t *)nullptr, n,
+           ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr);
+    return CC_OK;
+}
+
+// list[rank] = index of every non-zero flag; *total (device) = how many
+int compact_flags(cc_ctx *ctx, const uint8_t *flags, uint64_t n, uint32_t *list, uint32_t *total)
+{
+    if (n == 0) return CC_OK;   // *total was zeroed with the counter block
+    uint32_t *ticket;
+    TRY(scan_prepare(ctx, n, &ticket));
+    auto kernel = scan_kernel<SCAN_MODE_COMPACT, uint8_t>;
+    LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, flags, list, (uint32_t *)nullptr,
+           n, ptr<unsigned long long>(ctx->scan_status), ticket, total);
+    return CC_OK;
+}
+
+int compact_marks(cc_ctx *ctx, const uint32_t *marks, uint64_t n, uint32_t *list, uint32_t *carry)
+{
+    if (n == 0) return CC_OK;
+    uint32_t *ticket;
+    TRY(scan_prepare(ctx, n, &ticket));
+    auto kernel = scan_kernel<SCAN_MODE_COMPACT_CARRY, uint32_t>;
+    LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, marks, list,
+           carry, n, ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr);
+    return CC_OK;
+}
+
+int read_counters(cc_ctx *ctx)
+{
+    CK(cudaMemcpyAsync(ctx->host_ctr, ctx->counters.p, sizeof(ctx->host_ctr), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->host_ctr[CT_ERR])
+        return fail(ctx, CC_ERR_BASE, "a base other than A/C/G/T carries Q>=30 inside a family "
+                                      "(the reference raises IndexError/ValueError, SSCS_maker.py:119-122)");
+    return CC_OK;
+}
+
+int sort_bits_for(uint64_t n)
+{
+    int bits = 8;
+    while (bits < 32 && (1ull << bits) < n * 16) bits += 8;   // ~4 spare bits keep mixed runs rare
+    return bits;
+}
+
+// ---- stage 1: grouping ----------------------------------------------------------------------
+int do_group(cc_ctx *ctx)
+{
+    const uint64_t n = ctx->n;
+    ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = ctx->read_fam_ready = false;
+    ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = 0;
+    ctx->next_ticket = 0;
+    TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
+    TRY(ensure(ctx, ctx->stats, 16 * sizeof(unsigned long long)));
+    TRY(ensure(ctx, ctx->hist, CC_HIST_BINS * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->counters.p, 0, CT_COUNT * sizeof(uint32_t), ctx->stream));
+    CK(cudaMemsetAsync(ctx->stats.p, 0, 16 * sizeof(unsigned long long), ctx->stream));
+    CK(cudaMemsetAsync(ctx->hist.p, 0, CC_HIST_BINS * sizeof(unsigned long long), ctx->stream));
+    memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
+    if (n == 0) { ctx->grouped = true; return CC_OK; }
+
+    TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
+    TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
+    TRY(ensure(ctx, ctx->head, n));
+    const uint32_t ntiles = (uint32_t)radix_tiles(n);
+    TRY(ensure(ctx, ctx->radix_counts, (size_t)ntiles * RADIX_BINS * 4));
+
+    const int bits = sort_bits_for(n);
+    const uint32_t key_mask = bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
+    TRY(phase_begin(ctx, CC_PH_HASH));
+    LAUNCH(hash_kernel, blocks_for(n, 256), 256, ctx->fields, n, key_mask, ptr<uint32_t>(ctx->key_a));
+    TRY(phase_end(ctx, CC_PH_HASH));
+
+    TRY(phase_begin(ctx, CC_PH_SORT));
+    uint32_t *kin = ptr<uint32_t>(ctx->key_a), *kout = ptr<uint32_t>(ctx->key_b);
+    uint32_t *vin = nullptr, *vout = ptr<uint32_t>(ctx->val_a), *vother = ptr<uint32_t>(ctx->val_b);
+    uint32_t *counts = ptr<uint32_t>(ctx->radix_counts);
+    for (int shift = 0; shift < bits; shift += 8) {
+        LAUNCH(radix_hist_kernel, ntiles, RADIX_THREADS, kin, n, shift, ntiles, counts);
+        ctx->next_ticket = 0;   // scans inside the sort reuse ticket 0 (zeroed below)
+        CK(cudaMemsetAsync(ptr<uint32_t>(ctx->counters) + CT_TICKET0, 0, sizeof(uint32_t), ctx->stream));
+        TRY(scan_exclusive(ctx, counts, counts, (uint64_t)ntiles * RADIX_BINS));
+        LAUNCH(radix_scatter_kernel, ntiles, RADIX_THREADS, kin, vin, kout, vout, n, shift, ntiles, counts);
+        uint32_t *t = kin; kin = kout; kout = t;
+        vin = vout; vout = vother; vother = vin;
+    }
+    ctx->sorted_keys = kin; ctx->spare_keys = kout;
+    ctx->perm = vin; ctx->spare_vals = vout;
+    ctx->next_ticket = 0;
+    CK(cudaMemsetAsync(ptr<uint32_t>(ctx->counters) + CT_TICKET0, 0, sizeof(uint32_t), ctx->stream));
+    TRY(phase_end(ctx, CC_PH_SORT));
+
+    TRY(phase_begin(ctx, CC_PH_SEGMENT));
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
+    uint32_t *mixed_list = ctx->spare_keys;        // dead after the sort; at most n/2 runs
+    LAUNCH(boundary_kernel, blocks_for(n, 256), 256, ctx->fields, ctx->sorted_keys, ctx->perm, n,
+           ptr<uint8_t>(ctx->head), mixed_list, ctr + CT_MIXED, (uint32_t)(n / 2 + 1));
+    TRY(read_counters(ctx));                        // number of mixed runs
+    if (ctx->host_ctr[CT_MIXED]) {
+        uint32_t nm = ctx->host_ctr[CT_MIXED];
+        LAUNCH(fix_mixed_runs_kernel, blocks_for((uint64_t)nm * 32, 128), 128, ctx->fields, ctx->sorted_keys, ctx->perm,
+               ctx->spare_vals, n, ptr<uint8_t>(ctx->head), mixed_list, nm);
+    }
+    uint32_t *hs_start = ctx->spare_keys;          // reused again: start of every family in sorted order
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->head), n, hs_start, ctr + CT_NFAM));
+    TRY(read_counters(ctx));
+    const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
+
+    TRY(ensure(ctx, ctx->tmpl, (size_t)nf * 4)); TRY(ensure(ctx, ctx->c2hs, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->fam_start, (size_t)nf * 4)); TRY(ensure(ctx, ctx->fam_size, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->is_sscs, nf)); TRY(ensure(ctx, ctx->fam_mapq, nf)); TRY(ensure(ctx, ctx->fam_rg, nf));
+    TRY(ensure(ctx, ctx->fam_flag, (size_t)nf * 2)); TRY(ensure(ctx, ctx->fam_tlen, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4));
+
+    uint32_t *mark = ctx->spare_vals;              // dead after the fix-up
+    CK(cudaMemsetAsync(mark, 0, n * 4, ctx->stream));
+    LAUNCH(mark_first_kernel, blocks_for(nf, 256), 256, hs_start, ctx->perm, nf, mark);
+    TRY(compact_marks(ctx, mark, n, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->c2hs)));
+    LAUNCH(family_build_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->c2hs), hs_start,
+           ptr<uint32_t>(ctx->tmpl), nf, (uint32_t)n, ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size),
+           ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
+           ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
+           (uint32_t)CC_HIST_BINS);
+    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
+           ctr + CT_FAULTS);
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS));
+    TRY(phase_end(ctx, CC_PH_SEGMENT));
+    ctx->grouped = true;
+    return CC_OK;
+}
+
+// ---- stage 2: join + classification (index work only) -----------------------------------------
+int do_join_index(cc_ctx *ctx)
+{
+    const uint32_t nf = ctx->n_fam;
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
+    TRY(ensure(ctx, ctx->partner, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->f_dcs, nf)); TRY(ensure(ctx, ctx->f_corr, nf)); TRY(ensure(ctx, ctx->f_dcssc, nf));
+    TRY(ensure(ctx, ctx->dcs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->corr_list, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->dcssc_list, (size_t)nf * 4));
+    if (nf == 0) return CC_OK;
+    TRY(phase_begin(ctx, CC_PH_JOIN));
+    uint64_t slots = 64;
+    while (slots < 2ull * nf) slots <<= 1;
+    TRY(ensure(ctx, ctx->table, slots * 8));
+    CK(cudaMemsetAsync(ctx->table.p, 0, slots * 8, ctx->stream));
+    LAUNCH(join_build_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf,
+           ptr<unsigned long long>(ctx->table), slots - 1);
+    LAUNCH(join_probe_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc,
+           ctx->n_bc, ptr<unsigned long long>(ctx->table), slots - 1, ptr<int32_t>(ctx->partner));
+    TRY(phase_end(ctx, CC_PH_JOIN));
+    TRY(phase_begin(ctx, CC_PH_CLASSIFY));
+    LAUNCH(classify_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
+           (int)ctx->params.scorrect, ptr<uint8_t>(ctx->f_dcs), ptr<uint8_t>(ctx->f_corr),
+           ptr<uint8_t>(ctx->f_dcssc), ptr<unsigned long long>(ctx->stats));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcs), nf, ptr<uint32_t>(ctx->dcs_list), ctr + CT_NDCS));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_corr), nf, ptr<uint32_t>(ctx->corr_list), ctr + CT_NCORR));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcssc), nf, ptr<uint32_t>(ctx->dcssc_list), ctr + CT_NDCSSC));
+    TRY(phase_end(ctx, CC_PH_CLASSIFY));
+    return CC_OK;
+}
+
+int row_map(cc_ctx *ctx, DevBuf &row, DevBuf &list, uint32_t n_rows)
+{
+    const uint32_t nf = ctx->n_fam;
+    TRY(ensure(ctx, row, (size_t)nf * 4));
+    if (nf == 0) return CC_OK;
+    LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(row), (uint64_t)nf, -1);
+    if (n_rows) LAUNCH(rows_from_list_kernel, blocks_for(n_rows, 256), 256, ptr<uint32_t>(list), n_rows, ptr<int32_t>(row));
+    return CC_OK;
+}
+
+// counts known on the host -> row maps
+int do_lists(cc_ctx *ctx, bool with_join)
+{
+    TRY(read_counters(ctx));
+    if (ctx->host_ctr[CT_FAULTS])
+        return fail(ctx, CC_ERR_DOMAIN, "a read pair does not found/join its two families together "
+                                        "(SSCS_maker.py:275 would not emit this pair name): outside the GPU path's domain");
+    ctx->n_sscs = ctx->host_ctr[CT_NSSCS];
+    TRY(row_map(ctx, ctx->sscs_row, ctx->sscs_list, ctx->n_sscs));
+    if (with_join) {
+        ctx->n_dcs = ctx->host_ctr[CT_NDCS];
+        ctx->n_corr = ctx->host_ctr[CT_NCORR];
+        ctx->n_dcssc = ctx->host_ctr[CT_NDCSSC];
+        TRY(row_map(ctx, ctx->dcs_row, ctx->dcs_list, ctx->n_dcs));
+        TRY(row_map(ctx, ctx->corr_row, ctx->corr_list, ctx->n_corr));
+        TRY(row_map(ctx, ctx->dcssc_row, ctx->dcssc_list, ctx->n_dcssc));
+    }
+    ctx->listed = true;
+    return CC_OK;
+}
+
+int do_vote(cc_ctx *ctx)
+{
+    const uint32_t rows = ctx->n_sscs;
+    TRY(ensure(ctx, ctx->sscs_rows, (size_t)rows * ctx->stride));
+    TRY(phase_begin(ctx, CC_PH_VOTE));
+    if (rows)
+        LAUNCH(vote_kernel, blocks_for((uint64_t)rows * 32, 256), 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad,
+               ctx->perm, ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->sscs_list),
+               rows, ctx->params.cutoff, ptr<uint8_t>(ctx->sscs_rows), ptr<uint8_t>(ctx->fam_mapq),
+               ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
+               ptr<uint32_t>(ctx->counters) + CT_ERR);
+    TRY(phase_end(ctx, CC_PH_VOTE));
+    ctx->voted = true;
+    return CC_OK;
+}
+
+RowSources sources(cc_ctx *ctx)
+{
+    RowSources s;
+    s.payload = ctx->payload;
+    s.sscs_rows = ptr<uint8_t>(ctx->sscs_rows);
+    s.corr_rows = ptr<uint8_t>(ctx->corr_rows);
+    s.tmpl = ptr<uint32_t>(ctx->tmpl);
+    s.fam_size = ptr<uint32_t>(ctx->fam_size);
+    s.sscs_row = ptr<int32_t>(ctx->sscs_row);
+    s.corr_row = ptr<int32_t>(ctx->corr_row);
+    s.stride = ctx->stride;
+    return s;
+}
+
+inline uint32_t row_groups(const cc_ctx *ctx) { return ctx->lpad / 8; }
+
+int do_duplex(cc_ctx *ctx, bool after_sc)
+{
+    const uint32_t rows = after_sc ? ctx->n_dcssc : ctx->n_dcs;
+    DevBuf &out = after_sc ? ctx->dcssc_rows : ctx->dcs_rows;
+    DevBuf &mq = after_sc ? ctx->dcssc_mapq : ctx->dcs_mapq, &fl = after_sc ? ctx->dcssc_flag : ctx->dcs_flag;
+    DevBuf &tl = after_sc ? ctx->dcssc_tlen : ctx->dcs_tlen, &rg = after_sc ? ctx->dcssc_rg : ctx->dcs_rg;
+    TRY(ensure(ctx, out, (size_t)rows * ctx->stride));
+    TRY(ensure(ctx, mq, rows)); TRY(ensure(ctx, rg, rows));
+    TRY(ensure(ctx, fl, (size_t)rows * 2)); TRY(ensure(ctx, tl, (size_t)rows * 4));
+    const int ph = after_sc ? CC_PH_DCS_SC : CC_PH_DCS;
+    TRY(phase_begin(ctx, ph));
+    if (rows) {
+        const uint32_t g = row_groups(ctx);
+        LAUNCH(duplex_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx),
+               ptr<uint32_t>(after_sc ? ctx->dcssc_list : ctx->dcs_list), ptr<int32_t>(ctx->partner), rows, ctx->lpad, g,
+               after_sc ? 1 : 0, ptr<uint8_t>(out), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
+               ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<uint8_t>(mq), ptr<uint16_t>(fl),
+               ptr<int32_t>(tl), ptr<uint8_t>(rg));
+    }
+    TRY(phase_end(ctx, ph));
+    return CC_OK;
+}
+
+int do_rescue(cc_ctx *ctx)
+{
+    const uint32_t rows = ctx->n_corr;
+    TRY(ensure(ctx, ctx->corr_rows, (size_t)rows * ctx->stride));
+    TRY(phase_begin(ctx, CC_PH_RESCUE));
+    if (rows) {
+        const uint32_t g = row_groups(ctx);
+        LAUNCH(rescue_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx), ptr<uint32_t>(ctx->corr_list),
+               ptr<int32_t>(ctx->partner), rows, ctx->lpad, g, ptr<uint8_t>(ctx->corr_rows));
+    }
+    TRY(phase_end(ctx, CC_PH_RESCUE));
+    return CC_OK;
+}
+
+int check_geometry(cc_ctx *ctx, const void *fields, const void *payload, uint64_t n, uint32_t lpad, uint32_t stride)
+{
+    if (n && (!fields || !payload)) return fail(ctx, CC_ERR_ARG, "NULL fields/payload");
+    if (lpad == 0 || lpad % 32 || stride % 64 || stride < lpad / 2 + lpad)
+        return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride % 64 == 0, stride >= 3*lpad/2");
+    if (n >= (1ull << 31)) return fail(ctx, CC_ERR_TOO_LARGE, "a batch holds at most 2^31-1 reads");
+    if (n & 1) return fail(ctx, CC_ERR_ARG, "reads come in pairs (2k, 2k+1)");
+    return CC_OK;
+}
+
+
+}  // namespace
+
+// ==================================== C ABI ==========================================
+extern "C" {
+
+cc_ctx *cc_create(int device, const cc_params *params)
+{
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) {
+        g_create_error = e != cudaSuccess ? std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e)
+                                          : "no such CUDA device (this library has no CPU fallback)";
+        return nullptr;
+    }
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess || prop.major != 10) {
+        g_create_error = "device is not an sm_100 (B200) GPU; libccgpu.so carries sm_100a code only";
+        return nullptr;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) {
+        g_create_error = "cudaSetDevice failed";
+        return nullptr;
+    }
+    cc_ctx *ctx = new cc_ctx();
+    ctx->device = device;
+    if (params) ctx->params = *params;
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        g_create_error = "cudaStreamCreate failed";
+        delete ctx;
+        return nullptr;
+    }
+    ctx->stream = ctx->own_stream;
+    return ctx;
+}
+
+void cc_destroy(cc_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
+                     &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->hist, &ctx->stats,
+                     &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
+                     &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
+                     &ctx->f_dcssc, &ctx->sscs_list, &ctx->dcs_list, &ctx->corr_list, &ctx->dcssc_list, &ctx->sscs_row,
+                     &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
+                     &ctx->dcssc_rows, &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->dcssc_mapq,
+                     &ctx->dcssc_flag, &ctx->dcssc_tlen, &ctx->dcssc_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c};
+    for (DevBuf *b : all) release(ctx, *b);
+    for (auto &t : ctx->phase)
+        for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+}
+
+const char *cc_last_error(cc_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int cc_set_params(cc_ctx *ctx, const cc_params *params)
+{
+    if (!ctx || !params) return CC_ERR_ARG;
+    ctx->params = *params;
+    return CC_OK;
+}
+
+int cc_set_stream(cc_ctx *ctx, void *stream)
+{
+    if (!ctx) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : ctx->own_stream;
+    return CC_OK;
+}
+
+int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n, uint32_t lpad,
+                  uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc)
+{
+    if (!ctx) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    TRY(check_geometry(ctx, fields, payload, n, lpad, stride));
+    TRY(ensure(ctx, ctx->in_fields, n * sizeof(cc_fields)));
+    TRY(ensure(ctx, ctx->in_payload, n * (size_t)stride));
+    TRY(ensure(ctx, ctx->in_dup, (size_t)n_bc * 4));
+    TRY(phase_begin(ctx, CC_PH_H2D));
+    if (n) {
+        CK(cudaMemcpyAsync(ctx->in_fields.p, fields, n * sizeof(cc_fields), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->in_payload.p, payload, n * (size_t)stride, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (n_bc) CK(cudaMemcpyAsync(ctx->in_dup.p, dup_bc, (size_t)n_bc * 4, cudaMemcpyHostToDevice, ctx->stream));
+    TRY(phase_end(ctx, CC_PH_H2D));
+    ctx->fields = ptr<uint4>(ctx->in_fields);
+    ctx->payload = ptr<uint8_t>(ctx->in_payload);
+    ctx->dup_bc = ptr<uint32_t>(ctx->in_dup);
+    ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
+    ctx->have_reads = true;
+    ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
+    return CC_OK;
+}
+
+int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n, uint32_t lpad,
+                         uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc)
+{
+    if (!ctx) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    TRY(check_geometry(ctx, fields, payload, n, lpad, stride));
+    if (((uintptr_t)fields & 15) || ((uintptr_t)payload & 15)) return fail(ctx, CC_ERR_ARG, "device buffers must be 16-byte aligned");
+    ctx->fields = reinterpret_cast<const uint4 *>(fields);
+    ctx->payload = payload;
+    ctx->dup_bc = dup_bc;
+    ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
+    ctx->have_reads = true;
+    ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
+    return CC_OK;
+}
+
+int cc_group(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (!ctx->have_reads) return fail(ctx, CC_ERR_ARG, "cc_group before cc_load_reads");
+    CK(cudaSetDevice(ctx->device));
+    TRY(do_group(ctx));
+    return do_lists(ctx, false);
+}
+
+int cc_sscs_vote(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (!ctx->grouped || !ctx->listed) return fail(ctx, CC_ERR_ARG, "cc_sscs_vote before cc_group");
+    CK(cudaSetDevice(ctx->device));
+    TRY(do_vote(ctx));
+    return read_counters(ctx);
+}
+
+int cc_dcs_join(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (!ctx->voted) return fail(ctx, CC_ERR_ARG, "cc_dcs_join before cc_sscs_vote");
+    CK(cudaSetDevice(ctx->device));
+    TRY(do_join_index(ctx));
+    TRY(do_lists(ctx, true));
+    TRY(do_duplex(ctx, false));
+    ctx->joined = true;
+    return CC_OK;
+}
+
+int cc_sc_rescue(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (!ctx->joined) return fail(ctx, CC_ERR_ARG, "cc_sc_rescue before cc_dcs_join");
+    if (!ctx->params.scorrect) return fail(ctx, CC_ERR_ARG, "cc_sc_rescue with params.scorrect == 0");
+    CK(cudaSetDevice(ctx->device));
+    TRY(do_rescue(ctx));
+    TRY(do_duplex(ctx, true));
+    ctx->rescued = true;
+    return CC_OK;
+}
+
+int cc_run(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (!ctx->have_reads) return fail(ctx, CC_ERR_ARG, "cc_run before cc_load_reads");
+    CK(cudaSetDevice(ctx->device));
+    TRY(do_group(ctx));
+    TRY(do_join_index(ctx));
+    TRY(do_lists(ctx, true));
+    TRY(do_vote(ctx));
+    if (ctx->params.scorrect) TRY(do_rescue(ctx));
+    TRY(do_duplex(ctx, false));
+    ctx->joined = true;
+    if (ctx->params.scorrect) {
+        TRY(do_duplex(ctx, true));
+        ctx->rescued = true;
+    }
+    return read_counters(ctx);     // synchronises; surfaces a base error raised by the vote kernel
+}
+
+int cc_run_host(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n, uint32_t lpad,
+                uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc)
+{
+    TRY(cc_load_reads(ctx, fields, payload, n, lpad, stride, dup_bc, n_bc));
+    return cc_run(ctx);
+}
+
+int cc_counts(cc_ctx *ctx, uint64_t counts[8])
+{
+    if (!ctx || !counts) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    TRY(read_counters(ctx));
+    memset(counts, 0, 8 * sizeof(uint64_t));
+    counts[CC_N_READS] = ctx->n; counts[CC_N_FAM] = ctx->n_fam; counts[CC_N_SSCS] = ctx->n_sscs;
+    counts[CC_N_CORR] = ctx->n_corr; counts[CC_N_DCS] = ctx->n_dcs; counts[CC_N_DCSSC] = ctx->n_dcssc;
+    return CC_OK;
+}
+
+static const void *array_ptr(cc_ctx *ctx, int what, uint64_t *bytes)
+{
+    const uint64_t nf = ctx->n_fam, S = ctx->stride;
+    *bytes = 0;
+    if (!ctx->grouped) return nullptr;
+    switch (what) {
+    case CC_READ_FAM: *bytes = ctx->n * 4; return ctx->spare_vals;
+    case CC_FAM_SIZE: *bytes = nf * 4; return ctx->fam_size.p;
+    case CC_FAM_TMPL: *bytes = nf * 4; return ctx->tmpl.p;
+    case CC_FAM_MAPQ: *bytes = nf; return ctx->fam_mapq.p;
+    case CC_FAM_FLAG: *bytes = nf * 2; return ctx->fam_flag.p;
+    case CC_FAM_TLEN: *bytes = nf * 4; return ctx->fam_tlen.p;
+    case CC_FAM_RG: *bytes = nf; return ctx->fam_rg.p;
+    case CC_PARTNER: if (!ctx->joined) return nullptr; *bytes = nf * 4; return ctx->partner.p;
+    case CC_SSCS_ROW: if (!ctx->listed) return nullptr; *bytes = nf * 4; return ctx->sscs_row.p;
+    case CC_CORR_ROW: if (!ctx->joined) return nullptr; *bytes = nf * 4; return ctx->corr_row.p;
+    case CC_DCS_ROW: if (!ctx->joined) return nullptr; *bytes = nf * 4; return ctx->dcs_row.p;
+    case CC_DCSSC_ROW: if (!ctx->joined) return nullptr; *bytes = nf * 4; return ctx->dcssc_row.p;
+    case CC_SSCS_ROWS: if (!ctx->voted) return nullptr; *bytes = ctx->n_sscs * S; return ctx->sscs_rows.p;
+    case CC_CORR_ROWS: if (!ctx->rescued) return nullptr; *bytes = ctx->n_corr * S; return ctx->corr_rows.p;
+    case CC_DCS_ROWS: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs * S; return ctx->dcs_rows.p;
+    case CC_DCSSC_ROWS: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * S; return ctx->dcssc_rows.p;
+    case CC_DCS_MAPQ: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs; return ctx->dcs_mapq.p;
+    case CC_DCS_FLAG: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs * 2ull; return ctx->dcs_flag.p;
+    case CC_DCS_TLEN: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs * 4ull; return ctx->dcs_tlen.p;
+    case CC_DCS_RG: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs; return ctx->dcs_rg.p;
+    case CC_DCSSC_MAPQ: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcssc_mapq.p;
+    case CC_DCSSC_FLAG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 2ull; return ctx->dcssc_flag.p;
+    case CC_DCSSC_TLEN: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 4ull; return ctx->dcssc_tlen.p;
+    case CC_DCSSC_RG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcssc_rg.p;
+    case CC_STATS: *bytes = 16 * 8; return ctx->stats.p;
+    case CC_FAM_HIST: *bytes = CC_HIST_BINS * 8ull; return ctx->hist.p;
+    default: return nullptr;
+    }
+}
+
+uint64_t cc_array_bytes(cc_ctx *ctx, int what)
+{
+    if (!ctx) return 0;
+    uint64_t bytes = 0;
+    array_ptr(ctx, what, &bytes);
+    return bytes;
+}
+
+static int materialise(cc_ctx *ctx, int what)
+{
+    if (what == CC_READ_FAM && !ctx->read_fam_ready && ctx->n_fam) {
+        LAUNCH(read_fam_kernel, blocks_for((uint64_t)ctx->n_fam * 32, 256), 256, ptr<uint32_t>(ctx->fam_start),
+               ptr<uint32_t>(ctx->fam_size), ctx->perm, ctx->n_fam, ctx->spare_vals);
+        ctx->read_fam_ready = true;
+    }
+    return CC_OK;
+}
+
+const void *cc_device_ptr(cc_ctx *ctx, int what)
+{
+    if (!ctx) return nullptr;
+    uint64_t bytes = 0;
+    const void *p = array_ptr(ctx, what, &bytes);
+    if (!p || bytes == 0) return nullptr;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || materialise(ctx, what) != CC_OK) return nullptr;
+    return p;
+}
+
+int cc_fetch(cc_ctx *ctx, int what, void *host_dst, uint64_t bytes)
+{
+    if (!ctx) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    uint64_t have = 0;
+    const void *p = array_ptr(ctx, what, &have);
+    if (!p && have == 0 && !(ctx->grouped && bytes == 0)) {
+        if (bytes == 0) return CC_OK;
+        return fail(ctx, CC_ERR_ARG, "cc_fetch: array not produced yet");
+    }
+    if (bytes != have) return fail(ctx, CC_ERR_ARG, "cc_fetch: size mismatch (use cc_array_bytes)");
+    if (bytes == 0) return CC_OK;
+    if (!host_dst) return fail(ctx, CC_ERR_ARG, "cc_fetch: NULL destination");
+    TRY(materialise(ctx, what));
+    CK(cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return CC_OK;
+}
+
+int cc_consensus_maker(cc_ctx *ctx, const uint8_t *rows, uint32_t n, uint32_t lpad, uint32_t stride, double cutoff,
+                       uint8_t *out_row)
+{
+    if (!ctx || !rows || !out_row || n == 0) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (lpad == 0 || lpad % 32 || stride % 64 || stride < lpad / 2 + lpad)
+        return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride % 64 == 0, stride >= 3*lpad/2");
+    // one family: perm = identity, one segment [0, n), mode fields are discarded
+    const size_t meta = 4096;
+    TRY(ensure(ctx, ctx->tmp_a, (size_t)n * stride));
+    TRY(ensure(ctx, ctx->tmp_b, (size_t)n * 4 + meta + (size_t)n * 32));
+    TRY(ensure(ctx, ctx->tmp_c, (size_t)stride + 64));
+    uint8_t *base = ptr<uint8_t>(ctx->tmp_b);
+    uint32_t *perm = reinterpret_cast<uint32_t *>(base + meta + (size_t)n * 32);
+    uint32_t *small = reinterpret_cast<uint32_t *>(base);         // start, size, list, err, out meta
+    uint4 *fields = reinterpret_cast<uint4 *>(base + meta);
+    CK(cudaMemcpyAsync(ctx->tmp_a.p, rows, (size_t)n * stride, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(base, 0, meta + (size_t)n * 32, ctx->stream));
+    uint32_t hdr[2] = {0, n};
+    CK(cudaMemcpyAsync(small, hdr, sizeof(hdr), cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(iota_kernel, blocks_for(n, 256), 256, perm, n);
+    LAUNCH(vote_kernel, 1, 32, fields, ptr<uint8_t>(ctx->tmp_a), stride, lpad, perm, small + 0, small + 1, small + 2, 1u,
+           cutoff, ptr<uint8_t>(ctx->tmp_c), reinterpret_cast<uint8_t *>(small + 16), reinterpret_cast<uint16_t *>(small + 20),
+           reinterpret_cast<int32_t *>(small + 24), reinterpret_cast<uint8_t *>(small + 28), small + 8);
+    uint32_t err = 0;
+    CK(cudaMemcpyAsync(out_row, ctx->tmp_c.p, stride, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&err, small + 8, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (err)
+        return fail(ctx, CC_ERR_BASE, "a base other than A/C/G/T carries Q>=30 "
+                                      "(the reference raises IndexError/ValueError, SSCS_maker.py:119-122)");
+    return CC_OK;
+}
+
+int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2, uint64_t n_pairs, uint32_t lpad,
+                        uint32_t stride, int sc, uint8_t *out_rows)
+{
+    if (!ctx || !rows1 || !rows2 || !out_rows) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (lpad == 0 || lpad % 32 || stride % 64 || stride < lpad / 2 + lpad)
+        return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride % 64 == 0, stride >= 3*lpad/2");
+    if (n_pairs == 0) return CC_OK;
+    const size_t bytes = (size_t)n_pairs * stride;
+    TRY(ensure(ctx, ctx->tmp_a, bytes)); TRY(ensure(ctx, ctx->tmp_b, bytes)); TRY(ensure(ctx, ctx->tmp_c, bytes));
+    CK(cudaMemcpyAsync(ctx->tmp_a.p, rows1, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->tmp_b.p, rows2, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const uint32_t g = lpad / 8;
+    auto kernel = sc ? agree_pairs_kernel<true> : agree_pairs_kernel<false>;
+    LAUNCH(kernel, blocks_for(n_pairs * g, 256), 256, ptr<uint8_t>(ctx->tmp_a),
+           ptr<uint8_t>(ctx->tmp_b), n_pairs, lpad, stride, g, ptr<uint8_t>(ctx->tmp_c));
+    CK(cudaMemcpyAsync(out_rows, ctx->tmp_c.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return CC_OK;
+}
+
+int cc_profile(cc_ctx *ctx, int enable)
+{
+    if (!ctx) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    TRY(collect_phases(ctx));
+    for (auto &t : ctx->phase) { t.ms = 0.0; t.runs = 0; }
+    ctx->profile = enable != 0;
+    return CC_OK;
+}
+
+int cc_phase_ms(cc_ctx *ctx, int phase, double *ms, uint64_t *launches)
+{
+    if (!ctx || phase < 0 || phase >= CC_PH_COUNT) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    TRY(collect_phases(ctx));
+    if (ms) *ms = ctx->phase[phase].ms;
+    if (launches) *launches = ctx->phase[phase].runs;
+    return CC_OK;
+}
+
+uint64_t cc_kernel_launches(cc_ctx *ctx) { return ctx ? ctx->launches : 0; }
+uint64_t cc_device_bytes(cc_ctx *ctx) { return ctx ? ctx->dev_bytes : 0; }
+
+}  // extern "C"

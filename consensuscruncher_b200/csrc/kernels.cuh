@@ -1,0 +1,608 @@
+// Device kernels of the consensus path (sm_100a).  Each kernel names the
+// reference code it replaces (paths relative to the reference repository).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ccgpu {
+
+constexpr uint32_t NO_ID = 0xFFFFFFFFu;
+constexpr int Q_SSCS = 30;   // SSCS_maker.py:113  "query_qualities[i] < 30" fails a base
+constexpr int Q_SC = 29;     // singleton_correction.py:72  both qualities "> 29"
+constexpr int Q_CAP = 60;    // SSCS_maker.py:134, DCS_maker.py:113  quality ceiling
+
+// ---- field records -------------------------------------------------------------
+// 32-byte record = two 16-byte halves: a = (bc, cig, tid, pos), b = (mtid, mpos, tlen, meta)
+// with meta = flag | mapq << 16 | rg << 24.
+struct Rec { uint4 a, b; };
+
+__device__ __forceinline__ Rec load_rec(const uint4 *__restrict__ fields, uint32_t i)
+{
+    Rec r;
+    r.a = __ldg(&fields[2 * (uint64_t)i]);
+    r.b = __ldg(&fields[2 * (uint64_t)i + 1]);
+    return r;
+}
+
+// orientation (flag 0x10) and read number (flag 0x40) of unique_tag, consensus_helper.py:286-290
+__device__ __forceinline__ uint32_t key_bits(uint32_t meta) { return ((meta >> 4) & 1u) | (((meta >> 6) & 1u) << 1); }
+
+__device__ __forceinline__ bool same_tag(const Rec &x, const Rec &y)
+{
+    return x.a.x == y.a.x && x.a.y == y.a.y && x.a.z == y.a.z && x.a.w == y.a.w &&
+           x.b.x == y.b.x && x.b.y == y.b.y && key_bits(x.b.w) == key_bits(y.b.w);
+}
+
+__device__ __forceinline__ uint64_t mix64(uint64_t h, uint32_t w)
+{
+    h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+    return h ^ (h >> 32);
+}
+
+// 64-bit hash of the unique_tag tuple; low word = sort key, high word = join tag
+__device__ __forceinline__ uint64_t tag_hash(uint32_t bc, uint32_t cig, uint32_t tid, uint32_t pos,
+                                             uint32_t mtid, uint32_t mpos, uint32_t bits)
+{
+    uint64_t h = 0x243F6A8885A308D3ull;
+    h = mix64(h, bc); h = mix64(h, cig); h = mix64(h, tid); h = mix64(h, pos);
+    h = mix64(h, mtid); h = mix64(h, mpos); h = mix64(h, bits);
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+    return h;
+}
+
+__device__ __forceinline__ uint64_t rec_hash(const Rec &r)
+{
+    return tag_hash(r.a.x, r.a.y, r.a.z, r.a.w, r.b.x, r.b.y, key_bits(r.b.w));
+}
+
+// ---- K1: sort key of every read (unique_tag, consensus_helper.py:293-301) ---------
+__global__ void __launch_bounds__(256)
+hash_kernel(const uint4 *__restrict__ fields, uint64_t n, uint32_t key_mask, uint32_t *__restrict__ keys)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Rec r = load_rec(fields, (uint32_t)i);
+    keys[i] = (uint32_t)rec_hash(r) & key_mask;
+}
+
+// ---- K3: exact family boundaries in sorted order -------------------------------------
+// head[j] = 1 iff read perm[j] starts a family.  Reads with equal sort key but
+// different tags ("mixed runs", hash collisions) are queued for fix_mixed_runs.
+__global__ void __launch_bounds__(256)
+boundary_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ keys,
+                const uint32_t *__restrict__ perm, uint64_t n, uint8_t *__restrict__ head,
+                uint32_t *__restrict__ mixed_list, uint32_t *__restrict__ mixed_count, uint32_t mixed_cap)
+{
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    if (j == 0) { head[0] = 1; return; }
+    Rec cur = load_rec(fields, perm[j]);
+    Rec prv = load_rec(fields, perm[j - 1]);
+    bool differs = !same_tag(cur, prv);
+    head[j] = differs ? 1 : 0;
+    uint32_t k = keys[j];
+    if (differs && k == keys[j - 1]) {
+        // only the first tag change inside a run reports the run
+        uint64_t s = j - 1;
+        bool first = true;
+        while (s > 0 && keys[s - 1] == k) {
+            Rec p2 = load_rec(fields, perm[s - 1]);
+            if (!same_tag(prv, p2)) { first = false; break; }
+            prv = p2;
+            --s;
+        }
+        if (first) {
+            uint32_t slot = atomicAdd(mixed_count, 1u);
+            if (slot < mixed_cap) mixed_list[slot] = (uint32_t)s;
+        }
+    }
+}
+
+// One warp per mixed run: stable regrouping by tag, in order of first appearance.
+__global__ void __launch_bounds__(128)
+fix_mixed_runs_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ keys,
+                      uint32_t *__restrict__ perm, uint32_t *__restrict__ tmp, uint64_t n,
+                      uint8_t *__restrict__ head, const uint32_t *__restrict__ mixed_list, uint32_t n_mixed)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_mixed) return;
+    const uint64_t s = mixed_list[w];
+    const uint32_t k = keys[s];
+    uint64_t e = s + 1;
+    while (e < n && keys[e] == k) ++e;            // every lane walks the same (short) run
+    const uint32_t lt = (1u << lane) - 1u;
+    uint64_t out = s;
+    while (out < e) {
+        // first read not yet regrouped
+        uint64_t first = e;
+        for (uint64_t k0 = s; k0 < e && first == e; k0 += 32) {
+            uint64_t x = k0 + lane;
+            bool open = x < e && !(perm[x] >> 31);
+            uint32_t b = __ballot_sync(0xffffffffu, open);
+            if (b) first = k0 + __ffs(b) - 1;
+        }
+        Rec t = load_rec(fields, perm[first]);
+        uint64_t head_at = out;
+        for (uint64_t k0 = s; k0 < e; k0 += 32) {
+            uint64_t x = k0 + lane;
+            bool take = false;
+            uint32_t v = 0;
+            if (x < e) {
+                v = perm[x];
+                if (!(v >> 31)) take = same_tag(load_rec(fields, v), t);
+            }
+            uint32_t b = __ballot_sync(0xffffffffu, take);
+            if (take) {
+                uint64_t dst = out + __popc(b & lt);
+                tmp[dst] = v;
+                head[dst] = dst == head_at ? 1 : 0;
+                perm[x] = v | 0x80000000u;
+            }
+            out += __popc(b);
+        }
+        __syncwarp();
+    }
+    for (uint64_t x = s + lane; x < e; x += 32) perm[x] = tmp[x];
+}
+
+// ---- families in creation order -----------------------------------------------------
+// mark[first member of sorted family f] = f + 1   (stable sort => first member = min index)
+__global__ void __launch_bounds__(256)
+mark_first_kernel(const uint32_t *__restrict__ hs_start, const uint32_t *__restrict__ perm,
+                  uint32_t n_fam, uint32_t *__restrict__ mark)
+{
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < n_fam) mark[perm[hs_start[f]]] = f + 1;
+}
+
+// family c (creation order) -> its segment of perm, size, singleton meta, size histogram
+__global__ void __launch_bounds__(256)
+family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ c2hs,
+                    const uint32_t *__restrict__ hs_start, const uint32_t *__restrict__ tmpl,
+                    uint32_t n_fam, uint32_t n_reads, uint32_t *__restrict__ fam_start,
+                    uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
+                    uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag,
+                    int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
+                    unsigned long long *__restrict__ hist, uint32_t hist_bins)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_fam) return;
+    uint32_t f = c2hs[c];
+    uint32_t s = hs_start[f];
+    uint32_t e = (f + 1 < n_fam) ? hs_start[f + 1] : n_reads;
+    uint32_t size = e - s;
+    fam_start[c] = s;
+    fam_size[c] = size;
+    is_sscs[c] = size >= 2;
+    // a singleton keeps its own fields (SSCS_maker.py:278-282); larger families are
+    // overwritten by the vote kernel's mode fields
+    Rec r = load_rec(fields, tmpl[c]);
+    fam_tlen[c] = (int32_t)r.b.z;
+    fam_flag[c] = (uint16_t)(r.b.w & 0xFFFF);
+    fam_mapq[c] = (uint8_t)((r.b.w >> 16) & 0xFF);
+    fam_rg[c] = (uint8_t)(r.b.w >> 24);
+    uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
+    atomicAdd(&hist[bin], 1ull);
+}
+
+// Pair symmetry check (SSCS_maker.py:275 emits a pair name only with exactly two tags):
+// the mate of a family's template must be the template of the neighbouring family, of equal size.
+__global__ void __launch_bounds__(256)
+domain_check_kernel(const uint32_t *__restrict__ tmpl, const uint32_t *__restrict__ fam_size,
+                    uint32_t n_fam, uint32_t *__restrict__ faults)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_fam) return;
+    uint32_t o = c ^ 1u;
+    bool ok = o < n_fam && tmpl[o] == (tmpl[c] ^ 1u) && fam_size[o] == fam_size[c];
+    if (!ok) atomicAdd(faults, 1u);
+}
+
+// read -> family (only materialised when a caller fetches CC_READ_FAM)
+__global__ void __launch_bounds__(256)
+read_fam_kernel(const uint32_t *__restrict__ fam_start, const uint32_t *__restrict__ fam_size,
+                const uint32_t *__restrict__ perm, uint32_t n_fam, uint32_t *__restrict__ read_fam)
+{
+    const int lane = threadIdx.x & 31;
+    uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (c >= n_fam) return;
+    uint32_t s = fam_start[c], n = fam_size[c];
+    for (uint32_t j = lane; j < n; j += 32) read_fam[perm[s + j]] = c;
+}
+
+// ---- K6: complementary-key hash join (duplex_tag, consensus_helper.py:605-648) -------------
+// table entry: high word = join tag of the family's key hash, low word = family id + 1
+__global__ void __launch_bounds__(256)
+join_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, uint32_t n_fam,
+                  unsigned long long *__restrict__ table, uint64_t mask)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_fam) return;
+    Rec r = load_rec(fields, tmpl[c]);
+    uint64_t h = rec_hash(r);
+    unsigned long long entry = ((h >> 32) << 32) | (unsigned long long)(c + 1);
+    uint64_t slot = (h * 0xD6E8FEB86659FD93ull >> 20) & mask;
+    while (atomicCAS(&table[slot], 0ull, entry) != 0ull) slot = (slot + 1) & mask;
+}
+
+__global__ void __launch_bounds__(256)
+join_probe_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, uint32_t n_fam,
+                  const uint32_t *__restrict__ dup_bc, uint32_t n_bc,
+                  const unsigned long long *__restrict__ table, uint64_t mask, int32_t *__restrict__ partner)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_fam) return;
+    Rec r = load_rec(fields, tmpl[c]);
+    int32_t found = -1;
+    uint32_t d = r.a.x < n_bc ? __ldg(&dup_bc[r.a.x]) : NO_ID;
+    if (d != NO_ID) {
+        Rec q = r;
+        q.a.x = d;                 // barcode halves swapped
+        q.b.w ^= 0x40u;            // R1 <-> R2 (only the key bits of meta are compared)
+        uint64_t h = rec_hash(q);
+        uint32_t tag = (uint32_t)(h >> 32);
+        uint64_t slot = (h * 0xD6E8FEB86659FD93ull >> 20) & mask;
+        for (;;) {
+            unsigned long long e = table[slot];
+            if (e == 0ull) break;
+            if ((uint32_t)(e >> 32) == tag) {
+                uint32_t o = (uint32_t)e - 1u;
+                if (same_tag(load_rec(fields, tmpl[o]), q)) { found = (int32_t)o; break; }
+            }
+            slot = (slot + 1) & mask;
+        }
+    }
+    partner[c] = found;
+}
+
+// ---- classification of families into output classes ----------------------------------------
+// DCS_maker.py:233-253 (lead strand makes the DCS, the other is skipped, no partner ->
+// SSCS singleton); singleton_correction.py:258-283; second DCS pass over the merge of
+// sscs + sscs.correction + singleton.correction (ConsensusCruncher.py:247-270).
+__device__ __forceinline__ bool leads_after_sc(uint32_t c, uint32_t p, bool c_big, bool p_big)
+{
+    if (c_big != p_big) return c_big;   // sscs records precede correction records in the merge
+    return c < p;
+}
+
+__global__ void __launch_bounds__(256)
+classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict__ partner, uint32_t n_fam,
+                int scorrect, uint8_t *__restrict__ f_dcs, uint8_t *__restrict__ f_corr,
+                uint8_t *__restrict__ f_dcssc, unsigned long long *__restrict__ stats)
+{
+    __shared__ unsigned int s_st[16];
+    if (threadIdx.x < 16) s_st[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n_fam) {
+        bool big = fam_size[c] >= 2;
+        int32_t p = partner[c];
+        bool p_big = p >= 0 && fam_size[p] >= 2;
+        bool dcs = big && p_big && c < (uint32_t)p;
+        bool corr = scorrect && !big && p >= 0;
+        bool dcssc = scorrect && p >= 0 && leads_after_sc(c, (uint32_t)p, big, p_big);
+        f_dcs[c] = dcs; f_corr[c] = corr; f_dcssc[c] = dcssc;
+        atomicAdd(&s_st[big ? 0 : 1], 1u);
+        if (dcs) atomicAdd(&s_st[2], 1u);
+        if (big && !p_big) atomicAdd(&s_st[3], 1u);
+        if (scorrect) {
+            if (!big && p_big) atomicAdd(&s_st[4], 1u);
+            if (!big && p >= 0 && !p_big) atomicAdd(&s_st[5], 1u);
+            if (!big && p < 0) atomicAdd(&s_st[6], 1u);
+            if (dcssc) atomicAdd(&s_st[7], 1u);
+            if (big && p < 0) atomicAdd(&s_st[8], 1u);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 16 && s_st[threadIdx.x]) atomicAdd(&stats[threadIdx.x], (unsigned long long)s_st[threadIdx.x]);
+}
+
+// row[list[r]] = r for the families that own a row; everything else stays -1
+__global__ void __launch_bounds__(256)
+rows_from_list_kernel(const uint32_t *__restrict__ list, uint32_t n_rows, int32_t *__restrict__ row)
+{
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n_rows) row[list[r]] = (int32_t)r;
+}
+
+// ---- K4 + K5: SSCS vote and family mode fields ------------------------------------------------
+// consensus_maker (SSCS_maker.py:103-155): per position, among bases with Q >= 30, the
+// first maximum of A,C,G,T wins; quality = min(60, sum of the winner's qualities); the
+// winner is emitted iff count / passing >= cutoff (fp64), else N with the same quality.
+// Because a passing quality is >= 30, the capped sum is 60 as soon as two reads agree and
+// the single read's own quality otherwise, so only counts and an OR of qualities are kept.
+//
+// One warp per family, lane <-> 4 consecutive positions of a 128-position chunk.
+struct VoteAcc {
+    uint32_t cnt[4];   // A,C,G,T counts, one byte lane per position (flushed before 256)
+    uint32_t qor[4];   // OR of passing qualities per base, one byte lane per position
+};
+
+__device__ __forceinline__ uint32_t expand_nibbles(uint32_t s16)
+{
+    // s16 = two sequence bytes (4 bases, high nibble first) -> one base per byte, position order
+    uint32_t hi = (s16 >> 4) & 0x0F0Fu;      // positions 0 and 2
+    uint32_t lo = s16 & 0x0F0Fu;             // positions 1 and 3
+    return __byte_perm(hi, lo, 0x5140);
+}
+
+__device__ __forceinline__ void vote_row(VoteAcc &a, uint32_t q, uint32_t s16, uint32_t &err)
+{
+    // byte-wise q >= 30  (bit 7 after adding 128-30; values >= 128 pass through the OR)
+    uint32_t pass7 = ((((q & 0x7F7F7F7Fu) + 0x62626262u) | q) & 0x80808080u);
+    uint32_t pass1 = pass7 >> 7;
+    uint32_t b = expand_nibbles(s16) & (pass1 * 15u);
+    uint32_t e0 = b & 0x01010101u, e1 = (b >> 1) & 0x01010101u;
+    uint32_t e2 = (b >> 2) & 0x01010101u, e3 = (b >> 3) & 0x01010101u;
+    err |= (e0 + e1 + e2 + e3) ^ pass1;      // a passing base must be exactly one of A,C,G,T
+    a.cnt[0] += e0; a.cnt[1] += e1; a.cnt[2] += e2; a.cnt[3] += e3;
+    a.qor[0] |= q & (e0 * 0xFFu); a.qor[1] |= q & (e1 * 0xFFu);
+    a.qor[2] |= q & (e2 * 0xFFu); a.qor[3] |= q & (e3 * 0xFFu);
+}
+
+// mode of one field over a family, ties -> first appearance (what randint -> 0 selects in
+// read_mode, consensus_helper.py:491-495); flags prefer 99 > 83 > 147 > 163 on a tie (:521-531)
+__device__ __forceinline__ int flag_rank(uint32_t v) { return v == 99 ? 0 : v == 83 ? 1 : v == 147 ? 2 : v == 163 ? 3 : 4; }
+
+template <typename Get>
+__device__ uint32_t warp_mode(Get get, uint32_t n, bool is_flag, int lane)
+{
+    uint32_t best = 0, best_cnt = 0;
+    int best_rank = 9;
+    uint32_t counted = 0;
+    for (uint32_t i = 0; counted < n && i < n; i++) {
+        uint32_t vi = get(i);
+        uint32_t cnt = 0;
+        bool seen_before = false;
+        for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+            uint32_t j = j0 + lane;
+            bool m = j < n && get(j) == vi;
+            uint32_t b = __ballot_sync(0xffffffffu, m);
+            if (cnt == 0 && b && j0 + (uint32_t)__ffs(b) - 1u < i) { seen_before = true; break; }
+            cnt += __popc(b);
+        }
+        if (seen_before) continue;
+        counted += cnt;
+        int rank = is_flag ? flag_rank(vi) : 4;
+        if (cnt > best_cnt || (cnt == best_cnt && rank < best_rank)) { best = vi; best_cnt = cnt; best_rank = rank; }
+    }
+    return best;
+}
+
+__global__ void __launch_bounds__(256)
+vote_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
+            uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ fam_start,
+            const uint32_t *__restrict__ fam_size, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
+            double cutoff, uint8_t *__restrict__ out_rows, uint8_t *__restrict__ fam_mapq,
+            uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
+            uint32_t *__restrict__ err_flag)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= n_rows) return;
+    const uint32_t c = sscs_list[row];
+    const uint32_t start = fam_start[c], n = fam_size[c];
+    const uint32_t half = lpad >> 1;
+    uint8_t *out = out_rows + (uint64_t)row * stride;
+    uint32_t err = 0;
+
+    for (uint32_t chunk = 0; chunk * 128 < lpad; chunk++) {
+        const uint32_t p0 = chunk * 128 + lane * 4;           // first of this lane's 4 positions
+        const bool active = p0 < lpad;
+        uint32_t wide[4][4];                                   // [base][position] for families > 255 reads
+#pragma unroll
+        for (int bi = 0; bi < 4; bi++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) wide[bi][k] = 0;
+        VoteAcc acc;
+#pragma unroll
+        for (int bi = 0; bi < 4; bi++) { acc.cnt[bi] = 0; acc.qor[bi] = 0; }
+        uint32_t since_flush = 0;
+        for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+            // lanes fetch 32 member indices at once, then the warp walks the rows together
+            uint32_t mine = (j0 + lane < n) ? perm[start + j0 + lane] : 0;
+            uint32_t lim = min(32u, n - j0);
+            for (uint32_t jj = 0; jj < lim; jj++) {
+                uint32_t r = __shfl_sync(0xffffffffu, mine, jj);
+                if (active) {
+                    const uint8_t *src = payload + (uint64_t)r * stride;
+                    uint32_t s16 = *reinterpret_cast<const uint16_t *>(src + (p0 >> 1));
+                    uint32_t q = *reinterpret_cast<const uint32_t *>(src + half + p0);
+                    vote_row(acc, q, s16, err);
+                }
+                if (++since_flush == 255) {
+#pragma unroll
+                    for (int bi = 0; bi < 4; bi++) {
+#pragma unroll
+                        for (int k = 0; k < 4; k++) wide[bi][k] += (acc.cnt[bi] >> (8 * k)) & 0xFF;
+                        acc.cnt[bi] = 0;
+                    }
+                    since_flush = 0;
+                }
+            }
+        }
+        if (active) {
+            uint32_t seq_out = 0, q_out = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                uint32_t cA = wide[0][k] + ((acc.cnt[0] >> (8 * k)) & 0xFF);
+                uint32_t cC = wide[1][k] + ((acc.cnt[1] >> (8 * k)) & 0xFF);
+                uint32_t cG = wide[2][k] + ((acc.cnt[2] >> (8 * k)) & 0xFF);
+                uint32_t cT = wide[3][k] + ((acc.cnt[3] >> (8 * k)) & 0xFF);
+                uint32_t best = cA; int w = 0;                  // first maximum in A,C,G,T order
+                if (cC > best) { best = cC; w = 1; }
+                if (cG > best) { best = cG; w = 2; }
+                if (cT > best) { best = cT; w = 3; }
+                uint32_t pass = cA + cC + cG + cT;
+                uint32_t qw = (acc.qor[w] >> (8 * k)) & 0xFF;
+                uint32_t mq = best == 0 ? 0u : (best == 1 ? min(qw, (uint32_t)Q_CAP) : (uint32_t)Q_CAP);
+                uint32_t code = 15u;
+                if (pass != 0 && ((double)best / (double)pass) >= cutoff) code = 1u << w;
+                // positions 0,1 -> first sequence byte (high, low nibble); 2,3 -> second byte
+                seq_out |= code << ((k >> 1) * 8 + ((k & 1) ? 0 : 4));
+                q_out |= mq << (8 * k);
+            }
+            *reinterpret_cast<uint16_t *>(out + (p0 >> 1)) = (uint16_t)seq_out;
+            *reinterpret_cast<uint32_t *>(out + half + p0) = q_out;
+        }
+    }
+    for (uint32_t x = half + lpad + lane * 4; x < stride; x += 128) *reinterpret_cast<uint32_t *>(out + x) = 0;
+    if (err) atomicOr(err_flag, 1u);
+
+    // ---- mode fields of the family (create_aligned_segment, consensus_helper.py:569-583)
+    auto meta_of = [&](uint32_t j) { return __ldg(&fields[2 * (uint64_t)perm[start + j] + 1]); };
+    uint4 m0 = meta_of(0);
+    bool uniform = true, has_rg = true;
+    for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+        uint32_t j = j0 + lane;
+        uint4 m = j < n ? meta_of(j) : m0;
+        uniform = uniform && __all_sync(0xffffffffu, m.z == m0.z && m.w == m0.w);
+        has_rg = has_rg && __all_sync(0xffffffffu, (m.w >> 24) != 0xFFu);
+    }
+    uint32_t tlen = m0.z, flag = m0.w & 0xFFFF, mapq = (m0.w >> 16) & 0xFF, rg = m0.w >> 24;
+    if (!uniform) {
+        tlen = warp_mode([&](uint32_t j) { return meta_of(j).z; }, n, false, lane);
+        flag = warp_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, n, true, lane);
+        mapq = warp_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, n, false, lane);
+        rg = has_rg ? warp_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, n, false, lane) : 0xFFu;
+    }
+    if (lane == 0) {
+        fam_tlen[c] = (int32_t)tlen; fam_flag[c] = (uint16_t)flag;
+        fam_mapq[c] = (uint8_t)mapq; fam_rg[c] = (uint8_t)rg;
+    }
+}
+
+// ---- K7: duplex_consensus on two rows --------------------------------------------------------------
+// DCS_maker.py:107-119: equal bases -> base, min(60, q1+q2); else N, 0 (no quality filter).
+// singleton_correction.py:69-82: additionally both qualities must be > 29.
+// One thread handles 8 positions: 4 sequence bytes and 8 quality bytes of each row.
+template <bool SC>
+__device__ __forceinline__ void agree8(uint32_t s1, uint32_t s2, uint2 q1, uint2 q2, uint32_t &so, uint2 &qo)
+{
+    so = 0; qo.x = 0; qo.y = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        // position k: byte k/2 of the sequence word, high nibble when k is even
+        int sh = (k >> 1) * 8 + ((k & 1) ? 0 : 4);
+        uint32_t b1 = (s1 >> sh) & 15u, b2 = (s2 >> sh) & 15u;
+        uint32_t a = ((k < 4 ? q1.x : q1.y) >> ((k & 3) * 8)) & 0xFFu;
+        uint32_t b = ((k < 4 ? q2.x : q2.y) >> ((k & 3) * 8)) & 0xFFu;
+        bool ok = b1 == b2 && (!SC || (a > (uint32_t)Q_SC && b > (uint32_t)Q_SC));
+        uint32_t code = ok ? b1 : 15u;
+        uint32_t q = ok ? min(a + b, (uint32_t)Q_CAP) : 0u;
+        so |= code << sh;
+        if (k < 4) qo.x |= q << ((k & 3) * 8); else qo.y |= q << ((k & 3) * 8);
+    }
+}
+
+template <bool SC>
+__device__ __forceinline__ void agree_rows(const uint8_t *__restrict__ r1, const uint8_t *__restrict__ r2,
+                                           uint8_t *__restrict__ out, uint32_t lpad, uint32_t stride,
+                                           uint32_t g, uint32_t groups)
+{
+    const uint32_t half = lpad >> 1;
+    if (g < (lpad >> 3)) {
+        uint32_t s1 = *reinterpret_cast<const uint32_t *>(r1 + g * 4);
+        uint32_t s2 = *reinterpret_cast<const uint32_t *>(r2 + g * 4);
+        uint2 q1 = *reinterpret_cast<const uint2 *>(r1 + half + g * 8);
+        uint2 q2 = *reinterpret_cast<const uint2 *>(r2 + half + g * 8);
+        uint32_t so; uint2 qo;
+        agree8<SC>(s1, s2, q1, q2, so, qo);
+        *reinterpret_cast<uint32_t *>(out + g * 4) = so;
+        *reinterpret_cast<uint2 *>(out + half + g * 8) = qo;
+    }
+    for (uint32_t x = half + lpad + g * 4; x < stride; x += groups * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
+}
+
+// mode of two records (create_aligned_segment on [lead, partner]): equal -> value, else the
+// lead's value (first appearance); flags prefer 99 > 83 > 147 > 163
+__device__ __forceinline__ uint32_t pair_mode(uint32_t a, uint32_t b, bool is_flag)
+{
+    if (a == b) return a;
+    if (is_flag && flag_rank(b) < flag_rank(a)) return b;
+    return a;
+}
+
+struct RowSources {
+    const uint8_t *payload;       // original reads
+    const uint8_t *sscs_rows;
+    const uint8_t *corr_rows;
+    const uint32_t *tmpl;
+    const uint32_t *fam_size;
+    const int32_t *sscs_row;
+    const int32_t *corr_row;
+    uint32_t stride;
+};
+
+// singleton rescue: row r <-> singleton family corr_list[r]; partner SSCS consensus if the
+// partner family has one, else the partner singleton's original read
+__global__ void __launch_bounds__(256)
+rescue_kernel(RowSources src, const uint32_t *__restrict__ corr_list, const int32_t *__restrict__ partner,
+              uint32_t n_rows, uint32_t lpad, uint32_t groups, uint8_t *__restrict__ out_rows)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t row = (uint32_t)(t / groups), g = (uint32_t)(t % groups);
+    if (row >= n_rows) return;
+    uint32_t c = corr_list[row];
+    uint32_t p = (uint32_t)partner[c];
+    const uint8_t *mine = src.payload + (uint64_t)src.tmpl[c] * src.stride;
+    const uint8_t *other = src.fam_size[p] >= 2 ? src.sscs_rows + (uint64_t)src.sscs_row[p] * src.stride
+                                                : src.payload + (uint64_t)src.tmpl[p] * src.stride;
+    agree_rows<true>(mine, other, out_rows + (uint64_t)row * src.stride, lpad, src.stride, g, groups);
+}
+
+// DCS (after_sc = 0: both rows are SSCS consensus) or DCS over SSCS + corrected singletons
+__global__ void __launch_bounds__(256)
+duplex_kernel(RowSources src, const uint32_t *__restrict__ lead_list, const int32_t *__restrict__ partner,
+              uint32_t n_rows, uint32_t lpad, uint32_t groups, int after_sc, uint8_t *__restrict__ out_rows,
+              const uint8_t *__restrict__ fam_mapq, const uint16_t *__restrict__ fam_flag,
+              const int32_t *__restrict__ fam_tlen, const uint8_t *__restrict__ fam_rg,
+              uint8_t *__restrict__ o_mapq, uint16_t *__restrict__ o_flag, int32_t *__restrict__ o_tlen,
+              uint8_t *__restrict__ o_rg)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t row = (uint32_t)(t / groups), g = (uint32_t)(t % groups);
+    if (row >= n_rows) return;
+    uint32_t c = lead_list[row];
+    uint32_t p = (uint32_t)partner[c];
+    auto row_of = [&](uint32_t x) -> const uint8_t * {
+        if (!after_sc || src.fam_size[x] >= 2) return src.sscs_rows + (uint64_t)src.sscs_row[x] * src.stride;
+        return src.corr_rows + (uint64_t)src.corr_row[x] * src.stride;
+    };
+    agree_rows<false>(row_of(c), row_of(p), out_rows + (uint64_t)row * src.stride, lpad, src.stride, g, groups);
+    if (g == 0) {
+        o_mapq[row] = (uint8_t)pair_mode(fam_mapq[c], fam_mapq[p], false);
+        o_tlen[row] = (int32_t)pair_mode((uint32_t)fam_tlen[c], (uint32_t)fam_tlen[p], false);
+        o_flag[row] = (uint16_t)pair_mode(fam_flag[c], fam_flag[p], true);
+        uint32_t ra = fam_rg[c], rb = fam_rg[p];
+        o_rg[row] = (ra == 0xFFu || rb == 0xFFu) ? 0xFFu : (uint8_t)pair_mode(ra, rb, false);
+    }
+}
+
+// stand-alone duplex_consensus over independent row pairs (cc_duplex_consensus)
+template <bool SC>
+__global__ void __launch_bounds__(256)
+agree_pairs_kernel(const uint8_t *__restrict__ rows1, const uint8_t *__restrict__ rows2, uint64_t n_pairs,
+                   uint32_t lpad, uint32_t stride, uint32_t groups, uint8_t *__restrict__ out_rows)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t row = t / groups;
+    uint32_t g = (uint32_t)(t % groups);
+    if (row >= n_pairs) return;
+    agree_rows<SC>(rows1 + row * stride, rows2 + row * stride, out_rows + row * stride, lpad, stride, g, groups);
+}
+
+__global__ void fill_i32_kernel(int32_t *p, uint64_t n, int32_t v)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+__global__ void iota_kernel(uint32_t *p, uint32_t n)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = i;
+}
+
+}  // namespace ccgpu

@@ -1,0 +1,115 @@
+// Single-pass prefix sums with decoupled look-back (sm_100a).
+//
+// Three flavours share one kernel body:
+//   exclusive scan of u32 values                       -> out[i]
+//   compaction of the indices whose flag is non-zero   -> list[rank] = i
+//   compaction that also carries the flag value        -> list[rank] = i, carry[rank] = flag - 1
+// Tiles take their number from an atomic ticket so that a tile only ever waits
+// on tiles that have already started.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ccgpu {
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+struct ScanScratch {
+    unsigned long long *status;   // one word per tile: flag << 32 | value
+    uint32_t *ticket;             // tile ticket counter
+    uint64_t max_tiles;
+};
+
+__device__ __forceinline__ unsigned long long ld_status(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_status(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+enum { SCAN_MODE_EXCL = 0, SCAN_MODE_COMPACT = 1, SCAN_MODE_COMPACT_CARRY = 2 };
+
+// In: u32 values (MODE_EXCL), u8 flags (MODE_COMPACT) or u32 marks (MODE_COMPACT_CARRY).
+template <int MODE, typename InT>
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
+            uint64_t n, unsigned long long *status, uint32_t *ticket, uint32_t *total)
+{
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+    __shared__ uint32_t s_prefix;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint64_t base = (uint64_t)tile * SCAN_TILE + (uint64_t)tid * SCAN_ITEMS;
+
+    InT v[SCAN_ITEMS];
+    uint32_t w[SCAN_ITEMS];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        v[i] = (base + i < n) ? in[base + i] : (InT)0;
+        w[i] = (MODE == SCAN_MODE_EXCL) ? (uint32_t)v[i] : (v[i] != 0 ? 1u : 0u);
+        sum += w[i];
+    }
+    // block-wide exclusive prefix of the per-thread sums
+    uint32_t incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0, block_total = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_THREADS / 32; k++) {
+        uint32_t t = s_warp[k];
+        if (k < warp) warp_off += t;
+        block_total += t;
+    }
+    if (tid == 0) {
+        uint32_t excl = 0;
+        if (tile == 0) {
+            st_status(&status[0], (2ull << 32) | block_total);
+        } else {
+            st_status(&status[tile], (1ull << 32) | block_total);
+            for (int64_t p = (int64_t)tile - 1;; --p) {
+                unsigned long long s;
+                do { s = ld_status(&status[p]); } while ((s >> 32) == 0);
+                excl += (uint32_t)s;
+                if ((s >> 32) == 2) break;
+            }
+            st_status(&status[tile], (2ull << 32) | (uint32_t)(excl + block_total));
+        }
+        s_prefix = excl;
+        if (total != nullptr && tile == gridDim.x - 1)
+            *total = excl + block_total;      // the last tile publishes the grand total
+    }
+    __syncthreads();
+    uint32_t run = s_prefix + warp_off + (incl - sum);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        if (base + i < n) {
+            if (MODE == SCAN_MODE_EXCL) {
+                out[base + i] = run;
+            } else if (w[i]) {
+                out[run] = (uint32_t)(base + i);
+                if (MODE == SCAN_MODE_COMPACT_CARRY) carry[run] = (uint32_t)v[i] - 1u;
+            }
+        }
+        run += w[i];
+    }
+}
+
+inline uint64_t scan_tiles(uint64_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
+
+}  // namespace ccgpu

@@ -1,0 +1,252 @@
+"""ctypes binding of libccgpu.so (include/ccgpu.h) and the `GpuConsensus` engine.
+
+There is no CPU fallback: importing this module is harmless, but creating an
+engine without the built library or without an sm_100 GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+from .pack import DomainError, PackedReads
+from .result import ConsensusResult
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libccgpu.so")
+
+# enum cc_array / element types (include/ccgpu.h)
+ARRAYS = {
+    "read_fam": (0, np.uint32), "fam_size": (1, np.uint32), "fam_tmpl": (2, np.uint32),
+    "fam_mapq": (3, np.uint8), "fam_flag": (4, np.uint16), "fam_tlen": (5, np.int32),
+    "fam_rg": (6, np.uint8), "partner": (7, np.int32), "sscs_row": (8, np.int32),
+    "corr_row": (9, np.int32), "dcs_row": (10, np.int32), "dcssc_row": (11, np.int32),
+    "sscs_rows": (12, np.uint8), "corr_rows": (13, np.uint8), "dcs_rows": (14, np.uint8),
+    "dcssc_rows": (15, np.uint8), "dcs_mapq": (16, np.uint8), "dcs_flag": (17, np.uint16),
+    "dcs_tlen": (18, np.int32), "dcs_rg": (19, np.uint8), "dcssc_mapq": (20, np.uint8),
+    "dcssc_flag": (21, np.uint16), "dcssc_tlen": (22, np.int32), "dcssc_rg": (23, np.uint8),
+    "stats": (24, np.int64), "fam_hist": (25, np.uint64),
+}
+PHASES = ("h2d", "hash", "sort", "segment", "join", "classify", "vote", "rescue", "dcs", "dcs_sc")
+CC_ERR_BASE, CC_ERR_DOMAIN = -4, -5
+
+# every symbol include/ccgpu.h declares
+SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_stream", "cc_load_reads",
+           "cc_load_reads_device", "cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run",
+           "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
+           "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes")
+
+
+class CcParams(ctypes.Structure):
+    _fields_ = [("cutoff", ctypes.c_double), ("scorrect", ctypes.c_int32)]
+
+
+class GpuError(RuntimeError):
+    pass
+
+
+class BaseError(GpuError):
+    """N / IUPAC base with Q>=30 in a family (reference: IndexError / ValueError)."""
+
+
+_lib = None
+
+
+def load_library(path=LIB_PATH):
+    """dlopen libccgpu.so and declare its prototypes.  Raises if it was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise GpuError("libccgpu.so is missing (%s): build it with `python -m consensuscruncher_b200.build`; "
+                       "this package has no CPU fallback" % path)
+    L = ctypes.CDLL(path)
+    vp, u64, u32, i32 = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int
+    L.cc_create.restype = vp
+    L.cc_create.argtypes = [i32, ctypes.POINTER(CcParams)]
+    L.cc_destroy.restype = None
+    L.cc_destroy.argtypes = [vp]
+    L.cc_last_error.restype = ctypes.c_char_p
+    L.cc_last_error.argtypes = [vp]
+    L.cc_set_params.argtypes = [vp, ctypes.POINTER(CcParams)]
+    L.cc_set_stream.argtypes = [vp, vp]
+    load_args = [vp, vp, vp, u64, u32, u32, vp, u32]
+    L.cc_load_reads.argtypes = load_args
+    L.cc_load_reads_device.argtypes = load_args
+    L.cc_run_host.argtypes = load_args
+    for nm in ("cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run"):
+        getattr(L, nm).argtypes = [vp]
+    L.cc_counts.argtypes = [vp, ctypes.POINTER(u64)]
+    L.cc_fetch.argtypes = [vp, i32, vp, u64]
+    L.cc_array_bytes.restype = u64
+    L.cc_array_bytes.argtypes = [vp, i32]
+    L.cc_device_ptr.restype = vp
+    L.cc_device_ptr.argtypes = [vp, i32]
+    L.cc_consensus_maker.argtypes = [vp, vp, u32, u32, u32, ctypes.c_double, vp]
+    L.cc_duplex_consensus.argtypes = [vp, vp, vp, u64, u32, u32, i32, vp]
+    L.cc_profile.argtypes = [vp, i32]
+    L.cc_phase_ms.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(u64)]
+    L.cc_kernel_launches.restype = u64
+    L.cc_kernel_launches.argtypes = [vp]
+    L.cc_device_bytes.restype = u64
+    L.cc_device_bytes.argtypes = [vp]
+    _lib = L
+    return L
+
+
+class GpuConsensus:
+    """One context on one GPU: group -> SSCS vote -> DCS join -> singleton rescue."""
+
+    def __init__(self, device=0, cutoff=0.7, scorrect=True):
+        self.lib = load_library()
+        self.params = CcParams(float(cutoff), 1 if scorrect else 0)
+        self.ctx = self.lib.cc_create(int(device), ctypes.byref(self.params))
+        if not self.ctx:
+            raise GpuError("cc_create(device=%d) failed: %s" %
+                           (device, self.lib.cc_last_error(None).decode()))
+        self.device = int(device)
+        self.lpad = self.stride = 0
+        self._keep = None
+
+    # -- plumbing ----------------------------------------------------------
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.cc_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc):
+        if rc == 0:
+            return
+        msg = self.lib.cc_last_error(self.ctx).decode()
+        if rc == CC_ERR_BASE:
+            raise BaseError(msg)
+        if rc == CC_ERR_DOMAIN:
+            raise DomainError(msg)
+        raise GpuError("libccgpu error %d: %s" % (rc, msg))
+
+    def set_params(self, cutoff=None, scorrect=None):
+        if cutoff is not None:
+            self.params.cutoff = float(cutoff)
+        if scorrect is not None:
+            self.params.scorrect = 1 if scorrect else 0
+        self._check(self.lib.cc_set_params(self.ctx, ctypes.byref(self.params)))
+
+    def set_stream(self, cuda_stream_handle):
+        self._check(self.lib.cc_set_stream(self.ctx, ctypes.c_void_p(cuda_stream_handle or 0)))
+
+    # -- input ---------------------------------------------------------------
+    def _host_args(self, packed: PackedReads):
+        fields = np.ascontiguousarray(packed.fields)
+        payload = np.ascontiguousarray(packed.payload)
+        dup = np.ascontiguousarray(packed.dup_bc, dtype=np.uint32)
+        self._keep = (fields, payload, dup)
+        self.lpad, self.stride = packed.lpad, (packed.stride or 64)
+        return (self.ctx, fields.ctypes.data, payload.ctypes.data, packed.n, packed.lpad,
+                self.stride, dup.ctypes.data, len(dup))
+
+    def load(self, packed: PackedReads):
+        """Host SoA -> device (cc_load_reads)."""
+        self._check(self.lib.cc_load_reads(*self._host_args(packed)))
+
+    def load_device(self, fields_ptr, payload_ptr, n, lpad, stride, dup_ptr, n_bc):
+        """Adopt buffers that already live in device memory (cc_load_reads_device)."""
+        self.lpad, self.stride = int(lpad), int(stride)
+        self._check(self.lib.cc_load_reads_device(self.ctx, fields_ptr, payload_ptr, int(n), int(lpad),
+                                                  int(stride), dup_ptr, int(n_bc)))
+
+    # -- stages --------------------------------------------------------------------
+    def group(self):
+        self._check(self.lib.cc_group(self.ctx))
+
+    def sscs_vote(self):
+        self._check(self.lib.cc_sscs_vote(self.ctx))
+
+    def dcs_join(self):
+        self._check(self.lib.cc_dcs_join(self.ctx))
+
+    def sc_rescue(self):
+        self._check(self.lib.cc_sc_rescue(self.ctx))
+
+    def run(self):
+        self._check(self.lib.cc_run(self.ctx))
+
+    def run_host(self, packed: PackedReads):
+        """cc_run_host: copy in and run every stage."""
+        self._check(self.lib.cc_run_host(*self._host_args(packed)))
+
+    # -- results --------------------------------------------------------------------
+    def counts(self):
+        c = (ctypes.c_uint64 * 8)()
+        self._check(self.lib.cc_counts(self.ctx, c))
+        return dict(reads=c[0], fam=c[1], sscs=c[2], corr=c[3], dcs=c[4], dcssc=c[5])
+
+    def fetch(self, name):
+        what, dt = ARRAYS[name]
+        nbytes = self.lib.cc_array_bytes(self.ctx, what)
+        out = np.zeros(nbytes // np.dtype(dt).itemsize, dt)
+        if nbytes:
+            self._check(self.lib.cc_fetch(self.ctx, what, out.ctypes.data, nbytes))
+        if name.endswith("_rows"):
+            out = out.reshape(-1, self.stride)
+        return out
+
+    def device_ptr(self, name):
+        return self.lib.cc_device_ptr(self.ctx, ARRAYS[name][0])
+
+    def result(self) -> ConsensusResult:
+        from .result import ALL_ARRAYS
+        arrays = {k: self.fetch(k) for k in ALL_ARRAYS}
+        return ConsensusResult(self.lpad, self.stride, bool(self.params.scorrect), **arrays)
+
+    def consensus(self, packed: PackedReads) -> ConsensusResult:
+        """The whole path on one batch: host SoA in, family-level results out."""
+        self.run_host(packed)
+        return self.result()
+
+    # -- stand-alone primitives ----------------------------------------------------
+    def consensus_maker_rows(self, rows, lpad, cutoff):
+        rows = np.ascontiguousarray(rows, np.uint8)
+        out = np.zeros(rows.shape[1], np.uint8)
+        self._check(self.lib.cc_consensus_maker(self.ctx, rows.ctypes.data, rows.shape[0], int(lpad),
+                                                rows.shape[1], float(cutoff), out.ctypes.data))
+        return out
+
+    def duplex_consensus_rows(self, rows1, rows2, lpad, sc):
+        rows1 = np.ascontiguousarray(np.atleast_2d(rows1), np.uint8)
+        rows2 = np.ascontiguousarray(np.atleast_2d(rows2), np.uint8)
+        out = np.zeros_like(rows1)
+        self._check(self.lib.cc_duplex_consensus(self.ctx, rows1.ctypes.data, rows2.ctypes.data,
+                                                 rows1.shape[0], int(lpad), rows1.shape[1],
+                                                 1 if sc else 0, out.ctypes.data))
+        return out
+
+    # -- timing ------------------------------------------------------------------------
+    def profile(self, enable=True):
+        self._check(self.lib.cc_profile(self.ctx, 1 if enable else 0))
+
+    def phase_ms(self):
+        out = {}
+        for i, nm in enumerate(PHASES):
+            ms, runs = ctypes.c_double(0), ctypes.c_uint64(0)
+            self._check(self.lib.cc_phase_ms(self.ctx, i, ctypes.byref(ms), ctypes.byref(runs)))
+            out[nm] = (ms.value, runs.value)
+        return out
+
+    def kernel_launches(self):
+        return int(self.lib.cc_kernel_launches(self.ctx))
+
+    def device_bytes(self):
+        return int(self.lib.cc_device_bytes(self.ctx))

@@ -1,0 +1,200 @@
+/*
+ * ccgpu.h - C ABI of libccgpu.so: the B200 (sm_100a) implementation of
+ * ConsensusCruncher's consensus hot path.
+ *
+ * The reference has no FFI: its consensus path is Python that keeps reads in
+ * dictionaries.  These entry points are what a binding
+ * for that path would call instead; every one names the reference code it
+ * replaces (paths relative to the reference repository).  Plain pointers and
+ * sizes only - no torch / numpy types.  INTEGRATION.md shows the ctypes
+ * binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - return 0 on success, a negative cc_status on failure; cc_last_error()
+ *     gives the message (pass NULL for a failed cc_create).
+ *   - the caller owns every host buffer; the library owns device memory until
+ *     cc_destroy().  One context per GPU; a context is not thread-safe.
+ *   - there is no CPU fallback: cc_create fails without an sm_100 device.
+ *   - all work is issued on the context's stream (cc_set_stream); calls that
+ *     return counts synchronise that stream.
+ *
+ * Input layout ("packed reads", produced on host by consensuscruncher_b200/pack.py,
+ * i.e. the filter / mate-pairing half of read_bam, consensus_helper.py:376-436):
+ *   reads are in pair-completion order, read 2k = first-seen mate of pair k,
+ *   read 2k+1 = second-seen mate.
+ *   fields   n x 32-byte cc_fields records
+ *   payload  n x stride bytes: lpad/2 bytes of BAM 4-bit bases (high nibble first),
+ *            then lpad quality bytes, zero padded; lpad % 32 == 0, stride % 64 == 0,
+ *            stride >= 3*lpad/2
+ *   dup_bc   n_bc x u32: barcode id of the complementary strand's barcode
+ *            (duplex_tag, consensus_helper.py:629-639), 0xffffffff if absent
+ */
+#ifndef CCGPU_H
+#define CCGPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cc_ctx cc_ctx;
+
+/* One read's key and record fields (unique_tag, consensus_helper.py:293-301, plus
+ * the fields create_aligned_segment takes modes of, :569-581). */
+typedef struct {
+    uint32_t bc;      /* barcode dictionary id                         */
+    uint32_t cig;     /* ordered cigar-pair dictionary id (cigar_order) */
+    int32_t tid, pos, mtid, mpos;
+    int32_t tlen;
+    uint16_t flag;    /* 0x10 orientation and 0x40/0x80 read number are key fields */
+    uint8_t mapq;
+    uint8_t rg;       /* read-group dictionary id, 0xff = no RG tag     */
+} cc_fields;
+
+typedef struct {
+    double cutoff;    /* SSCS_maker.py --cutoff: fraction of passing bases the winner needs */
+    int32_t scorrect; /* ConsensusCruncher.py --scorrect: run the rescue + second DCS pass  */
+} cc_params;
+
+enum cc_status {
+    CC_OK = 0,
+    CC_ERR_CUDA = -1,        /* CUDA runtime error (message has the call)               */
+    CC_ERR_ARG = -2,         /* bad geometry / NULL pointer / wrong call order          */
+    CC_ERR_NO_DEVICE = -3,   /* no sm_100 device                                        */
+    CC_ERR_BASE = -4,        /* N or IUPAC base with Q>=30 inside a family: the reference
+                                raises IndexError / ValueError (SSCS_maker.py:119-122)   */
+    CC_ERR_DOMAIN = -5,      /* a read pair does not found/join its two families together:
+                                outside the domain where a consensus pair name owns exactly
+                                two equal families (SSCS_maker.py:275) */
+    CC_ERR_TOO_LARGE = -6
+};
+
+/* Result arrays readable with cc_fetch (element types in brackets).  Per-family
+ * arrays are indexed by family id in order of family creation. */
+enum cc_array {
+    CC_READ_FAM = 0,     /* [u32 x n_reads]  family of each read                      */
+    CC_FAM_SIZE = 1,     /* [u32 x n_fam]    tag_dict[tag]                            */
+    CC_FAM_TMPL = 2,     /* [u32 x n_fam]    first member = template read             */
+    CC_FAM_MAPQ = 3,     /* [u8]  read_mode('mapping_quality')                        */
+    CC_FAM_FLAG = 4,     /* [u16] consensus_flag                                      */
+    CC_FAM_TLEN = 5,     /* [i32] read_mode('template_length')                        */
+    CC_FAM_RG = 6,       /* [u8]  read_mode("get_tag('RG')"), 0xff = none             */
+    CC_PARTNER = 7,      /* [i32] family with the duplex_tag key, -1 = none           */
+    CC_SSCS_ROW = 8,     /* [i32] row in CC_SSCS_ROWS or -1 (singleton)               */
+    CC_CORR_ROW = 9,     /* [i32] row in CC_CORR_ROWS or -1                           */
+    CC_DCS_ROW = 10,     /* [i32] row in CC_DCS_ROWS or -1 (set on the leading strand) */
+    CC_DCSSC_ROW = 11,   /* [i32] row in CC_DCSSC_ROWS or -1                          */
+    CC_SSCS_ROWS = 12,   /* [u8 x n_sscs x stride]  consensus_maker output            */
+    CC_CORR_ROWS = 13,   /* [u8 x n_corr x stride]  corrected singletons              */
+    CC_DCS_ROWS = 14,    /* [u8 x n_dcs x stride]   duplex_consensus (DCS_maker)      */
+    CC_DCSSC_ROWS = 15,  /* [u8 x n_dcssc x stride] DCS after singleton correction    */
+    CC_DCS_MAPQ = 16, CC_DCS_FLAG = 17, CC_DCS_TLEN = 18, CC_DCS_RG = 19,         /* per DCS row   */
+    CC_DCSSC_MAPQ = 20, CC_DCSSC_FLAG = 21, CC_DCSSC_TLEN = 22, CC_DCSSC_RG = 23, /* per DCS-SC row */
+    CC_STATS = 24,       /* [i64 x 16] see cc_stat                                    */
+    CC_FAM_HIST = 25     /* [u64 x CC_HIST_BINS] families per size (last bin: >= CC_HIST_BINS-1) */
+};
+
+#define CC_HIST_BINS 65536
+
+/* Indices into CC_STATS: the counters of the reference's stats.txt blocks
+ * (SSCS_maker.py:312-318, DCS_maker.py:264-270, singleton_correction.py:294-300). */
+enum cc_stat {
+    CC_ST_SSCS = 0, CC_ST_SINGLETONS = 1, CC_ST_DCS = 2, CC_ST_SSCS_SINGLETONS = 3,
+    CC_ST_SC_BY_SSCS = 4, CC_ST_SC_BY_SINGLETON = 5, CC_ST_UNCORRECTED = 6,
+    CC_ST_DCS_SC = 7, CC_ST_SSCS_SC_SINGLETONS = 8
+};
+
+enum cc_count { CC_N_READS = 0, CC_N_FAM = 1, CC_N_SSCS = 2, CC_N_CORR = 3, CC_N_DCS = 4, CC_N_DCSSC = 5 };
+
+/* Timed phases (cc_profile / cc_phase_ms). */
+enum cc_phase {
+    CC_PH_H2D = 0, CC_PH_HASH = 1, CC_PH_SORT = 2, CC_PH_SEGMENT = 3, CC_PH_JOIN = 4,
+    CC_PH_CLASSIFY = 5, CC_PH_VOTE = 6, CC_PH_RESCUE = 7, CC_PH_DCS = 8, CC_PH_DCS_SC = 9,
+    CC_PH_COUNT = 10
+};
+
+/* Context on `device` (must be an sm_100 GPU).  Replaces the per-stage dictionary
+ * set-up of SSCS_maker.py:211-214 / DCS_maker.py:165-178 / singleton_correction.py:145-155. */
+cc_ctx *cc_create(int device, const cc_params *params);
+void cc_destroy(cc_ctx *ctx);
+const char *cc_last_error(cc_ctx *ctx);
+int cc_set_params(cc_ctx *ctx, const cc_params *params);
+
+/* Issue all later work on `stream` (a cudaStream_t); NULL restores the context's own stream. */
+int cc_set_stream(cc_ctx *ctx, void *stream);
+
+/* Hand over one batch of packed reads from HOST memory (copied to the device on the
+ * context's stream).  Replaces the read_dict/pair_dict hand-over at the end of
+ * read_bam's pairing step (consensus_helper.py:418-441). */
+int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
+                  uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
+
+/* Same, for buffers that already live in DEVICE memory (not copied, must stay valid). */
+int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
+                         uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
+
+/* Family grouping: key hash, stable radix sort, exact family boundaries, families in
+ * creation order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
+ * construction (consensus_helper.py:438-475) and Counter(tag_dict.values())
+ * (SSCS_maker.py:361). */
+int cc_group(cc_ctx *ctx);
+
+/* Per-position vote for every family of size >= 2 and the family's mode fields.
+ * Replaces consensus_maker (SSCS_maker.py:75-157), read_mode / consensus_flag
+ * (consensus_helper.py:483-535) and the size-1 / size>=2 split (SSCS_maker.py:274-292). */
+int cc_sscs_vote(cc_ctx *ctx);
+
+/* Complementary-key join over the families and duplex consensus of paired SSCS.
+ * Replaces duplex_tag (consensus_helper.py:605-648), the probes and duplex_consensus of
+ * DCS_maker.py:226-259, :99-121 and the two-record modes of create_aligned_segment. */
+int cc_dcs_join(cc_ctx *ctx);
+
+/* Singleton rescue (by SSCS, else by singleton) and the DCS pass over
+ * SSCS + corrected singletons.  Replaces singleton_correction.py:249-285, :61-104 and the
+ * second DCS_maker run (ConsensusCruncher.py:247-270).  Needs cc_dcs_join first. */
+int cc_sc_rescue(cc_ctx *ctx);
+
+/* cc_group, cc_sscs_vote, cc_dcs_join and (if params.scorrect) cc_sc_rescue in one call
+ * with a single host synchronisation for the row counts. */
+int cc_run(cc_ctx *ctx);
+
+/* Whole path from host buffers to host results: cc_load_reads + cc_run; afterwards
+ * fetch what is needed with cc_fetch. */
+int cc_run_host(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
+                uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
+
+/* counts[CC_N_*] after the stage that produces them (synchronises). */
+int cc_counts(cc_ctx *ctx, uint64_t counts[8]);
+
+/* Copy result array `what` (enum cc_array) into host memory; `bytes` must be the exact size. */
+int cc_fetch(cc_ctx *ctx, int what, void *host_dst, uint64_t bytes);
+/* Size in bytes of result array `what` (0 if not produced yet). */
+uint64_t cc_array_bytes(cc_ctx *ctx, int what);
+/* Device address of result array `what` (NULL if not produced yet); valid until the next load. */
+const void *cc_device_ptr(cc_ctx *ctx, int what);
+
+/* Stand-alone primitives on host buffers, mirroring the reference's function signatures.
+ * consensus_maker(readList, cutoff) (SSCS_maker.py:75): rows = n x stride payload rows of
+ * one family, out = one row. */
+int cc_consensus_maker(cc_ctx *ctx, const uint8_t *rows, uint32_t n, uint32_t lpad, uint32_t stride,
+                       double cutoff, uint8_t *out_row);
+/* duplex_consensus(read1, read2): DCS_maker.py:99-121 (sc = 0) or
+ * singleton_correction.py:61-84 (sc = 1), for n_pairs independent pairs of rows. */
+int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2, uint64_t n_pairs,
+                        uint32_t lpad, uint32_t stride, int sc, uint8_t *out_rows);
+
+/* Phase timing with CUDA events on the context's stream. */
+int cc_profile(cc_ctx *ctx, int enable);
+/* Milliseconds spent in `phase` (enum cc_phase) since the last cc_profile(ctx, 1) and the
+ * number of times it ran; synchronises. */
+int cc_phase_ms(cc_ctx *ctx, int phase, double *ms, uint64_t *launches);
+/* Number of kernels this library has launched on this context. */
+uint64_t cc_kernel_launches(cc_ctx *ctx);
+/* Device bytes currently held by the context. */
+uint64_t cc_device_bytes(cc_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCGPU_H */

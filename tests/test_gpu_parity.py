@@ -1,0 +1,186 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle and the reference's goldens.
+Bit-exact: every result array must be identical, byte for byte."""
+import numpy as np
+import pytest
+
+from consensuscruncher_b200 import api, pack, synth
+from consensuscruncher_b200.engine import BaseError, GpuConsensus, GpuError
+from consensuscruncher_b200.records import Read
+from oracle import golden, oracle
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+def _both(engine, packed, cutoff=0.7, scorrect=True):
+    engine.set_params(cutoff=cutoff, scorrect=scorrect)
+    got = engine.consensus(packed)
+    exp = oracle.run(packed, cutoff, scorrect)
+    helpers.assert_same_result(got, exp)
+    return got
+
+
+@pytest.mark.parametrize("name", golden.names())
+def test_gpu_reproduces_reference_outputs(engine, name):
+    g, reads, packed = helpers.load_case(name)
+    engine.set_params(cutoff=g["params"]["cutoff"], scorrect=g["params"]["scorrect"])
+    res = engine.consensus(packed)
+    helpers.assert_matches_golden(g, reads, packed, res)
+    helpers.assert_same_result(res, oracle.run(packed, g["params"]["cutoff"], g["params"]["scorrect"]))
+
+
+@pytest.mark.parametrize("kw", [
+    dict(seed=21, n_molecules=3000, L=128),
+    dict(seed=22, n_molecules=3000, L=150, fam_mean=2.0, p_duplex=0.5),
+    dict(seed=23, n_molecules=2000, L=100, dist="wgs", p_duplex=0.3, n_tid=4),
+    dict(seed=24, n_molecules=300, L=64, dist="lognormal", fam_mean=12.0, err=0.02),
+    dict(seed=25, n_molecules=4000, L=36, umi_len=1, region=(0, 600), insert_sd=2.0),   # crowded keys
+    dict(seed=26, n_molecules=1500, L=250, mapq_mixed=True),
+    dict(seed=27, n_molecules=2, L=32, dist="const", fam_mean=700, p_duplex=1.0, err=0.05),   # > 255 reads / family
+    dict(seed=28, n_molecules=40, L=40, dist="const", fam_mean=40, p_duplex=1.0, mapq_mixed=True),  # mode over > 32 reads
+])
+def test_gpu_equals_oracle_on_synthetic(engine, kw):
+    packed = synth.generate(**kw).to_packed()
+    res = _both(engine, packed)
+    assert res.n_fam > 0
+
+
+@pytest.mark.parametrize("cutoff", [0.5, 0.6, 0.7, 0.8, 0.9, 1.0])
+@pytest.mark.parametrize("scorrect", [True, False])
+def test_cutoff_sweep(engine, cutoff, scorrect):
+    packed = synth.generate(seed=31, n_molecules=1500, L=64, err=0.05, fam_mean=3.0).to_packed()
+    _both(engine, packed, cutoff, scorrect)
+
+
+def test_medium_batch_and_properties(engine):
+    s = synth.generate(seed=41, n_molecules=40000, L=128)
+    packed = s.to_packed()
+    res = _both(engine, packed)
+    # size-independent properties
+    assert int(res.fam_size.sum()) == packed.n
+    assert (res.fam_tmpl[1:] > res.fam_tmpl[:-1]).all()                 # creation order
+    p = res.partner
+    has = p >= 0
+    assert (p[p[has]] == np.nonzero(has)[0]).all()                       # the join is an involution
+    assert res.stat("sscs") + res.stat("singletons") == res.n_fam
+    assert res.stat("dcs") * 2 + res.stat("sscs_singletons") == res.stat("sscs")
+
+
+def test_stagewise_calls_equal_one_shot(engine):
+    packed = synth.generate(seed=42, n_molecules=2500, L=96).to_packed()
+    engine.set_params(cutoff=0.7, scorrect=True)
+    one = engine.consensus(packed)
+    engine.load(packed)
+    engine.group()
+    assert engine.counts()["fam"] == one.n_fam
+    engine.sscs_vote()
+    engine.dcs_join()
+    engine.sc_rescue()
+    helpers.assert_same_result(engine.result(), one)
+
+
+def test_empty_and_tiny_batches(engine):
+    engine.set_params(cutoff=0.7, scorrect=True)
+    empty = pack.pack_reads([])
+    res = engine.consensus(empty)
+    assert res.n_fam == 0 and res.sscs_rows.shape == (0, 64)
+    one_pair = synth.generate(seed=3, n_molecules=1, dist="const", fam_mean=1, p_duplex=0.0, L=33).to_packed()
+    _both(engine, one_pair)
+    two = synth.generate(seed=4, n_molecules=1, dist="const", fam_mean=2, p_duplex=1.0, L=31).to_packed()
+    _both(engine, two)
+
+
+def test_repeated_runs_reuse_the_context(engine):
+    a = synth.generate(seed=51, n_molecules=1200, L=128).to_packed()
+    b = synth.generate(seed=52, n_molecules=300, L=64).to_packed()
+    for p in (a, b, a):
+        _both(engine, p)
+
+
+def test_hash_collisions_are_regrouped_exactly(engine):
+    # a tiny position range and 1-nt UMIs with many molecules force equal sort keys for
+    # different tags (the sort only uses as many hash bits as the batch needs)
+    packed = synth.generate(seed=61, n_molecules=30000, L=32, umi_len=2, region=(0, 1200),
+                            fam_mean=1.5, insert_sd=8.0).to_packed()
+    _both(engine, packed)
+
+
+def test_n_base_with_high_quality_is_an_error(engine):
+    s = synth.generate(seed=71, n_molecules=20, L=32, dist="const", fam_mean=3, p_n=0.0)
+    s.codes[5, 7] = 15
+    s.qual[5, 7] = 37
+    packed = s.to_packed()
+    engine.set_params(cutoff=0.7, scorrect=True)
+    with pytest.raises(BaseError):
+        engine.consensus(packed)
+    with pytest.raises(oracle.OracleError):
+        oracle.run(packed)
+
+
+def test_domain_fault_is_reported(engine):
+    # pair 99/147 and pair 65/129 with the same UMI and coordinates: R1 tags merge, R2 tags do not (F11)
+    def pair(q, f1, f2):
+        return [Read(q, f1, 0, 100, 60, "30M", 0, 200, 130, "A" * 30, [35] * 30, rg="1"),
+                Read(q, f2, 0, 200, 60, "30M", 0, 100, -130, "C" * 30, [35] * 30, rg="1")]
+    reads = pair("a|AC.GT", 99, 147) + pair("b|AC.GT", 65, 129)
+    reads = [reads[0], reads[2], reads[1], reads[3]]
+    packed = pack.pack_reads(reads)
+    engine.set_params(cutoff=0.7, scorrect=True)
+    with pytest.raises(pack.DomainError):
+        engine.consensus(packed)
+
+
+def test_geometry_is_validated(engine):
+    p = synth.generate(seed=81, n_molecules=5, L=32).to_packed()
+    bad = pack.PackedReads(p.fields, p.payload[:, :48].copy(), p.lpad, p.barcodes, p.dup_bc, p.cigar_pairs, p.rgs)
+    bad.stride = 48
+    with pytest.raises(GpuError):
+        engine.load(bad)
+
+
+# ---- function-level mirrors (the reference's docstring examples) ----------------------------
+def _reads(seqs, quals):
+    return [Read("r%d" % i, seq=s, qual=q) for i, (s, q) in enumerate(zip(seqs, quals))]
+
+
+def test_consensus_maker_known_answers(engine):
+    seqs = ["ACTGATACTT", "ACTGAAACCT", "ACTGATACCT", "ACTGATACTT"]           # SSCS_maker.py:23-29
+    assert api.consensus_maker(_reads(seqs, [[40] * 10] * 4), 0.7, engine) == ("ACTGATACNT", [60] * 10)
+    r = _reads(["AC", "CC", "AA", "CA"], [[40, 40], [40, 10], [40, 40], [40, 40]])
+    assert api.consensus_maker(r, 0.5, engine) == ("AA", [60, 60])
+    assert api.consensus_maker(r, 0.7, engine) == ("NN", [60, 60])
+    assert api.consensus_maker(_reads(["A", "A"], [[10], [20]]), 0.7, engine) == ("N", [0])
+    assert api.consensus_maker(_reads(["A", "C"], [[35], [33]]), 0.7, engine) == ("N", [35])
+    with pytest.raises(BaseError):
+        api.consensus_maker(_reads(["N", "A"], [[35], [35]]), 0.7, engine)
+
+
+def test_duplex_consensus_known_answers(engine):
+    a, b = _reads(["ACGTN", "ACGAN"], [[40, 20, 35, 40, 2], [25, 20, 30, 40, 2]])
+    assert api.duplex_consensus(a, b, engine) == ("ACGNN", [60, 40, 60, 0, 4])
+    assert api.sc_duplex_consensus(a, b, engine) == ("NNGNN", [0, 0, 60, 0, 0])
+
+
+def test_primitives_equal_oracle_on_random_rows(engine):
+    rng = np.random.default_rng(7)
+    for lpad in (32, 128, 160, 288):
+        stride = pack.row_geometry(lpad)[1]
+        n = 37
+        rows = np.zeros((n, stride), np.uint8)
+        codes = np.array([1, 2, 4, 8], np.uint8)[rng.integers(0, 4, (n, lpad))]
+        codes[:, : lpad // 2] = codes[0, : lpad // 2]                  # half the columns mostly agree
+        qual = rng.integers(0, 60, (n, lpad)).astype(np.uint8)
+        nn = rng.random((n, lpad)) < 0.02
+        codes[nn] = 15
+        qual[nn] = 2
+        for i in range(n):
+            pack.pack_row(codes[i], qual[i], lpad, rows[i])
+        for cutoff in (0.5, 0.7, 1.0):
+            for k in (2, 3, 37):
+                got = engine.consensus_maker_rows(rows[:k], lpad, cutoff)
+                assert (got == oracle.consensus_maker_rows(rows[:k], lpad, cutoff)).all()
+        for sc in (False, True):
+            got = engine.duplex_consensus_rows(rows[:18], rows[18:36], lpad, sc)
+            for i in range(18):
+                assert (got[i] == oracle.duplex_consensus_rows(rows[i], rows[18 + i], lpad, sc)).all()

@@ -1,0 +1,129 @@
+"""CPU: host-side mirror of the reference's helper functions, packing, synthetic data."""
+import numpy as np
+import pytest
+
+from consensuscruncher_b200 import keys, pack, synth
+from consensuscruncher_b200.records import Read, merge_records, sort_records
+
+
+def _r(flag, tid, pos, mtid, mpos, cigar="98M", tlen=100, qname="x|AAAA"):
+    return Read(qname, flag, tid, pos, 60, cigar, mtid, mpos, tlen, "A" * 5, [30] * 5)
+
+
+def test_which_read_docstring():                      # consensus_helper.py:62-67
+    assert keys.which_read(83) == "R1"
+    assert keys.which_read(131) == "R2"
+    assert keys.which_read(177) == "R2"
+    assert keys.which_read(1024 + 99) is None
+
+
+def test_which_strand_vectors():
+    for f in (147, 67, 131, 99):
+        assert keys.which_strand(_r(f, 1, 10, 1, 50)) == "pos"
+    for f in (83, 163, 115, 179):
+        assert keys.which_strand(_r(f, 1, 10, 1, 50)) == "neg"
+    for f in (81, 97, 65, 113):                       # R1: pos iff (tid,pos) < (mtid,mpos)
+        assert keys.which_strand(_r(f, 12, 10, 16, 5)) == "pos"
+        assert keys.which_strand(_r(f, 16, 10, 12, 5)) == "neg"
+        assert keys.which_strand(_r(f, 3, 10, 3, 50)) == "pos"
+        assert keys.which_strand(_r(f, 3, 50, 3, 10)) == "neg"
+    for f in (161, 145, 129, 177):                    # R2: the mirror image
+        assert keys.which_strand(_r(f, 12, 10, 16, 5)) == "neg"
+        assert keys.which_strand(_r(f, 16, 10, 12, 5)) == "pos"
+    assert keys.which_strand(_r(97, 3, 10, 3, 10)) == "neg"   # equal coordinates
+    assert keys.which_strand(_r(1024, 3, 10, 3, 10)) is None
+
+
+def test_key_string_narratives():                     # consensus_helper.py:177-183, :210-220, :276-284
+    r1 = _r(99, 24, 58847416, 24, 58847448, "137M10S", 148, "q|TTTG")
+    r2 = _r(147, 24, 58847448, 24, 58847416, "147M", -148, "q|TTTG")
+    for a, b in ((r1, r2), (r2, r1)):
+        cig = keys.cigar_order(a, b)
+        assert cig == "137M10S_147M"
+        assert keys.sscs_qname(a, b, "TTTG", cig) == "TTTG_24_58847416_24_58847448_137M10S_147M_pos_148"
+    assert keys.unique_tag(r1, "TTTG", "137M10S_147M") == "TTTG_24_58847416_24_58847448_137M10S_147M_fwd_R1"
+    assert keys.unique_tag(r2, "TTTG", "137M10S_147M") == "TTTG_24_58847448_24_58847416_137M10S_147M_rev_R2"
+    n1 = _r(83, 24, 58847448, 24, 58847416, "147M", -148)
+    n2 = _r(163, 24, 58847416, 24, 58847448, "137M10S", 148)
+    assert keys.cigar_order(n1, n2) == "137M10S_147M" == keys.cigar_order(n2, n1)
+
+
+def test_duplex_tag_actual_outputs():                 # SURVEY.md App. D 7 (docstring is stale)
+    assert keys.duplex_tag("GTCT_1_1507809_7_55224319_98M_98M_fwd_R1") == "CTGT_1_1507809_7_55224319_98M_98M_fwd_R2"
+    assert keys.duplex_tag("AC.GT_1_2_3_4_5M_5M_fwd_R1") == "GT.AC_1_2_3_4_5M_5M_fwd_R2"
+    assert keys.duplex_tag("ACG.T_1_2_3_4_5M_5M_rev_R2") == "T.ACG_1_2_3_4_5M_5M_rev_R1"
+    assert keys.duplex_barcode("ACGTA") == "GTAAC"      # odd, undotted: not an involution (Q11)
+
+
+def test_dcs_consensus_tag_docstring():               # DCS_maker.py:67-74
+    f = keys.dcs_consensus_tag
+    assert f("TTCA_7_55259315_7_55259454_98M_98M_neg:3", "CATT_7_55259315_7_55259454_98M_98M_pos:6") == \
+        "CATT_TTCA_7_55259315_7_55259454_98M_98M:6_3"
+    assert f("CTTC_23_74804535_23_74804611_98M_98M_pos:2", "TCCT_23_74804535_23_74804611_98M_98M_neg:3") == \
+        "CTTC_TCCT_23_74804535_23_74804611_98M_98M:2_3"
+    assert f("TTTC_7_140477735_7_140477790_98M_98M_neg:3", "TCTT_7_140477735_7_140477790_98M_98M_pos:2") == \
+        "TCTT_TTTC_7_140477735_7_140477790_98M_98M:2_3"
+
+
+def test_bed_separator_reads_cytoband(tmp_path):
+    p = tmp_path / "b.txt"
+    p.write_text("chr1\t0\t2300000\tp36.33\tgneg\nchr1\t2300000\t5400000\tp36.32\tgpos25\n")
+    assert keys.bed_separator(str(p)) == {"chr1_p36.33": (0, 2300000), "chr1_p36.32": (2300000, 5400000)}
+
+
+def test_row_roundtrip_and_geometry():
+    rng = np.random.default_rng(0)
+    for n in (1, 31, 32, 33, 100, 128, 150, 151):
+        lpad, stride = pack.row_geometry(n)
+        assert lpad % 32 == 0 and stride % 64 == 0 and stride >= lpad * 3 // 2 and lpad >= n
+        codes = rng.integers(0, 16, n).astype(np.uint8)
+        qual = rng.integers(0, 94, n).astype(np.uint8)
+        row = np.full(stride, 0xAB, np.uint8)
+        pack.pack_row(codes, qual, lpad, row)
+        c2, q2 = pack.unpack_row(row, lpad, n)
+        assert (c2 == codes).all() and (q2 == qual).all()
+        assert (row[lpad // 2 + n:] == 0).all()
+
+
+def test_filter_and_pairing_counters():
+    good1 = _r(99, 0, 10, 0, 60, qname="a|AA.CC")
+    good2 = _r(147, 0, 60, 0, 10, qname="a|AA.CC")
+    nospacer = _r(99, 0, 11, 0, 61, qname="nodelim")
+    unmapped = Read("u|AA.CC", 77, -1, -1, 0, "", -1, -1, 0, "A", [2])
+    mate_unmapped = _r(73, 0, 12, 0, 12, qname="m|AA.CC")
+    secondary = _r(99 | 256, 0, 13, 0, 63, qname="s|AA.CC")
+    lonely = _r(99, 0, 14, 0, 64, qname="l|AA.CC")
+    reads = [good1, nospacer, unmapped, mate_unmapped, secondary, lonely, good2]
+    p = pack.pack_reads(reads)
+    assert p.n == 2 and list(p.src) == [0, 6]
+    assert p.counters == dict(total=6, unmapped=1, unmapped_mate=1, multiple_mapping=1, bad_spacer=1)
+    assert p.bad == [1, 2, 3, 4] and p.leftover == [5]
+    assert p.barcodes == ["AA.CC"] and p.dup_bc[0] == pack.NO_ID
+    with pytest.raises(pack.DomainError):
+        pack.pack_reads([_r(99 | 1024, 0, 1, 0, 2, qname="d|AA.CC"), _r(147, 0, 2, 0, 1, qname="d|AA.CC")])
+
+
+def test_region_visit_order_matches_fetch_filter():
+    reads = [_r(99, 0, p, 0, p + 50, qname="q%d|AA.CC" % p) for p in (0, 5, 10, 15, 20)]
+    assert list(pack.visit_order(reads, [(0, 10, 20), (0, 0, 10), (1, 0, 100)])) == [2, 3, 0, 1]
+
+
+def test_synth_packed_equals_packed_records():
+    s = synth.generate(seed=5, n_molecules=120, L=40, fam_mean=2.5, region=(0, 3000))
+    direct = s.to_packed()
+    via = pack.pack_reads(s.to_reads())
+    assert direct.n == via.n == s.n
+    assert (direct.fields == via.fields).all()
+    assert (direct.payload == via.payload).all()
+    assert direct.barcodes == via.barcodes and (direct.dup_bc == via.dup_bc).all()
+    assert direct.cigar_pairs == via.cigar_pairs and (direct.src == via.src).all()
+
+
+def test_sort_and_merge_model():
+    a = _r(163, 0, 10, 0, 60, qname="a")
+    b = _r(99, 0, 10, 0, 60, qname="b")
+    c = _r(83, 0, 10, 0, 0, qname="c")
+    d = _r(99, 0, 5, 0, 60, qname="d")
+    u = Read("u", 77, -1, -1)
+    assert [r.qname for r in sort_records([u, a, c, b, d])] == ["d", "a", "b", "c", "u"]
+    assert [r.qname for r in merge_records([b], [a], [d])] == ["d", "b", "a"]
