@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""Benchmark of the consensus hot path (BASELINE.json metric: consensus reads/sec, SSCS+DCS+SC).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1]): synthetic duplex-UMI batch, 10 M read pairs
+(2e7 reads) per GPU, one region (chr1:0-2.3 Mb), L = 128, family size ~ zero-truncated
+Poisson(4), both strands present w.p. 0.8, cutoff 0.7, singleton correction on.
+A step is one pass of the whole path (group -> SSCS vote -> DCS join -> rescue -> DCS after
+rescue) over that batch.  With N > 1 every rank owns its own batch (genomic shards are
+independent), so scaling is weak; the only collective is the all-reduce of
+the stats counters and the family-size histogram.
+
+value   reads/s with the batch resident in HBM when the timed region starts
+e2e     reads/s through cc_run_host: pinned host buffers in, every result array read
+        back to pinned host memory, copies inside the timed region
+Inputs (4.5 GB per GPU) are far larger than L2 (126 MB), so no L2 flush is needed
+between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "consensus reads/sec (SSCS+DCS+SC)"
+UNIT = "reads/s"
+PAIRS_PER_GPU = 10_000_000
+L = 128
+CUTOFF = 0.7
+CPU_SAMPLE_PAIRS = 2_000_000
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="read pairs per GPU")
+    ap.add_argument("--cpu-pairs", type=int, default=CPU_SAMPLE_PAIRS, help="read pairs of the CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(pairs):
+    return {"workload": "synthetic duplex UMI batch, %d read pairs per GPU, single region chr1:0-2.3Mb, "
+                        "L=128, family size ~ zero-truncated Poisson(4), p(duplex)=0.8, cutoff 0.7, "
+                        "scorrect True (BASELINE.json configs[1])" % pairs,
+            "reads_per_gpu": 2 * pairs, "read_length": L, "cutoff": CUTOFF, "scorrect": True,
+            "l2_policy": "inputs (%.1f GB/GPU) exceed L2; no flush needed" % (2 * pairs * (32 + 192) / 1e9)}
+
+
+# ---- clocks -------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm = sorted(int(r[1]) for r in self.rows if len(r) > 2 and r[1].isdigit())
+        mx = [int(r[2]) for r in self.rows if len(r) > 2 and r[2].isdigit()]
+        reasons = set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            for nm, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- CPU legs (the only places bench.py may execute oracle/) ---------------------------------
+def cpu_sample(pairs, seed):
+    """A bounded sample of the same workload, generated on the host with the numpy generator."""
+    from consensuscruncher_b200 import synth
+    mean = 4.0 / (1 - 2.718281828 ** -4.0)
+    mol = max(1, int(pairs / (mean * 1.8)))
+    return synth.generate(seed=seed, n_molecules=mol, L=L).to_packed()
+
+
+def run_oracle_threads(shards, threads):
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(lambda p: oracle.run(p, CUTOFF, True), shards))
+    return time.perf_counter() - t0
+
+
+def reference_arm(args):
+    """--impl reference: the CPU implementation of the path on the host cores.
+
+    The reference is pure Python and cannot run on the GPU box (no pysam, /root/reference is
+    absent there), so this times the oracle port (oracle/cc_oracle.c), one independent shard
+    per host thread - the reference's own scale-out model is independent jobs
+    (docs/source/FAQ.rst:4-7)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle
+    oracle.build()
+    cores = os.cpu_count() or 1
+    per = max(1000, args.cpu_pairs // cores)
+    shards = [cpu_sample(per, 9000 + i) for i in range(cores)]
+    reads = sum(p.n for p in shards)
+    for _ in range(max(1, min(args.warmup, 1))):
+        run_oracle_threads(shards[:cores], cores)
+    t = 0.0
+    for _ in range(args.steps):
+        t += run_oracle_threads(shards, cores)
+    value = reads * args.steps / t
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic", "config": workload_config(args.pairs),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "%d reads of the same distribution per step, %d shards of %d pairs, "
+                                       "one oracle thread per shard" % (reads, cores, per)},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ---- our arm ---------------------------------------------------------------------------------
+def vote_algorithmic_bytes(res_sizes, n_sscs, stride_l):
+    """N*(1.5L+4) + F2*(1.5L+16), N = reads in families of size >= 2."""
+    n_big = int(res_sizes[res_sizes >= 2].sum())
+    return n_big * (1.5 * stride_l + 4) + n_sscs * (1.5 * stride_l + 16), n_big
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from consensuscruncher_b200 import build
+    from consensuscruncher_b200.engine import GpuConsensus
+    from consensuscruncher_b200.synth_device import generate_device
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    if args.warmup < 3:
+        args.warmup = 3
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    build.build_lib()
+
+    batch = generate_device(seed=1234 + rank, n_pairs=args.pairs, L=L, device=str(dev))
+    n_reads = batch.n
+    eng = GpuConsensus(local, cutoff=CUTOFF, scorrect=True)
+    stream = torch.cuda.current_stream(dev)
+    eng.set_stream(stream.cuda_stream)
+
+    def reduce_stats():
+        """The path's one collective: sum of the stage counters and the family-size histogram."""
+        if world == 1:
+            return
+        from consensuscruncher_b200.shard import device_tensor
+        for name, dt, count in (("stats", torch.int64, 16), ("fam_hist", torch.int64, 65536)):
+            t = device_tensor(eng.device_ptr(name), count, dt, local)
+            dist.all_reduce(t)
+
+    def step():
+        eng.load_device(batch.fields.data_ptr(), batch.payload.data_ptr(), n_reads, batch.lpad, batch.stride,
+                        batch.dup_bc.data_ptr(), batch.n_bc)
+        eng.run()
+        reduce_stats()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step()
+    counts = eng.counts()
+    sizes = eng.fetch("fam_size")
+    stats_once = eng.fetch("stats")
+
+    # ---- device-resident timing -------------------------------------------------------
+    clocks = ClockSampler(local)
+    eng.profile(True)
+    l0 = eng.kernel_launches()
+    barrier()
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = eng.kernel_launches() - l0
+    phases = eng.phase_ms()
+    eng.profile(False)
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = n_reads * world * args.steps / (ms_max * 1e-3)
+
+    # ---- end to end: pinned host in, results back to pinned host ------------------------
+    e2e = None
+    if not args.no_e2e:
+        h_fields = torch.empty(batch.fields.shape, dtype=batch.fields.dtype, pin_memory=True)
+        h_payload = torch.empty(batch.payload.shape, dtype=torch.uint8, pin_memory=True)
+        h_dup = torch.empty(batch.dup_bc.shape, dtype=batch.dup_bc.dtype, pin_memory=True)
+        h_fields.copy_(batch.fields); h_payload.copy_(batch.payload); h_dup.copy_(batch.dup_bc)
+        torch.cuda.synchronize(dev)
+        out_names = ("fam_size", "fam_tmpl", "fam_mapq", "fam_flag", "fam_tlen", "fam_rg", "partner",
+                     "sscs_row", "corr_row", "dcs_row", "dcssc_row", "sscs_rows", "corr_rows", "dcs_rows",
+                     "dcssc_rows", "dcs_mapq", "dcs_flag", "dcs_tlen", "dcs_rg", "dcssc_mapq", "dcssc_flag",
+                     "dcssc_tlen", "dcssc_rg", "stats", "fam_hist")
+        from consensuscruncher_b200.engine import ARRAYS
+        h_out = {}
+
+        def e2e_step():
+            eng._check(eng.lib.cc_run_host(eng.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
+                                           batch.stride, h_dup.data_ptr(), batch.n_bc))
+            reduce_stats()
+            total = 0
+            for nm in out_names:
+                what = ARRAYS[nm][0]
+                nbytes = eng.lib.cc_array_bytes(eng.ctx, what)
+                if nbytes == 0:
+                    continue
+                buf = h_out.get(nm)
+                if buf is None or buf.numel() < nbytes:
+                    buf = h_out[nm] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8, pin_memory=True)
+                eng._check(eng.lib.cc_fetch(eng.ctx, what, buf.data_ptr(), nbytes))
+                total += nbytes
+            return total
+
+        # free the device-resident copy of the inputs' consumer state is not needed; warm up once
+        d2h = e2e_step()
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        e0.record(stream)
+        e2e_steps = max(2, min(args.steps, 3))
+        for _ in range(e2e_steps):
+            d2h = e2e_step()
+        e1.record(stream)
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        ems = max(e0.elapsed_time(e1), wall)          # host-side fetches serialise with the stream
+        t = torch.tensor([ems], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": n_reads * world * e2e_steps / (float(t.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(batch.nbytes()), "d2h_bytes_per_step": int(d2h),
+               "steps": e2e_steps, "ms_per_step": float(t.item()) / e2e_steps}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (SSCS vote) ----------------------------------------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    vote_ms, vote_runs = phases["vote"]
+    alg_bytes, n_big = vote_algorithmic_bytes(sizes, counts["sscs"], L)
+    achieved = alg_bytes / (vote_ms / max(1, vote_runs) * 1e-3) / 1e9 if vote_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "vote_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "kernel": "vote_kernel (SSCS vote + family mode fields)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "ms_per_launch": vote_ms / max(1, vote_runs),
+                "phase_ms_per_step": {k: v[0] / max(1, v[1]) for k, v in phases.items() if v[1]}}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import oracle
+        oracle.build()
+        sample = cpu_sample(args.cpu_pairs, 777)
+        t0 = time.perf_counter()
+        oracle.run(sample, CUTOFF, True)
+        dt = time.perf_counter() - t0
+        cpu = {"value": sample.n / dt, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "%d reads (%d pairs) of the same distribution, oracle/cc_oracle.c single thread, %.1f s"
+                         % (sample.n, sample.n // 2, dt),
+               "host_cores_available": os.cpu_count()}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": workload_config(args.pairs), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu,
+            "counts": {k: int(v) for k, v in counts.items()},
+            "stats": {"sscs": int(stats_once[0]), "singletons": int(stats_once[1]), "dcs": int(stats_once[2]),
+                      "dcs_sc": int(stats_once[7])}}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
