@@ -815,3 +815,93 @@ uint64_t cc_kernel_launches(cc_ctx *ctx) { return ctx ? ctx->launches : 0; }
 uint64_t cc_device_bytes(cc_ctx *ctx) { return ctx ? ctx->dev_bytes : 0; }
 
 }  // extern "C"
+
+// ======================= allocation-free consensus_maker ==========================================
+// Scratch of cc_consensus_maker_static: a fixed array in the library's device image, shared by
+// every call on a device (see include/ccgpu.h).  Device code may name it directly; host code
+// must not - there the symbol is only a stand-in, so the address is looked up once per device.
+namespace {
+
+struct StaticVoteScratch {
+    uint4 fields[2 * CC_STATIC_MAX_READS];   // zeroed field records: every member has the same mode fields
+    uint32_t perm[CC_STATIC_MAX_READS];      // member list 0..n-1
+    uint32_t header[16];                     // [0] segment start, [1] family size, [2] list entry, [3] error flag
+    uint32_t meta_out[16];                   // mode fields the kernel writes and nobody reads
+};
+
+static __device__ __align__(256) unsigned char g_static_vote_scratch[sizeof(StaticVoteScratch)];
+
+constexpr int kMaxDevices = 64;
+void *g_static_vote_ptr[kMaxDevices];        // device address of the array, per device
+bool g_static_vote_ready[kMaxDevices];
+
+// Everything a call relies on is rewritten here, because the array still holds the previous
+// call's contents: member list, header, the error flag and the field records of this family.
+__global__ void static_vote_prepare_kernel(uint32_t n)
+{
+    StaticVoteScratch *s = reinterpret_cast<StaticVoteScratch *>(g_static_vote_scratch);
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        s->perm[i] = i;
+        s->fields[2 * i] = make_uint4(0, 0, 0, 0);
+        s->fields[2 * i + 1] = make_uint4(0, 0, 0, 0);
+    }
+    if (i < 16) {
+        s->header[i] = (i == 1) ? n : 0u;
+        s->meta_out[i] = 0;
+    }
+}
+
+int static_fail(int code, const std::string &msg)
+{
+    g_create_error = msg;
+    return code;
+}
+
+}  // namespace
+
+extern "C" int cc_consensus_maker_static(const uint8_t *d_rows, uint32_t n, uint32_t lpad, uint32_t stride,
+                                         double cutoff, uint8_t *d_out_row, void *stream)
+{
+    if (!d_rows || !d_out_row || n == 0) return static_fail(CC_ERR_ARG, "cc_consensus_maker_static: NULL pointer or empty family");
+    if (n > CC_STATIC_MAX_READS)
+        return static_fail(CC_ERR_TOO_LARGE, "cc_consensus_maker_static: family of " + std::to_string(n) +
+                                                 " reads exceeds CC_STATIC_MAX_READS (" +
+                                                 std::to_string(CC_STATIC_MAX_READS) + "); use cc_consensus_maker");
+    if (lpad == 0 || lpad % 32 || stride % 64 || stride < lpad / 2 + lpad)
+        return static_fail(CC_ERR_ARG, "cc_consensus_maker_static: need lpad % 32 == 0, stride % 64 == 0, stride >= 3*lpad/2");
+    if (((uintptr_t)d_rows & 3) || ((uintptr_t)d_out_row & 3))
+        return static_fail(CC_ERR_ARG, "cc_consensus_maker_static: device rows must be 4-byte aligned");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+        return static_fail(CC_ERR_CUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+    if (!g_static_vote_ready[dev]) {
+        // once per device, with that device current: the symbol's device address
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_vote_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return static_fail(CC_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(e));
+        g_static_vote_ptr[dev] = p;
+        g_static_vote_ready[dev] = true;
+    }
+    StaticVoteScratch *s = reinterpret_cast<StaticVoteScratch *>(g_static_vote_ptr[dev]);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    static_vote_prepare_kernel<<<(n + 255) / 256 > 0 ? (n + 255) / 256 : 1, 256, 0, st>>>(n);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(CC_ERR_CUDA, std::string("prepare launch: ") + cudaGetErrorString(e));
+    vote_kernel<<<1, 32, 0, st>>>(s->fields, d_rows, stride, lpad, s->perm, &s->header[0], &s->header[1], &s->header[2], 1u,
+                                  cutoff, d_out_row, reinterpret_cast<uint8_t *>(&s->meta_out[0]),
+                                  reinterpret_cast<uint16_t *>(&s->meta_out[4]), reinterpret_cast<int32_t *>(&s->meta_out[8]),
+                                  reinterpret_cast<uint8_t *>(&s->meta_out[12]), &s->header[3]);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(CC_ERR_CUDA, std::string("vote launch: ") + cudaGetErrorString(e));
+    uint32_t err = 0;
+    e = cudaMemcpyAsync(&err, &s->header[3], sizeof(err), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return static_fail(CC_ERR_CUDA, std::string("cc_consensus_maker_static: ") + cudaGetErrorString(e));
+    if (err)
+        return static_fail(CC_ERR_BASE, "a base other than A/C/G/T carries Q>=30 "
+                                        "(the reference raises IndexError/ValueError, SSCS_maker.py:119-122)");
+    return CC_OK;
+}

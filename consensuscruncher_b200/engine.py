@@ -35,7 +35,8 @@ CC_ERR_BASE, CC_ERR_DOMAIN = -4, -5
 SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_stream", "cc_load_reads",
            "cc_load_reads_device", "cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run",
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
-           "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes")
+           "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
+           "cc_consensus_maker_static")
 
 
 class CcParams(ctypes.Structure):
@@ -85,6 +86,7 @@ def load_library(path=LIB_PATH):
     L.cc_device_ptr.argtypes = [vp, i32]
     L.cc_consensus_maker.argtypes = [vp, vp, u32, u32, u32, ctypes.c_double, vp]
     L.cc_duplex_consensus.argtypes = [vp, vp, vp, u64, u32, u32, i32, vp]
+    L.cc_consensus_maker_static.argtypes = [vp, u32, u32, u32, ctypes.c_double, vp, vp]
     L.cc_profile.argtypes = [vp, i32]
     L.cc_phase_ms.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(u64)]
     L.cc_kernel_launches.restype = u64

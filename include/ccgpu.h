@@ -184,6 +184,33 @@ int cc_consensus_maker(cc_ctx *ctx, const uint8_t *rows, uint32_t n, uint32_t lp
 int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2, uint64_t n_pairs,
                         uint32_t lpad, uint32_t stride, int sc, uint8_t *out_rows);
 
+/* Largest family cc_consensus_maker_static accepts (its scratch is sized for this). */
+#define CC_STATIC_MAX_READS 4096
+
+/* This entry point has no counterpart in the reference.  It is cc_consensus_maker for
+ * callers that are not allowed to allocate device memory while they run - code inside a
+ * framework whose memory pool owns the whole GPU, a real-time or plugin host that forbids
+ * driver allocations after start-up, a caller between other libraries' graph captures where
+ * a cudaMalloc would synchronise the device.  Such callers already hold device buffers, so
+ * both the family's rows and the result row are DEVICE pointers here, and the working
+ * memory the vote kernel needs (member list, segment header, zeroed field records, error
+ * flag; about 145 KB) lives in a fixed array inside the library's device image instead of
+ * coming from cudaMalloc.  Every GPU that loads libccgpu.so carries that array until exit.
+ *
+ *   d_rows     n x stride bytes, payload rows of ONE family, in device memory
+ *   d_out_row  stride bytes in device memory: the consensus row
+ *   stream     cudaStream_t of the calling thread's current device (NULL = default stream)
+ *
+ * Runs on the current device.  Calls no cudaMalloc / cudaFree and no allocating library.
+ * The first call on each device looks up the array's device address; make that first call
+ * outside any stream capture.  The call waits for its own work before returning.
+ * All calls on a device share the one array: two calls whose GPU work overlaps (different
+ * streams or threads) race; issue them one after the other.
+ * Returns CC_ERR_TOO_LARGE if n > CC_STATIC_MAX_READS, CC_ERR_BASE as cc_consensus_maker
+ * does; the message is read with cc_last_error(NULL). */
+int cc_consensus_maker_static(const uint8_t *d_rows, uint32_t n, uint32_t lpad, uint32_t stride,
+                              double cutoff, uint8_t *d_out_row, void *stream);
+
 /* Phase timing with CUDA events on the context's stream. */
 int cc_profile(cc_ctx *ctx, int enable);
 /* Milliseconds spent in `phase` (enum cc_phase) since the last cc_profile(ctx, 1) and the
