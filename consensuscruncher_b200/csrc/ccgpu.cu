@@ -11,6 +11,7 @@
 #include "kernels.cuh"
 #include "radix.cuh"
 #include "scan.cuh"
+#include "vote.cuh"
 
 using namespace ccgpu;
 
@@ -31,7 +32,7 @@ struct PhaseTimer {
 };
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
-           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_COUNT = 32 };
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NBIG = 30, CT_COUNT = 32 };
 
 }  // namespace
 
@@ -58,6 +59,9 @@ struct cc_ctx {
     DevBuf sscs_list, dcs_list, corr_list, dcssc_list, sscs_row, dcs_row, corr_row, dcssc_row;
     DevBuf sscs_rows, corr_rows, dcs_rows, dcssc_rows;
     DevBuf dcs_mapq, dcs_flag, dcs_tlen, dcs_rg, dcssc_mapq, dcssc_flag, dcssc_tlen, dcssc_rg;
+    DevBuf vstart, vsize, big_list, thr_table;
+    uint8_t thr_host[128];
+    bool thr_valid = false;
     DevBuf tmp_a, tmp_b, tmp_c;   // stand-alone primitives
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
@@ -175,7 +179,7 @@ int scan_prepare(cc_ctx *ctx, uint64_t n, uint32_t **ticket)
     uint64_t tiles = scan_tiles(n);
     TRY(ensure(ctx, ctx->scan_status, (tiles + 1) * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (tiles + 1) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_COUNT - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    if (ctx->next_ticket >= CT_NBIG - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
     *ticket = ptr<uint32_t>(ctx->counters) + CT_TICKET0 + ctx->next_ticket++;
     return CC_OK;
 }
@@ -379,18 +383,71 @@ int do_lists(cc_ctx *ctx, bool with_join)
     return CC_OK;
 }
 
+// thr[p] = smallest count c with (double)c / (double)p >= cutoff: the comparison of
+// SSCS_maker.py:143-144, evaluated once per possible (count, passing) pair with IEEE division
+int upload_thresholds(cc_ctx *ctx)
+{
+    TRY(ensure(ctx, ctx->thr_table, 128));
+    const double cutoff = ctx->params.cutoff;
+    ctx->thr_host[0] = 255;
+    for (int p = 1; p < 128; p++) {
+        int t = 255;
+        for (int c = 0; c <= p; c++)
+            if ((double)c / (double)p >= cutoff) { t = c; break; }
+        ctx->thr_host[p] = (uint8_t)t;
+    }
+    CK(cudaMemcpyAsync(ctx->thr_table.p, ctx->thr_host, 128, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->thr_valid = true;
+    return CC_OK;
+}
+
+template <int G>
+int launch_vote_small(cc_ctx *ctx, uint32_t rows)
+{
+    const uint32_t warps = (rows + (32 / G) - 1) / (32 / G);
+    auto kernel = vote_small_kernel<G>;
+    LAUNCH(kernel, blocks_for((uint64_t)warps * 32, 256), 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
+           ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list), rows,
+           ptr<uint8_t>(ctx->thr_table), (1.0 >= ctx->params.cutoff) ? 1 : 0, ptr<uint8_t>(ctx->sscs_rows),
+           ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
+           ptr<uint8_t>(ctx->fam_rg), ptr<uint32_t>(ctx->counters) + CT_ERR);
+    return CC_OK;
+}
+
 int do_vote(cc_ctx *ctx)
 {
     const uint32_t rows = ctx->n_sscs;
     TRY(ensure(ctx, ctx->sscs_rows, (size_t)rows * ctx->stride));
+    TRY(ensure(ctx, ctx->vstart, (size_t)rows * 4)); TRY(ensure(ctx, ctx->vsize, (size_t)rows * 4));
+    TRY(ensure(ctx, ctx->big_list, (size_t)rows * 4));
+    if (!ctx->thr_valid) TRY(upload_thresholds(ctx));
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
+    if (rows) {
+        TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
+        LAUNCH(vote_segments_kernel, blocks_for(rows, 256), 256, ptr<uint32_t>(ctx->sscs_list),
+               ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), rows, ptr<uint32_t>(ctx->vstart),
+               ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG);
+        TRY(phase_end(ctx, CC_PH_VOTE_AUX));
+    }
     TRY(phase_begin(ctx, CC_PH_VOTE));
-    if (rows)
-        LAUNCH(vote_kernel, blocks_for((uint64_t)rows * 32, 256), 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad,
-               ctx->perm, ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->sscs_list),
-               rows, ctx->params.cutoff, ptr<uint8_t>(ctx->sscs_rows), ptr<uint8_t>(ctx->fam_mapq),
-               ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
-               ptr<uint32_t>(ctx->counters) + CT_ERR);
+    if (rows) {
+        const uint32_t lanes = (ctx->lpad + 15) / 16;
+        if (lanes <= 2) TRY(launch_vote_small<2>(ctx, rows));
+        else if (lanes <= 4) TRY(launch_vote_small<4>(ctx, rows));
+        else if (lanes <= 8) TRY(launch_vote_small<8>(ctx, rows));
+        else if (lanes <= 16) TRY(launch_vote_small<16>(ctx, rows));
+        else TRY(launch_vote_small<32>(ctx, rows));
+    }
     TRY(phase_end(ctx, CC_PH_VOTE));
+    if (rows) {
+        TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
+        LAUNCH(vote_big_kernel, 296, 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
+               ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list),
+               ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG, ctx->params.cutoff, ptr<uint8_t>(ctx->sscs_rows),
+               ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
+               ptr<uint8_t>(ctx->fam_rg), ctr + CT_ERR);
+        TRY(phase_end(ctx, CC_PH_VOTE_AUX));
+    }
     ctx->voted = true;
     return CC_OK;
 }
@@ -507,7 +564,8 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->f_dcssc, &ctx->sscs_list, &ctx->dcs_list, &ctx->corr_list, &ctx->dcssc_list, &ctx->sscs_row,
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcssc_rows, &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->dcssc_mapq,
-                     &ctx->dcssc_flag, &ctx->dcssc_tlen, &ctx->dcssc_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c};
+                     &ctx->dcssc_flag, &ctx->dcssc_tlen, &ctx->dcssc_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
+                     &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->thr_table};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
@@ -521,6 +579,7 @@ int cc_set_params(cc_ctx *ctx, const cc_params *params)
 {
     if (!ctx || !params) return CC_ERR_ARG;
     ctx->params = *params;
+    ctx->thr_valid = false;
     return CC_OK;
 }
 

@@ -166,24 +166,32 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
                     int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
                     unsigned long long *__restrict__ hist, uint32_t hist_bins)
 {
+    __shared__ uint32_t small_hist[256];           // sizes < 256 are counted per block first
+    small_hist[threadIdx.x] = 0;
+    __syncthreads();
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n_fam) return;
-    uint32_t f = c2hs[c];
-    uint32_t s = hs_start[f];
-    uint32_t e = (f + 1 < n_fam) ? hs_start[f + 1] : n_reads;
-    uint32_t size = e - s;
-    fam_start[c] = s;
-    fam_size[c] = size;
-    is_sscs[c] = size >= 2;
-    // a singleton keeps its own fields (SSCS_maker.py:278-282); larger families are
-    // overwritten by the vote kernel's mode fields
-    Rec r = load_rec(fields, tmpl[c]);
-    fam_tlen[c] = (int32_t)r.b.z;
-    fam_flag[c] = (uint16_t)(r.b.w & 0xFFFF);
-    fam_mapq[c] = (uint8_t)((r.b.w >> 16) & 0xFF);
-    fam_rg[c] = (uint8_t)(r.b.w >> 24);
-    uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
-    atomicAdd(&hist[bin], 1ull);
+    if (c < n_fam) {
+        uint32_t f = c2hs[c];
+        uint32_t s = hs_start[f];
+        uint32_t e = (f + 1 < n_fam) ? hs_start[f + 1] : n_reads;
+        uint32_t size = e - s;
+        fam_start[c] = s;
+        fam_size[c] = size;
+        is_sscs[c] = size >= 2;
+        // a singleton keeps its own fields (SSCS_maker.py:278-282); larger families are
+        // overwritten by the vote kernel's mode fields
+        Rec r = load_rec(fields, tmpl[c]);
+        fam_tlen[c] = (int32_t)r.b.z;
+        fam_flag[c] = (uint16_t)(r.b.w & 0xFFFF);
+        fam_mapq[c] = (uint8_t)((r.b.w >> 16) & 0xFF);
+        fam_rg[c] = (uint8_t)(r.b.w >> 24);
+        uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
+        if (bin < 256) atomicAdd(&small_hist[bin], 1u);
+        else atomicAdd(&hist[bin], 1ull);
+    }
+    __syncthreads();
+    uint32_t v = small_hist[threadIdx.x];
+    if (v) atomicAdd(&hist[threadIdx.x], (unsigned long long)v);
 }
 
 // Pair symmetry check (SSCS_maker.py:275 emits a pair name only with exactly two tags):
@@ -370,21 +378,18 @@ __device__ uint32_t warp_mode(Get get, uint32_t n, bool is_flag, int lane)
     return best;
 }
 
-__global__ void __launch_bounds__(256)
-vote_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
-            uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ fam_start,
-            const uint32_t *__restrict__ fam_size, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
-            double cutoff, uint8_t *__restrict__ out_rows, uint8_t *__restrict__ fam_mapq,
-            uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-            uint32_t *__restrict__ err_flag)
+// One warp votes one family of any size: members perm[start .. start+n), consensus row -> out,
+// mode fields -> fam_*[c].  Used for families too large for vote_small_kernel (vote.cuh) and by
+// the single-family entry points.
+__device__ __forceinline__ void
+vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
+                 uint32_t lpad, const uint32_t *__restrict__ perm, uint32_t start, uint32_t n, double cutoff,
+                 uint8_t *__restrict__ out, uint32_t c, uint8_t *__restrict__ fam_mapq,
+                 uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
+                 uint32_t *__restrict__ err_flag)
 {
     const int lane = threadIdx.x & 31;
-    const uint32_t row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row >= n_rows) return;
-    const uint32_t c = sscs_list[row];
-    const uint32_t start = fam_start[c], n = fam_size[c];
     const uint32_t half = lpad >> 1;
-    uint8_t *out = out_rows + (uint64_t)row * stride;
     uint32_t err = 0;
 
     for (uint32_t chunk = 0; chunk * 128 < lpad; chunk++) {
@@ -471,6 +476,21 @@ vote_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payloa
         fam_tlen[c] = (int32_t)tlen; fam_flag[c] = (uint16_t)flag;
         fam_mapq[c] = (uint8_t)mapq; fam_rg[c] = (uint8_t)rg;
     }
+}
+
+__global__ void __launch_bounds__(256)
+vote_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
+            uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ fam_start,
+            const uint32_t *__restrict__ fam_size, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
+            double cutoff, uint8_t *__restrict__ out_rows, uint8_t *__restrict__ fam_mapq,
+            uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
+            uint32_t *__restrict__ err_flag)
+{
+    const uint32_t row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= n_rows) return;
+    const uint32_t c = sscs_list[row];
+    vote_family_warp(fields, payload, stride, lpad, perm, fam_start[c], fam_size[c], cutoff,
+                     out_rows + (uint64_t)row * stride, c, fam_mapq, fam_flag, fam_tlen, fam_rg, err_flag);
 }
 
 // ---- K7: duplex_consensus on two rows --------------------------------------------------------------

@@ -28,7 +28,7 @@ ARRAYS = {
     "dcssc_flag": (21, np.uint16), "dcssc_tlen": (22, np.int32), "dcssc_rg": (23, np.uint8),
     "stats": (24, np.int64), "fam_hist": (25, np.uint64),
 }
-PHASES = ("h2d", "hash", "sort", "segment", "join", "classify", "vote", "rescue", "dcs", "dcs_sc")
+PHASES = ("h2d", "hash", "sort", "segment", "join", "classify", "vote", "rescue", "dcs", "dcs_sc", "vote_aux")
 CC_ERR_BASE, CC_ERR_DOMAIN = -4, -5
 
 # every symbol include/ccgpu.h declares

@@ -111,7 +111,8 @@ enum cc_count { CC_N_READS = 0, CC_N_FAM = 1, CC_N_SSCS = 2, CC_N_CORR = 3, CC_N
 enum cc_phase {
     CC_PH_H2D = 0, CC_PH_HASH = 1, CC_PH_SORT = 2, CC_PH_SEGMENT = 3, CC_PH_JOIN = 4,
     CC_PH_CLASSIFY = 5, CC_PH_VOTE = 6, CC_PH_RESCUE = 7, CC_PH_DCS = 8, CC_PH_DCS_SC = 9,
-    CC_PH_COUNT = 10
+    CC_PH_VOTE_AUX = 10,   /* segment list + the warp-per-family kernel for families > 127 reads */
+    CC_PH_COUNT = 11
 };
 
 /* Context on `device` (must be an sm_100 GPU).  Replaces the per-stage dictionary
