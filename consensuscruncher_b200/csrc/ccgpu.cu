@@ -309,7 +309,8 @@ int do_group(cc_ctx *ctx)
     LAUNCH(mark_first_kernel, blocks_for(nf, 256), 256, hs_start, ctx->perm, nf, mark);
     TRY(compact_marks(ctx, mark, n, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->c2hs)));
     LAUNCH(family_build_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->c2hs), hs_start,
-           ptr<uint32_t>(ctx->tmpl), nf, (uint32_t)n, ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size),
+           ptr<uint32_t>(ctx->tmpl), ptr<uint8_t>(ctx->head), nf, (uint32_t)n, ptr<uint32_t>(ctx->fam_start),
+           ptr<uint32_t>(ctx->fam_size),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
            ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
            (uint32_t)CC_HIST_BINS);
@@ -404,13 +405,19 @@ int upload_thresholds(cc_ctx *ctx)
 template <int G>
 int launch_vote_small(cc_ctx *ctx, uint32_t rows)
 {
-    const uint32_t warps = (rows + (32 / G) - 1) / (32 / G);
     auto kernel = vote_small_kernel<G>;
-    LAUNCH(kernel, blocks_for((uint64_t)warps * 32, 256), 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
+    static bool configured = false;      // per template instance
+    if (!configured) {
+        CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VOTE_RING_BYTES));
+        configured = true;
+    }
+    kernel<<<blocks_for(rows, VOTE_CHUNK), 256, VOTE_RING_BYTES, ctx->stream>>>( ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
            ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list), rows,
            ptr<uint8_t>(ctx->thr_table), (1.0 >= ctx->params.cutoff) ? 1 : 0, ptr<uint8_t>(ctx->sscs_rows),
            ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
            ptr<uint8_t>(ctx->fam_rg), ptr<uint32_t>(ctx->counters) + CT_ERR);
+    ctx->launches++;
+    CK(cudaGetLastError());
     return CC_OK;
 }
 
@@ -425,12 +432,14 @@ int do_vote(cc_ctx *ctx)
     if (rows) {
         TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
         LAUNCH(vote_segments_kernel, blocks_for(rows, 256), 256, ptr<uint32_t>(ctx->sscs_list),
-               ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), rows, ptr<uint32_t>(ctx->vstart),
-               ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG);
+               ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), ptr<uint8_t>(ctx->is_sscs), rows,
+               ptr<uint32_t>(ctx->vstart),
+               ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG,
+               ctx->lpad <= 512 ? VOTE_SMALL_MAX : 0u);   // a lane group covers at most 512 positions
         TRY(phase_end(ctx, CC_PH_VOTE_AUX));
     }
     TRY(phase_begin(ctx, CC_PH_VOTE));
-    if (rows) {
+    if (rows && ctx->lpad <= 512) {
         const uint32_t lanes = (ctx->lpad + 15) / 16;
         if (lanes <= 2) TRY(launch_vote_small<2>(ctx, rows));
         else if (lanes <= 4) TRY(launch_vote_small<4>(ctx, rows));

@@ -66,7 +66,7 @@ hash_kernel(const uint4 *__restrict__ fields, uint64_t n, uint32_t key_mask, uin
 }
 
 // ---- K3: exact family boundaries in sorted order -------------------------------------
-// head[j] = 1 iff read perm[j] starts a family.  Reads with equal sort key but
+// head[j] bit 0 set iff read perm[j] starts a family.  Reads with equal sort key but
 // different tags ("mixed runs", hash collisions) are queued for fix_mixed_runs.
 __global__ void __launch_bounds__(256)
 boundary_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ keys,
@@ -79,7 +79,8 @@ boundary_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ k
     Rec cur = load_rec(fields, perm[j]);
     Rec prv = load_rec(fields, perm[j - 1]);
     bool differs = !same_tag(cur, prv);
-    head[j] = differs ? 1 : 0;
+    // bit 0: starts a family; bit 1: same family, but tlen / flag / mapq / RG differ from the previous member
+    head[j] = differs ? 1 : ((cur.b.z != prv.b.z || cur.b.w != prv.b.w) ? 2 : 0);
     uint32_t k = keys[j];
     if (differs && k == keys[j - 1]) {
         // only the first tag change inside a run reports the run
@@ -136,7 +137,7 @@ fix_mixed_runs_kernel(const uint4 *__restrict__ fields, const uint32_t *__restri
             if (take) {
                 uint64_t dst = out + __popc(b & lt);
                 tmp[dst] = v;
-                head[dst] = dst == head_at ? 1 : 0;
+                head[dst] = dst == head_at ? 1 : 2;      // 2: let the vote kernel take the exact mode path
                 perm[x] = v | 0x80000000u;
             }
             out += __popc(b);
@@ -160,8 +161,8 @@ mark_first_kernel(const uint32_t *__restrict__ hs_start, const uint32_t *__restr
 __global__ void __launch_bounds__(256)
 family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ c2hs,
                     const uint32_t *__restrict__ hs_start, const uint32_t *__restrict__ tmpl,
-                    uint32_t n_fam, uint32_t n_reads, uint32_t *__restrict__ fam_start,
-                    uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
+                    const uint8_t *__restrict__ head, uint32_t n_fam, uint32_t n_reads,
+                    uint32_t *__restrict__ fam_start, uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
                     uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag,
                     int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
                     unsigned long long *__restrict__ hist, uint32_t hist_bins)
@@ -175,9 +176,11 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
         uint32_t s = hs_start[f];
         uint32_t e = (f + 1 < n_fam) ? hs_start[f + 1] : n_reads;
         uint32_t size = e - s;
+        uint32_t mixed = 0;                           // do the members' mode fields differ anywhere?
+        for (uint32_t j = s + 1; j < e; j++) mixed |= head[j];
         fam_start[c] = s;
         fam_size[c] = size;
-        is_sscs[c] = size >= 2;
+        is_sscs[c] = size >= 2 ? ((mixed & 2) ? 3 : 1) : 0;   // bit 0: has a consensus row, bit 1: mode fields differ
         // a singleton keeps its own fields (SSCS_maker.py:278-282); larger families are
         // overwritten by the vote kernel's mode fields
         Rec r = load_rec(fields, tmpl[c]);

@@ -2,7 +2,7 @@
 //
 // Three flavours share one kernel body:
 //   exclusive scan of u32 values                       -> out[i]
-//   compaction of the indices whose flag is non-zero   -> list[rank] = i
+//   compaction of the indices whose flag has bit 0 set -> list[rank] = i
 //   compaction that also carries the flag value        -> list[rank] = i, carry[rank] = flag - 1
 // Tiles take their number from an atomic ticket so that a tile only ever waits
 // on tiles that have already started.
@@ -57,7 +57,7 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
         v[i] = (base + i < n) ? in[base + i] : (InT)0;
-        w[i] = (MODE == SCAN_MODE_EXCL) ? (uint32_t)v[i] : (v[i] != 0 ? 1u : 0u);
+        w[i] = (MODE == SCAN_MODE_EXCL) ? (uint32_t)v[i] : (MODE == SCAN_MODE_COMPACT ? ((uint32_t)v[i] & 1u) : (v[i] != 0 ? 1u : 0u));
         sum += w[i];
     }
     // block-wide exclusive prefix of the per-thread sums

@@ -21,15 +21,40 @@
 
 namespace ccgpu {
 
-constexpr uint32_t VOTE_SMALL_MAX = 127;     // byte-lane compares below need counts < 128
-constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows a lane keeps in flight
+constexpr uint32_t VOTE_SMALL_MAX = 31;      // T counts are kept times 8 in a byte lane
+constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows per staged batch
+constexpr int VOTE_DEPTH = 3;                // ring slots per lane: VOTE_DEPTH - 1 batches in flight
+constexpr int VOTE_RING_BYTES = VOTE_DEPTH * VOTE_ROWS_PER_BATCH * 256 * 24;   // dynamic shared memory per block
+
+__device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem)
+                 : "memory");
+}
+
+__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem)
+                 : "memory");
+}
+
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ uint32_t pass7_of(uint32_t q)
 {
     return (((q & 0x7F7F7F7Fu) + 0x62626262u) | q) & 0x80808080u;    // bit 7 of each byte: q >= 30
 }
 
-__device__ __forceinline__ uint32_t bytes_of(uint32_t bit7) { return (bit7 >> 7) * 0xFFu; }
+// 0xFF in every byte whose bit 7 is set (PRMT sign-replicate mode), 0x00 elsewhere
+__device__ __forceinline__ uint32_t bytes_of(uint32_t bit7)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %1, 0xBA98;" : "=r"(r) : "r"(bit7));   // selector bit 3 = replicate the byte's sign
+    return r;
+}
 
 // bit 7 of each byte: a >= b, for bytes < 128
 __device__ __forceinline__ uint32_t ge7(uint32_t a, uint32_t b) { return ((a | 0x80808080u) - b) & 0x80808080u; }
@@ -39,20 +64,24 @@ __device__ __forceinline__ uint32_t nz7(uint32_t x) { return (x + 0x7F7F7F7Fu) &
 
 __device__ __forceinline__ uint32_t sel(uint32_t a, uint32_t b, uint32_t mask) { return (a & mask) | (b & ~mask); }
 
+// x + y as an integer multiply-add: with `one` a run-time 1 the compiler cannot fold it back
+// into an add, so it issues on the FMA pipe instead of the (saturated) ALU pipe.
+__device__ __forceinline__ uint32_t fadd(uint32_t x, uint32_t y, uint32_t one) { return x * one + y; }
+
 struct Quad {            // accumulators of 4 positions (one byte lane each)
-    uint32_t cA, cC, cG, cT, pc;
+    uint32_t cA, cC, cG, cT, pc;     // cC, cG, cT hold 2x, 4x, 8x the count (no shifts in the row loop)
 };
 
-__device__ __forceinline__ void quad_add(Quad &a, uint32_t nib, uint32_t q, uint32_t &err)
+__device__ __forceinline__ void quad_add(Quad &a, uint32_t nib, uint32_t q, uint32_t &err, uint32_t one)
 {
-    uint32_t p1 = pass7_of(q) >> 7;
-    uint32_t b = nib & (p1 * 0xFFu);
-    err |= ((b | 0x80808080u) - 0x01010101u) & b;        // more than one bit set in a passing base
-    a.cA += b & 0x01010101u;
-    a.cC += (b >> 1) & 0x01010101u;
-    a.cG += (b >> 2) & 0x01010101u;
-    a.cT += (b >> 3) & 0x01010101u;
-    a.pc += p1;
+    uint32_t m = bytes_of(fadd(q & 0x7F7F7F7Fu, 0x62626262u, one) | q);    // 0xFF where q >= 30
+    uint32_t b = nib & m;
+    err |= fadd(b | 0x80808080u, 0xFEFEFEFFu, one) & b;  // (b | 0x80..) - 0x01..: more than one bit set in a passing base
+    a.cA = fadd(b & 0x01010101u, a.cA, one);
+    a.cC = fadd(b & 0x02020202u, a.cC, one);
+    a.cG = fadd(b & 0x04040404u, a.cG, one);
+    a.cT = fadd(b & 0x08080808u, a.cT, one);
+    a.pc = fadd(m & 0x01010101u, a.pc, one);
 }
 
 struct QuadOut {
@@ -67,14 +96,16 @@ struct QuadOut {
 __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr, bool unanimous_ok, uint32_t &err)
 {
     QuadOut o;
-    uint32_t m1 = bytes_of(ge7(a.cA, a.cC));              // ties keep the earlier base: A,C,G,T order
-    uint32_t m2 = bytes_of(ge7(a.cG, a.cT));
-    uint32_t bAC = sel(a.cA, a.cC, m1), wAC = sel(0x01010101u, 0x02020202u, m1);
-    uint32_t bGT = sel(a.cG, a.cT, m2), wGT = sel(0x04040404u, 0x08080808u, m2);
+    const uint32_t cA = a.cA, cC = (a.cC >> 1) & 0x7F7F7F7Fu, cG = (a.cG >> 2) & 0x3F3F3F3Fu,
+                   cT = (a.cT >> 3) & 0x1F1F1F1Fu;
+    uint32_t m1 = bytes_of(ge7(cA, cC));                  // ties keep the earlier base: A,C,G,T order
+    uint32_t m2 = bytes_of(ge7(cG, cT));
+    uint32_t bAC = sel(cA, cC, m1), wAC = sel(0x01010101u, 0x02020202u, m1);
+    uint32_t bGT = sel(cG, cT, m2), wGT = sel(0x04040404u, 0x08080808u, m2);
     uint32_t m3 = bytes_of(ge7(bAC, bGT));
     uint32_t best = sel(bAC, bGT, m3);
     o.win = sel(wAC, wGT, m3);
-    uint32_t sum = a.cA + a.cC + a.cG + a.cT;
+    uint32_t sum = cA + cC + cG + cT;
     err |= sum ^ a.pc;                                     // a passing base that is none of A,C,G,T
     uint32_t pass = a.pc;
     uint32_t split = nz7(best ^ pass);                     // not unanimous
@@ -156,9 +187,36 @@ __device__ uint32_t group_mode(Get get, uint32_t n, bool is_flag, int gl, int G,
     return best;
 }
 
-// vstart / vsize: segment of `perm` of every SSCS row (filled by vote_segments_kernel)
+// Two-read family, 4 positions, in closed form (the commonest family after singletons):
+//   both pass and agree -> base, 60;  one passes -> its base and min(60, q);
+//   both pass, differ   -> tie: the earlier base in A,C,G,T order with its own quality,
+//                          emitted iff 1/2 >= cutoff;  none passes -> N, 0.
+__device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t nib2, uint32_t q2, bool tie_ok,
+                                          bool unanimous_ok, uint32_t &code, uint32_t &qual, uint32_t &err)
+{
+    uint32_t m1 = bytes_of(pass7_of(q1)), m2 = bytes_of(pass7_of(q2));
+    uint32_t b1 = nib1 & m1, b2 = nib2 & m2;
+    err |= (((b1 | 0x80808080u) - 0x01010101u) & b1) | (((b2 | 0x80808080u) - 0x01010101u) & b2);
+    err |= (m1 & ~bytes_of(nz7(b1))) | (m2 & ~bytes_of(nz7(b2)));      // passing base that is none of A,C,G,T
+    uint32_t both = m1 & m2, differ = bytes_of(nz7(b1 ^ b2));
+    uint32_t agree = both & ~differ, clash = both & differ;
+    uint32_t first = bytes_of(ge7(b2, b1));                              // read 1 holds the earlier base
+    uint32_t win = sel(b1, b2, (m1 & ~m2) | (clash & first) | agree);
+    uint32_t wq = sel(q1, q2, (m1 & ~m2) | (clash & first));
+    uint32_t ok = (agree | (m1 ^ m2)) & (unanimous_ok ? 0xFFFFFFFFu : 0u);
+    if (tie_ok) ok |= clash;
+    code = sel(win, 0x0F0F0F0Fu, ok);
+    qual = sel(0x3C3C3C3Cu, cap60(wq), agree) & (m1 | m2);
+}
+
+constexpr int VOTE_CHUNK = 1024;    // SSCS rows a block sorts by family size and then votes
+
+// vstart / vsize: segment of `perm` of every SSCS row (filled by vote_segments_kernel).
+// A block takes VOTE_CHUNK consecutive rows, orders them by family size in shared memory and
+// hands them to its lane groups in that order, so the groups of a warp walk families of
+// (nearly) equal size and their row loops stay in step.
 template <int G>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
                   uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
                   const uint32_t *__restrict__ vsize, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
@@ -167,124 +225,241 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
                   uint8_t *__restrict__ fam_rg, uint32_t *__restrict__ err_flag)
 {
     __shared__ uint8_t thr[128];
-    if (threadIdx.x < 128) thr[threadIdx.x] = thr_table[threadIdx.x];
-    __syncthreads();
+    __shared__ uint32_t s_start[VOTE_CHUNK];
+    __shared__ uint8_t s_size[VOTE_CHUNK];
+    __shared__ uint16_t s_order[VOTE_CHUNK];
+    __shared__ uint32_t s_bin[128];
     constexpr int GROUPS = 32 / G;
-    const int lane = threadIdx.x & 31, gl = lane % G, grp = lane / G;
+    constexpr int BLOCK_GROUPS = 8 * GROUPS;
+    const int tid = threadIdx.x, lane = tid & 31, gl = lane % G, grp = lane / G;
     const uint32_t gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << (grp * G);
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t row = warp * GROUPS + grp;
     const uint32_t half = lpad >> 1;
-    uint32_t start = 0, n = 0;
-    if (row < n_rows) {
-        start = __ldg(&vstart[row]);
-        n = __ldg(&vsize[row]);
-        if (n > VOTE_SMALL_MAX) n = 0;                     // large families go to vote_big_kernel
-    }
-    uint8_t *out = out_rows + (uint64_t)row * stride;
-    uint32_t err = 0;
+    const uint32_t row0 = blockIdx.x * VOTE_CHUNK;
+    const uint32_t rows_here = min((uint32_t)VOTE_CHUNK, n_rows - row0);
 
-    for (uint32_t base = 0; base < lpad; base += G * 16) { // one pass unless lpad > 16 * G
-        const uint32_t pos0 = base + gl * 16;
-        const bool active = n != 0 && pos0 < lpad;
-        Quad acc[4];
+    if (tid < 128) { thr[tid] = thr_table[tid]; s_bin[tid] = 0; }
+    __syncthreads();
+    for (uint32_t i = tid; i < rows_here; i += 256) {
+        const uint32_t v = __ldg(&vsize[row0 + i]);
+        uint32_t n = v & 0x7FFFFFFFu;
+        if (n > VOTE_SMALL_MAX) n = 0;                     // large families go to vote_big_kernel
+        s_start[i] = __ldg(&vstart[row0 + i]);
+        s_size[i] = (uint8_t)(n | ((v >> 31) << 7));       // bit 7: mode fields differ inside the family
+        atomicAdd(&s_bin[n], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {                                        // exclusive prefix over the 128 size bins
+        uint32_t v[4], sum = 0;
 #pragma unroll
-        for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0};
-        if (active) {
-            for (uint32_t j0 = 0; j0 < n; j0 += VOTE_ROWS_PER_BATCH) {
-                uint32_t idx[VOTE_ROWS_PER_BATCH];
-                LaneRow r[VOTE_ROWS_PER_BATCH];
+        for (int k = 0; k < 4; k++) { v[k] = s_bin[tid * 4 + k]; sum += v[k]; }
+        uint32_t incl = sum;
 #pragma unroll
-                for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++)
-                    idx[k] = __ldg(&perm[start + min(j0 + k, n - 1)]);
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (tid >= d) incl += t;
+        }
+        uint32_t run = incl - sum;
 #pragma unroll
-                for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) r[k] = load_lane_row(payload, stride, half, idx[k], pos0);
+        for (int k = 0; k < 4; k++) { s_bin[tid * 4 + k] = run; run += v[k]; }
+    }
+    __syncthreads();
+    const uint32_t skipped = s_bin[1];                     // bin 0 = rows this kernel does not vote
+    __syncthreads();
+    for (uint32_t i = tid; i < rows_here; i += 256) s_order[atomicAdd(&s_bin[s_size[i] & 0x7F], 1u)] = (uint16_t)i;
+    __syncthreads();
+
+    const bool tie_ok = 1 >= thr[2];
+    uint32_t err = 0;
+    const uint32_t one = (uint32_t)unanimous_ok | 1u;      // 1, but only known at run time (see fadd)
+    const uint32_t todo = rows_here - skipped;
+    const uint32_t my_slot = (tid >> 5) * GROUPS + grp;
+    const uint32_t pos0 = gl * 16;
+    const bool lane_on = pos0 < lpad;                      // this lane owns 16 positions of the rows
+
+    // Lane-private staging ring in shared memory, filled with cp.async: every lane copies its
+    // own 8 sequence bytes + 16 quality bytes of up to VOTE_ROWS_PER_BATCH rows per batch and
+    // keeps VOTE_DEPTH - 1 batches in flight while it votes the oldest one.  Bytes in flight
+    // no longer occupy registers, which is what bounds the achieved HBM bandwidth here.
+    extern __shared__ __align__(16) uint8_t ring[];
+    uint4 *ring_q = reinterpret_cast<uint4 *>(ring);                                        // [depth][row][thread]
+    uint2 *ring_s = reinterpret_cast<uint2 *>(ring + VOTE_DEPTH * VOTE_ROWS_PER_BATCH * 256 * 16);
+    auto slot_q = [&](uint32_t batch, int k) { return &ring_q[((batch % VOTE_DEPTH) * VOTE_ROWS_PER_BATCH + k) * 256 + tid]; };
+    auto slot_s = [&](uint32_t batch, int k) { return &ring_s[((batch % VOTE_DEPTH) * VOTE_ROWS_PER_BATCH + k) * 256 + tid]; };
+
+    // producer cursor: the batch that will be issued next
+    uint32_t p_t = my_slot, p_start = 0, p_n = 0, p_j0 = 0, p_batch = 0;
+    uint32_t p_idx[VOTE_ROWS_PER_BATCH];
+    auto p_load_family = [&]() {
+        p_start = 0; p_n = 0; p_j0 = 0;
+        if (p_t < todo) {
+            uint32_t i = s_order[skipped + p_t];
+            p_start = s_start[i];
+            p_n = s_size[i] & 0x7F;
+        }
+    };
+    auto p_load_idx = [&]() {                              // member indices of the producer's batch
 #pragma unroll
-                for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
-                    if (j0 + k < n) {
-                        uint32_t nib[4], q[4];
-                        split_row(r[k], nib, q);
+        for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++)
+            p_idx[k] = (p_n != 0) ? __ldg(&perm[p_start + min(p_j0 + k, p_n - 1)]) : 0u;
+    };
+    auto p_issue = [&]() {                                 // copy the producer's batch, then move on
+        if (p_n != 0 && lane_on) {
 #pragma unroll
-                        for (int g = 0; g < 4; g++) quad_add(acc[g], nib[g], q[g], err);
+            for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
+                if (p_j0 + k < p_n) {
+                    const uint8_t *src = payload + (uint64_t)p_idx[k] * stride;
+                    cp_async_8(slot_s(p_batch, k), src + (pos0 >> 1));
+                    cp_async_16(slot_q(p_batch, k), src + half + pos0);
+                }
+            }
+        }
+        cp_async_commit();
+        p_batch++;
+        p_j0 += VOTE_ROWS_PER_BATCH;
+        if (p_j0 >= p_n) { p_t += BLOCK_GROUPS; p_load_family(); }
+        p_load_idx();
+    };
+    p_load_family();
+    p_load_idx();
+#pragma unroll 1
+    for (int d = 0; d < VOTE_DEPTH - 1; d++) p_issue();
+
+    uint32_t c_batch = 0;                                  // consumer: oldest batch still in the ring
+    for (uint32_t t0 = 0; t0 < todo; t0 += BLOCK_GROUPS) {
+        const uint32_t t = t0 + my_slot;
+        uint32_t start = 0, n = 0, row = 0;
+        bool mixed = false;
+        if (t < todo) {
+            uint32_t i = s_order[skipped + t];
+            start = s_start[i];
+            n = s_size[i] & 0x7F;
+            mixed = (s_size[i] & 0x80) != 0;
+            row = row0 + i;
+        }
+        uint8_t *out = out_rows + (uint64_t)row * stride;
+
+        if (n != 0) {
+            uint32_t code[4] = {0, 0, 0, 0}, qual[4] = {0, 0, 0, 0};
+            if (n == 2) {
+                p_issue();
+                cp_async_wait<VOTE_DEPTH - 1>();
+                if (lane_on) {
+                    LaneRow r1{*slot_s(c_batch, 0), *slot_q(c_batch, 0)}, r2{*slot_s(c_batch, 1), *slot_q(c_batch, 1)};
+                    uint32_t n1[4], q1[4], n2[4], q2[4];
+                    split_row(r1, n1, q1);
+                    split_row(r2, n2, q2);
+#pragma unroll
+                    for (int g = 0; g < 4; g++) quad_pair(n1[g], q1[g], n2[g], q2[g], tie_ok, unanimous_ok != 0, code[g], qual[g], err);
+                }
+                c_batch++;
+            } else {
+                Quad acc[4];
+#pragma unroll
+                for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0};
+                const uint32_t first_batch = c_batch;
+                for (uint32_t j0 = 0; j0 < n; j0 += VOTE_ROWS_PER_BATCH) {
+                    p_issue();
+                    cp_async_wait<VOTE_DEPTH - 1>();
+                    if (lane_on) {
+#pragma unroll
+                        for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
+                            if (j0 + k < n) {
+                                LaneRow r{*slot_s(c_batch, k), *slot_q(c_batch, k)};
+                                uint32_t nib[4], q[4];
+                                split_row(r, nib, q);
+#pragma unroll
+                                for (int g = 0; g < 4; g++) quad_add(acc[g], nib[g], q[g], err, one);
+                            }
+                        }
                     }
+                    c_batch++;
+                }
+                if (lane_on) {
+                    QuadOut o[4];
+                    uint32_t any_single = 0;
+#pragma unroll
+                    for (int g = 0; g < 4; g++) {
+                        o[g] = quad_finish(acc[g], thr, unanimous_ok != 0, err);
+                        any_single |= o[g].single;
+                    }
+#ifdef VOTE_EXP_NO_PICK
+                    any_single = 0;
+#endif
+                    if (any_single) {                      // lane-local: re-walk the rows for the lone supporters
+                        uint32_t pick[4] = {0, 0, 0, 0};
+                        // the ring still holds the last VOTE_DEPTH - 1 batches that were consumed... but
+                        // the producer has already reused older slots, so only short families re-read it
+                        const bool in_ring = n <= VOTE_ROWS_PER_BATCH;
+                        for (uint32_t j = 0; j < n; j++) {
+                            LaneRow rr;
+                            if (in_ring) { rr.s = *slot_s(first_batch, j); rr.q = *slot_q(first_batch, j); }
+                            else rr = load_lane_row(payload, stride, half, __ldg(&perm[start + j]), pos0);
+                            uint32_t nib[4], q[4];
+                            split_row(rr, nib, q);
+#pragma unroll
+                            for (int g = 0; g < 4; g++) pick[g] |= quad_pick(nib[g], q[g], o[g].win, o[g].single);
+                        }
+#pragma unroll
+                        for (int g = 0; g < 4; g++) o[g].qual |= cap60(pick[g]) & o[g].single;
+                    }
+#pragma unroll
+                    for (int g = 0; g < 4; g++) { code[g] = o[g].code; qual[g] = o[g].qual; }
                 }
             }
-            QuadOut o[4];
-            uint32_t any_single = 0;
-#pragma unroll
-            for (int g = 0; g < 4; g++) {
-                o[g] = quad_finish(acc[g], thr, unanimous_ok != 0, err);
-                any_single |= o[g].single;
+            if (lane_on) {
+                uint2 so;
+                uint4 qo;
+                so.x = (code[0] << 4) | code[1];
+                so.y = (code[2] << 4) | code[3];
+                qo.x = __byte_perm(qual[0], qual[1], 0x5140); qo.y = __byte_perm(qual[0], qual[1], 0x7362);
+                qo.z = __byte_perm(qual[2], qual[3], 0x5140); qo.w = __byte_perm(qual[2], qual[3], 0x7362);
+                *reinterpret_cast<uint2 *>(out + (pos0 >> 1)) = so;
+                *reinterpret_cast<uint4 *>(out + half + pos0) = qo;
             }
-            if (any_single) {                              // lane-local: re-walk the rows for the lone supporters
-                uint32_t pick[4] = {0, 0, 0, 0};
-                for (uint32_t j = 0; j < n; j++) {
-                    LaneRow r = load_lane_row(payload, stride, half, __ldg(&perm[start + j]), pos0);
-                    uint32_t nib[4], q[4];
-                    split_row(r, nib, q);
-#pragma unroll
-                    for (int g = 0; g < 4; g++) pick[g] |= quad_pick(nib[g], q[g], o[g].win, o[g].single);
-                }
-#pragma unroll
-                for (int g = 0; g < 4; g++) o[g].qual |= cap60(pick[g]) & o[g].single;
+            for (uint32_t x = half + lpad + gl * 4; x < stride; x += G * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
+        }
+
+        // ---- mode fields (create_aligned_segment, consensus_helper.py:569-583) -------------------
+        // A family whose members all carry the same tlen / flag / mapq / RG keeps the template's
+        // values, which family_build_kernel already stored.  Only families flagged by the
+        // boundary pass need the real modes; that branch is uniform per lane group.
+        if (n != 0 && mixed) {
+            auto meta_of = [&](uint32_t j) { return __ldg(&fields[2 * (uint64_t)__ldg(&perm[start + j]) + 1]); };
+            bool has_rg = true;
+            for (uint32_t j0 = 0; j0 < n; j0 += G) {
+                uint32_t j = j0 + gl;
+                uint32_t rg_ok = __ballot_sync(gmask, j >= n || (meta_of(j).w >> 24) != 0xFFu) & gmask;
+                has_rg = has_rg && rg_ok == gmask;
             }
-            uint2 so;
-            uint4 qo;
-            so.x = (o[0].code << 4) | o[1].code;
-            so.y = (o[2].code << 4) | o[3].code;
-            qo.x = __byte_perm(o[0].qual, o[1].qual, 0x5140); qo.y = __byte_perm(o[0].qual, o[1].qual, 0x7362);
-            qo.z = __byte_perm(o[2].qual, o[3].qual, 0x5140); qo.w = __byte_perm(o[2].qual, o[3].qual, 0x7362);
-            *reinterpret_cast<uint2 *>(out + (pos0 >> 1)) = so;
-            *reinterpret_cast<uint4 *>(out + half + pos0) = qo;
+            uint32_t tlen = group_mode([&](uint32_t j) { return meta_of(j).z; }, n, false, gl, G, gmask);
+            uint32_t flag = group_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, n, true, gl, G, gmask);
+            uint32_t mapq = group_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, n, false, gl, G, gmask);
+            uint32_t rg = has_rg ? group_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, n, false, gl, G, gmask) : 0xFFu;
+            if (gl == 0) {
+                const uint32_t c = __ldg(&sscs_list[row]);
+                fam_tlen[c] = (int32_t)tlen; fam_flag[c] = (uint16_t)flag;
+                fam_mapq[c] = (uint8_t)mapq; fam_rg[c] = (uint8_t)rg;
+            }
         }
     }
-    if (n != 0)
-        for (uint32_t x = half + lpad + gl * 4; x < stride; x += G * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
+    cp_async_wait<0>();
     if (err) atomicOr(err_flag, 1u);
-
-    // ---- mode fields (create_aligned_segment, consensus_helper.py:569-583) -------------------
-    // every lane of the warp takes part in the ballots; groups without a family carry n = 0
-    auto meta_of = [&](uint32_t j) { return __ldg(&fields[2 * (uint64_t)__ldg(&perm[start + j]) + 1]); };
-    uint32_t nmax = n;
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, d));
-    if (nmax == 0) return;
-    uint4 m0 = n ? meta_of(0) : make_uint4(0, 0, 0, 0);
-    bool uniform = true, has_rg = true;
-    for (uint32_t j0 = 0; j0 < nmax; j0 += G) {
-        uint32_t j = j0 + gl;
-        uint4 m = j < n ? meta_of(j) : m0;
-        uint32_t same = __ballot_sync(0xffffffffu, m.z == m0.z && m.w == m0.w);
-        uint32_t rg_ok = __ballot_sync(0xffffffffu, j >= n || (m.w >> 24) != 0xFFu);
-        uniform = uniform && (same & gmask) == gmask;
-        has_rg = has_rg && (rg_ok & gmask) == gmask;
-    }
-    uint32_t tlen = m0.z, flag = m0.w & 0xFFFF, mapq = (m0.w >> 16) & 0xFF, rg = m0.w >> 24;
-    if (n != 0 && !uniform) {                              // group-uniform branch; ballots use the group mask
-        tlen = group_mode([&](uint32_t j) { return meta_of(j).z; }, n, false, gl, G, gmask);
-        flag = group_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, n, true, gl, G, gmask);
-        mapq = group_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, n, false, gl, G, gmask);
-        rg = has_rg ? group_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, n, false, gl, G, gmask) : 0xFFu;
-    }
-    if (n != 0 && gl == 0) {
-        const uint32_t c = __ldg(&sscs_list[row]);
-        fam_tlen[c] = (int32_t)tlen; fam_flag[c] = (uint16_t)flag;
-        fam_mapq[c] = (uint8_t)mapq; fam_rg[c] = (uint8_t)rg;
-    }
 }
 
 // segment of every SSCS row, and the list of rows too large for vote_small_kernel
 __global__ void __launch_bounds__(256)
 vote_segments_kernel(const uint32_t *__restrict__ sscs_list, const uint32_t *__restrict__ fam_start,
-                     const uint32_t *__restrict__ fam_size, uint32_t n_rows, uint32_t *__restrict__ vstart,
-                     uint32_t *__restrict__ vsize, uint32_t *__restrict__ big_list, uint32_t *__restrict__ n_big)
+                     const uint32_t *__restrict__ fam_size, const uint8_t *__restrict__ fam_class, uint32_t n_rows,
+                     uint32_t *__restrict__ vstart,
+                     uint32_t *__restrict__ vsize, uint32_t *__restrict__ big_list, uint32_t *__restrict__ n_big,
+                     uint32_t small_max)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
     uint32_t c = sscs_list[r];
     uint32_t n = fam_size[c];
     vstart[r] = fam_start[c];
-    vsize[r] = n;
+    vsize[r] = n | ((uint32_t)(fam_class[c] & 2) << 30);   // bit 31: members' mode fields differ
     if (n > VOTE_SMALL_MAX) big_list[atomicAdd(n_big, 1u)] = r;
 }
 
@@ -301,7 +476,7 @@ vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ pa
     const uint32_t total = *n_big;
     for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
         const uint32_t row = big_list[i];
-        vote_family_warp(fields, payload, stride, lpad, perm, vstart[row], vsize[row], cutoff,
+        vote_family_warp(fields, payload, stride, lpad, perm, vstart[row], vsize[row] & 0x7FFFFFFFu, cutoff,
                          out_rows + (uint64_t)row * stride, sscs_list[row], fam_mapq, fam_flag, fam_tlen, fam_rg,
                          err_flag);
     }

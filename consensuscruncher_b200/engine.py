@@ -54,11 +54,13 @@ class BaseError(GpuError):
 _lib = None
 
 
-def load_library(path=LIB_PATH):
-    """dlopen libccgpu.so and declare its prototypes.  Raises if it was not built."""
+def load_library(path=None):
+    """dlopen libccgpu.so and declare its prototypes.  Raises if it was not built.
+    CCGPU_LIB names an alternative build of the same library (kernel experiments)."""
     global _lib
     if _lib is not None:
         return _lib
+    path = path or os.environ.get("CCGPU_LIB") or LIB_PATH
     if not os.path.exists(path):
         raise GpuError("libccgpu.so is missing (%s): build it with `python -m consensuscruncher_b200.build`; "
                        "this package has no CPU fallback" % path)
