@@ -53,12 +53,13 @@ struct cc_ctx {
     uint32_t *perm = nullptr, *sorted_keys = nullptr, *spare_keys = nullptr, *spare_vals = nullptr;
     uint32_t next_ticket = 0;
     // families
-    uint32_t n_fam = 0, n_sscs = 0, n_dcs = 0, n_corr = 0, n_dcssc = 0;
+    uint32_t n_fam = 0, n_sscs = 0, n_dcs = 0, n_corr = 0, n_dcssc = 0;   // n_dcssc = n_dcs + n_extra when rescuing
+    uint32_t n_extra = 0;                                                 // second-pass pairs with a row of their own
     DevBuf tmpl, c2hs, fam_start, fam_size, is_sscs, fam_mapq, fam_flag, fam_tlen, fam_rg;
     DevBuf partner, table, f_dcs, f_corr, f_dcssc;
     DevBuf sscs_list, dcs_list, corr_list, dcssc_list, sscs_row, dcs_row, corr_row, dcssc_row;
-    DevBuf sscs_rows, corr_rows, dcs_rows, dcssc_rows;
-    DevBuf dcs_mapq, dcs_flag, dcs_tlen, dcs_rg, dcssc_mapq, dcssc_flag, dcssc_tlen, dcssc_rg;
+    DevBuf sscs_rows, corr_rows, dcs_rows;                 // dcs_rows: pool of all duplex rows (see do_duplex)
+    DevBuf dcs_mapq, dcs_flag, dcs_tlen, dcs_rg;
     DevBuf vstart, vsize, big_list, thr_table;
     uint8_t thr_host[128];
     bool thr_valid = false;
@@ -240,7 +241,7 @@ int do_group(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = ctx->read_fam_ready = false;
-    ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = 0;
+    ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = ctx->n_extra = 0;
     ctx->next_ticket = 0;
     TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
     TRY(ensure(ctx, ctx->stats, 16 * sizeof(unsigned long long)));
@@ -353,13 +354,14 @@ int do_join_index(cc_ctx *ctx)
     return CC_OK;
 }
 
-int row_map(cc_ctx *ctx, DevBuf &row, DevBuf &list, uint32_t n_rows)
+int row_map(cc_ctx *ctx, DevBuf &row, DevBuf &list, uint32_t n_rows, uint32_t first_row = 0, bool clear = true)
 {
     const uint32_t nf = ctx->n_fam;
     TRY(ensure(ctx, row, (size_t)nf * 4));
     if (nf == 0) return CC_OK;
-    LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(row), (uint64_t)nf, -1);
-    if (n_rows) LAUNCH(rows_from_list_kernel, blocks_for(n_rows, 256), 256, ptr<uint32_t>(list), n_rows, ptr<int32_t>(row));
+    if (clear) LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(row), (uint64_t)nf, -1);
+    if (n_rows)
+        LAUNCH(rows_from_list_kernel, blocks_for(n_rows, 256), 256, ptr<uint32_t>(list), n_rows, ptr<int32_t>(row), first_row);
     return CC_OK;
 }
 
@@ -375,10 +377,13 @@ int do_lists(cc_ctx *ctx, bool with_join)
     if (with_join) {
         ctx->n_dcs = ctx->host_ctr[CT_NDCS];
         ctx->n_corr = ctx->host_ctr[CT_NCORR];
-        ctx->n_dcssc = ctx->host_ctr[CT_NDCSSC];
+        ctx->n_extra = ctx->host_ctr[CT_NDCSSC];
+        ctx->n_dcssc = ctx->params.scorrect ? ctx->n_dcs + ctx->n_extra : 0;
         TRY(row_map(ctx, ctx->dcs_row, ctx->dcs_list, ctx->n_dcs));
         TRY(row_map(ctx, ctx->corr_row, ctx->corr_list, ctx->n_corr));
-        TRY(row_map(ctx, ctx->dcssc_row, ctx->dcssc_list, ctx->n_dcssc));
+        // second pass: SSCS-SSCS pairs keep their DCS row, the others follow in the same pool
+        TRY(row_map(ctx, ctx->dcssc_row, ctx->dcs_list, ctx->params.scorrect ? ctx->n_dcs : 0));
+        TRY(row_map(ctx, ctx->dcssc_row, ctx->dcssc_list, ctx->n_extra, ctx->n_dcs, false));
     }
     ctx->listed = true;
     return CC_OK;
@@ -477,24 +482,27 @@ RowSources sources(cc_ctx *ctx)
 
 inline uint32_t row_groups(const cc_ctx *ctx) { return ctx->lpad / 8; }
 
+// One pool holds every duplex row: [0, n_dcs) the SSCS-SSCS pairs (DCS_maker's first run; the
+// second run reproduces them unchanged), [n_dcs, n_dcs + n_extra) the pairs of the second run
+// that involve a corrected singleton.
 int do_duplex(cc_ctx *ctx, bool after_sc)
 {
-    const uint32_t rows = after_sc ? ctx->n_dcssc : ctx->n_dcs;
-    DevBuf &out = after_sc ? ctx->dcssc_rows : ctx->dcs_rows;
-    DevBuf &mq = after_sc ? ctx->dcssc_mapq : ctx->dcs_mapq, &fl = after_sc ? ctx->dcssc_flag : ctx->dcs_flag;
-    DevBuf &tl = after_sc ? ctx->dcssc_tlen : ctx->dcs_tlen, &rg = after_sc ? ctx->dcssc_rg : ctx->dcs_rg;
-    TRY(ensure(ctx, out, (size_t)rows * ctx->stride));
-    TRY(ensure(ctx, mq, rows)); TRY(ensure(ctx, rg, rows));
-    TRY(ensure(ctx, fl, (size_t)rows * 2)); TRY(ensure(ctx, tl, (size_t)rows * 4));
+    const uint32_t total = ctx->n_dcs + ctx->n_extra;
+    const uint32_t rows = after_sc ? ctx->n_extra : ctx->n_dcs;
+    const uint32_t first = after_sc ? ctx->n_dcs : 0;
+    TRY(ensure(ctx, ctx->dcs_rows, (size_t)total * ctx->stride));
+    TRY(ensure(ctx, ctx->dcs_mapq, total)); TRY(ensure(ctx, ctx->dcs_rg, total));
+    TRY(ensure(ctx, ctx->dcs_flag, (size_t)total * 2)); TRY(ensure(ctx, ctx->dcs_tlen, (size_t)total * 4));
     const int ph = after_sc ? CC_PH_DCS_SC : CC_PH_DCS;
     TRY(phase_begin(ctx, ph));
     if (rows) {
         const uint32_t g = row_groups(ctx);
         LAUNCH(duplex_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx),
                ptr<uint32_t>(after_sc ? ctx->dcssc_list : ctx->dcs_list), ptr<int32_t>(ctx->partner), rows, ctx->lpad, g,
-               after_sc ? 1 : 0, ptr<uint8_t>(out), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
-               ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<uint8_t>(mq), ptr<uint16_t>(fl),
-               ptr<int32_t>(tl), ptr<uint8_t>(rg));
+               after_sc ? 1 : 0, ptr<uint8_t>(ctx->dcs_rows) + (size_t)first * ctx->stride,
+               ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
+               ptr<uint8_t>(ctx->fam_rg), ptr<uint8_t>(ctx->dcs_mapq) + first, ptr<uint16_t>(ctx->dcs_flag) + first,
+               ptr<int32_t>(ctx->dcs_tlen) + first, ptr<uint8_t>(ctx->dcs_rg) + first);
     }
     TRY(phase_end(ctx, ph));
     return CC_OK;
@@ -572,8 +580,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
                      &ctx->f_dcssc, &ctx->sscs_list, &ctx->dcs_list, &ctx->corr_list, &ctx->dcssc_list, &ctx->sscs_row,
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
-                     &ctx->dcssc_rows, &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->dcssc_mapq,
-                     &ctx->dcssc_flag, &ctx->dcssc_tlen, &ctx->dcssc_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
+                     &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
                      &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->thr_table};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
@@ -742,15 +749,15 @@ static const void *array_ptr(cc_ctx *ctx, int what, uint64_t *bytes)
     case CC_SSCS_ROWS: if (!ctx->voted) return nullptr; *bytes = ctx->n_sscs * S; return ctx->sscs_rows.p;
     case CC_CORR_ROWS: if (!ctx->rescued) return nullptr; *bytes = ctx->n_corr * S; return ctx->corr_rows.p;
     case CC_DCS_ROWS: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs * S; return ctx->dcs_rows.p;
-    case CC_DCSSC_ROWS: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * S; return ctx->dcssc_rows.p;
+    case CC_DCSSC_ROWS: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * S; return ctx->dcs_rows.p;
     case CC_DCS_MAPQ: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs; return ctx->dcs_mapq.p;
     case CC_DCS_FLAG: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs * 2ull; return ctx->dcs_flag.p;
     case CC_DCS_TLEN: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs * 4ull; return ctx->dcs_tlen.p;
     case CC_DCS_RG: if (!ctx->joined) return nullptr; *bytes = ctx->n_dcs; return ctx->dcs_rg.p;
-    case CC_DCSSC_MAPQ: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcssc_mapq.p;
-    case CC_DCSSC_FLAG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 2ull; return ctx->dcssc_flag.p;
-    case CC_DCSSC_TLEN: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 4ull; return ctx->dcssc_tlen.p;
-    case CC_DCSSC_RG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcssc_rg.p;
+    case CC_DCSSC_MAPQ: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcs_mapq.p;
+    case CC_DCSSC_FLAG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 2ull; return ctx->dcs_flag.p;
+    case CC_DCSSC_TLEN: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 4ull; return ctx->dcs_tlen.p;
+    case CC_DCSSC_RG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcs_rg.p;
     case CC_STATS: *bytes = 16 * 8; return ctx->stats.p;
     case CC_FAM_HIST: *bytes = CC_HIST_BINS * 8ull; return ctx->hist.p;
     default: return nullptr;

@@ -293,7 +293,9 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
         bool dcs = big && p_big && c < (uint32_t)p;
         bool corr = scorrect && !big && p >= 0;
         bool dcssc = scorrect && p >= 0 && leads_after_sc(c, (uint32_t)p, big, p_big);
-        f_dcs[c] = dcs; f_corr[c] = corr; f_dcssc[c] = dcssc;
+        // a pair of two SSCS gives the same record before and after the rescue: its row is shared,
+        // only pairs that involve a corrected singleton get a row of their own in the second pass
+        f_dcs[c] = dcs; f_corr[c] = corr; f_dcssc[c] = dcssc && !dcs;
         atomicAdd(&s_st[big ? 0 : 1], 1u);
         if (dcs) atomicAdd(&s_st[2], 1u);
         if (big && !p_big) atomicAdd(&s_st[3], 1u);
@@ -309,12 +311,12 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
     if (threadIdx.x < 16 && s_st[threadIdx.x]) atomicAdd(&stats[threadIdx.x], (unsigned long long)s_st[threadIdx.x]);
 }
 
-// row[list[r]] = r for the families that own a row; everything else stays -1
+// row[list[r]] = first_row + r for the families that own a row; everything else stays -1
 __global__ void __launch_bounds__(256)
-rows_from_list_kernel(const uint32_t *__restrict__ list, uint32_t n_rows, int32_t *__restrict__ row)
+rows_from_list_kernel(const uint32_t *__restrict__ list, uint32_t n_rows, int32_t *__restrict__ row, uint32_t first_row)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r < n_rows) row[list[r]] = (int32_t)r;
+    if (r < n_rows) row[list[r]] = (int32_t)(first_row + r);
 }
 
 // ---- K4 + K5: SSCS vote and family mode fields ------------------------------------------------

@@ -19,11 +19,18 @@
 
 #include "kernels.cuh"
 
+#ifndef VOTE_DEPTH_CFG
+#define VOTE_DEPTH_CFG 3
+#endif
+#ifndef VOTE_BLOCKS_CFG
+#define VOTE_BLOCKS_CFG 2
+#endif
+
 namespace ccgpu {
 
 constexpr uint32_t VOTE_SMALL_MAX = 31;      // T counts are kept times 8 in a byte lane
 constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows per staged batch
-constexpr int VOTE_DEPTH = 3;                // ring slots per lane: VOTE_DEPTH - 1 batches in flight
+constexpr int VOTE_DEPTH = VOTE_DEPTH_CFG;                // ring slots per lane: VOTE_DEPTH - 1 batches in flight
 constexpr int VOTE_RING_BYTES = VOTE_DEPTH * VOTE_ROWS_PER_BATCH * 256 * 24;   // dynamic shared memory per block
 
 __device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
@@ -70,6 +77,7 @@ __device__ __forceinline__ uint32_t fadd(uint32_t x, uint32_t y, uint32_t one) {
 
 struct Quad {            // accumulators of 4 positions (one byte lane each)
     uint32_t cA, cC, cG, cT, pc;     // cC, cG, cT hold 2x, 4x, 8x the count (no shifts in the row loop)
+    uint32_t qany;                   // OR of the passing qualities: the supporter's quality when one read passes
 };
 
 __device__ __forceinline__ void quad_add(Quad &a, uint32_t nib, uint32_t q, uint32_t &err, uint32_t one)
@@ -82,6 +90,14 @@ __device__ __forceinline__ void quad_add(Quad &a, uint32_t nib, uint32_t q, uint
     a.cG = fadd(b & 0x04040404u, a.cG, one);
     a.cT = fadd(b & 0x08080808u, a.cT, one);
     a.pc = fadd(m & 0x01010101u, a.pc, one);
+    a.qany |= q & m;
+}
+
+__device__ __forceinline__ uint32_t cap60(uint32_t q)
+{
+    uint32_t lo = q & 0x7F7F7F7Fu;
+    uint32_t big = bytes_of(ge7(lo, 0x3C3C3C3Cu) | (q & 0x80808080u));
+    return sel(0x3C3C3C3Cu, lo, big);
 }
 
 struct QuadOut {
@@ -119,8 +135,10 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
     }
     o.code = sel(o.win, 0x0F0F0F0Fu, ok);
     uint32_t two = bytes_of(ge7(best, 0x02020202u));
-    o.single = bytes_of(nz7(best)) & ~two;
-    o.qual = two & 0x3C3C3C3Cu;                            // 60 where two or more passing reads agree
+    uint32_t lone = bytes_of(nz7(best)) & ~two;            // winner has exactly one supporter
+    uint32_t one_pass = lone & ~bytes_of(ge7(pass, 0x02020202u));   // ... and it is the only passing read
+    o.single = lone & ~one_pass;                           // several passing reads, all different: needs a re-walk
+    o.qual = (two & 0x3C3C3C3Cu) | (cap60(a.qany) & one_pass);     // 60 where two or more passing reads agree
     return o;
 }
 
@@ -130,13 +148,6 @@ __device__ __forceinline__ uint32_t quad_pick(uint32_t nib, uint32_t q, uint32_t
     uint32_t b = nib & bytes_of(pass7_of(q));
     uint32_t same = ~bytes_of(nz7(b ^ win)) & single;      // win is never 0, so `same` implies passing
     return q & same;
-}
-
-__device__ __forceinline__ uint32_t cap60(uint32_t q)
-{
-    uint32_t lo = q & 0x7F7F7F7Fu;
-    uint32_t big = bytes_of(ge7(lo, 0x3C3C3C3Cu) | (q & 0x80808080u));
-    return sel(0x3C3C3C3Cu, lo, big);
 }
 
 struct LaneRow {
@@ -216,7 +227,7 @@ constexpr int VOTE_CHUNK = 1024;    // SSCS rows a block sorts by family size an
 // hands them to its lane groups in that order, so the groups of a warp walk families of
 // (nearly) equal size and their row loops stay in step.
 template <int G>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, VOTE_BLOCKS_CFG)
 vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
                   uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
                   const uint32_t *__restrict__ vsize, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
@@ -355,7 +366,7 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
             } else {
                 Quad acc[4];
 #pragma unroll
-                for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0};
+                for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0, 0};
                 const uint32_t first_batch = c_batch;
                 for (uint32_t j0 = 0; j0 < n; j0 += VOTE_ROWS_PER_BATCH) {
                     p_issue();

@@ -88,7 +88,9 @@ enum cc_array {
     CC_SSCS_ROWS = 12,   /* [u8 x n_sscs x stride]  consensus_maker output            */
     CC_CORR_ROWS = 13,   /* [u8 x n_corr x stride]  corrected singletons              */
     CC_DCS_ROWS = 14,    /* [u8 x n_dcs x stride]   duplex_consensus (DCS_maker)      */
-    CC_DCSSC_ROWS = 15,  /* [u8 x n_dcssc x stride] DCS after singleton correction    */
+    CC_DCSSC_ROWS = 15,  /* [u8 x n_dcssc x stride] DCS after singleton correction; its first n_dcs rows
+                            ARE the CC_DCS_ROWS (two SSCS pair up identically in both DCS_maker runs),
+                            the pairs that involve a corrected singleton follow */
     CC_DCS_MAPQ = 16, CC_DCS_FLAG = 17, CC_DCS_TLEN = 18, CC_DCS_RG = 19,         /* per DCS row   */
     CC_DCSSC_MAPQ = 20, CC_DCSSC_FLAG = 21, CC_DCSSC_TLEN = 22, CC_DCSSC_RG = 23, /* per DCS-SC row */
     CC_STATS = 24,       /* [i64 x 16] see cc_stat                                    */

@@ -332,7 +332,9 @@ int cco_run(void *ctx, int scorrect)
         k.bits ^= 2u;                                        /* R1 <-> R2 */
         c->partner[g] = (int32_t)table_find(c, &k);
     }
-    /* classify, number the output rows in family creation order */
+    /* classify, number the output rows in family creation order.  A pair of two SSCS yields the
+     * same record in both DCS_maker runs, so the second run's rows are laid out as
+     * [the nd DCS rows | pairs that involve a corrected singleton]. */
     uint64_t ns = 0, nc = 0, nd = 0, ndsc = 0;
     int64_t *st = c->stats;
     for (uint64_t g = 0; g < nf; g++) {
@@ -341,10 +343,7 @@ int cco_run(void *ctx, int scorrect)
         c->sscs_row[g] = big ? (int32_t)ns++ : -1;
         c->dcs_row[g] = (big && p >= 0 && c->fam_size[p] >= 2 && leads(c, g, (uint64_t)p, 0)) ? (int32_t)nd++ : -1;
         c->corr_row[g] = -1; c->dcssc_row[g] = -1;
-        if (scorrect) {
-            if (!big && p >= 0) c->corr_row[g] = (int32_t)nc++;
-            if (p >= 0 && leads(c, g, (uint64_t)p, 1)) c->dcssc_row[g] = (int32_t)ndsc++;
-        }
+        if (scorrect && !big && p >= 0) c->corr_row[g] = (int32_t)nc++;
         if (big) st[0]++; else st[1]++;                          /* SSCS reads / singletons */
         if (big && !(p >= 0 && c->fam_size[p] >= 2)) st[3]++;    /* SSCS singletons (no duplex) */
         if (scorrect) {
@@ -352,6 +351,14 @@ int cco_run(void *ctx, int scorrect)
             if (!big && p >= 0 && c->fam_size[p] < 2) st[5]++;   /* rescued by singleton */
             if (!big && p < 0) st[6]++;                          /* uncorrected */
             if (big && p < 0) st[8]++;                           /* SSCS SC singletons */
+        }
+    }
+    if (scorrect) {
+        ndsc = nd;
+        for (uint64_t g = 0; g < nf; g++) {
+            int32_t p = c->partner[g];
+            if (p < 0 || !leads(c, g, (uint64_t)p, 1)) continue;
+            c->dcssc_row[g] = c->dcs_row[g] >= 0 ? c->dcs_row[g] : (int32_t)ndsc++;
         }
     }
     st[2] = (int64_t)nd; st[7] = (int64_t)ndsc;
