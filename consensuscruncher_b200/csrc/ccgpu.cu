@@ -480,7 +480,7 @@ RowSources sources(cc_ctx *ctx)
     return s;
 }
 
-inline uint32_t row_groups(const cc_ctx *ctx) { return ctx->lpad / 8; }
+inline uint32_t row_groups(const cc_ctx *ctx) { return (ctx->lpad + 15) / 16; }   // threads per row, 16 positions each
 
 // One pool holds every duplex row: [0, n_dcs) the SSCS-SSCS pairs (DCS_maker's first run; the
 // second run reproduces them unchanged), [n_dcs, n_dcs + n_extra) the pairs of the second run
@@ -497,7 +497,7 @@ int do_duplex(cc_ctx *ctx, bool after_sc)
     TRY(phase_begin(ctx, ph));
     if (rows) {
         const uint32_t g = row_groups(ctx);
-        LAUNCH(duplex_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx),
+        LAUNCH(duplex16_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx),
                ptr<uint32_t>(after_sc ? ctx->dcssc_list : ctx->dcs_list), ptr<int32_t>(ctx->partner), rows, ctx->lpad, g,
                after_sc ? 1 : 0, ptr<uint8_t>(ctx->dcs_rows) + (size_t)first * ctx->stride,
                ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
@@ -515,7 +515,7 @@ int do_rescue(cc_ctx *ctx)
     TRY(phase_begin(ctx, CC_PH_RESCUE));
     if (rows) {
         const uint32_t g = row_groups(ctx);
-        LAUNCH(rescue_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx), ptr<uint32_t>(ctx->corr_list),
+        LAUNCH(rescue16_kernel, blocks_for((uint64_t)rows * g, 256), 256, sources(ctx), ptr<uint32_t>(ctx->corr_list),
                ptr<int32_t>(ctx->partner), rows, ctx->lpad, g, ptr<uint8_t>(ctx->corr_rows));
     }
     TRY(phase_end(ctx, CC_PH_RESCUE));
@@ -857,8 +857,8 @@ int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2,
     TRY(ensure(ctx, ctx->tmp_a, bytes)); TRY(ensure(ctx, ctx->tmp_b, bytes)); TRY(ensure(ctx, ctx->tmp_c, bytes));
     CK(cudaMemcpyAsync(ctx->tmp_a.p, rows1, bytes, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->tmp_b.p, rows2, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    const uint32_t g = lpad / 8;
-    auto kernel = sc ? agree_pairs_kernel<true> : agree_pairs_kernel<false>;
+    const uint32_t g = (lpad + 15) / 16;
+    auto kernel = sc ? agree_pairs16_kernel<true> : agree_pairs16_kernel<false>;
     LAUNCH(kernel, blocks_for(n_pairs * g, 256), 256, ptr<uint8_t>(ctx->tmp_a),
            ptr<uint8_t>(ctx->tmp_b), n_pairs, lpad, stride, g, ptr<uint8_t>(ctx->tmp_c));
     CK(cudaMemcpyAsync(out_rows, ctx->tmp_c.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));

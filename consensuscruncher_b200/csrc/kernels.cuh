@@ -498,48 +498,6 @@ vote_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payloa
                      out_rows + (uint64_t)row * stride, c, fam_mapq, fam_flag, fam_tlen, fam_rg, err_flag);
 }
 
-// ---- K7: duplex_consensus on two rows --------------------------------------------------------------
-// DCS_maker.py:107-119: equal bases -> base, min(60, q1+q2); else N, 0 (no quality filter).
-// singleton_correction.py:69-82: additionally both qualities must be > 29.
-// One thread handles 8 positions: 4 sequence bytes and 8 quality bytes of each row.
-template <bool SC>
-__device__ __forceinline__ void agree8(uint32_t s1, uint32_t s2, uint2 q1, uint2 q2, uint32_t &so, uint2 &qo)
-{
-    so = 0; qo.x = 0; qo.y = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        // position k: byte k/2 of the sequence word, high nibble when k is even
-        int sh = (k >> 1) * 8 + ((k & 1) ? 0 : 4);
-        uint32_t b1 = (s1 >> sh) & 15u, b2 = (s2 >> sh) & 15u;
-        uint32_t a = ((k < 4 ? q1.x : q1.y) >> ((k & 3) * 8)) & 0xFFu;
-        uint32_t b = ((k < 4 ? q2.x : q2.y) >> ((k & 3) * 8)) & 0xFFu;
-        bool ok = b1 == b2 && (!SC || (a > (uint32_t)Q_SC && b > (uint32_t)Q_SC));
-        uint32_t code = ok ? b1 : 15u;
-        uint32_t q = ok ? min(a + b, (uint32_t)Q_CAP) : 0u;
-        so |= code << sh;
-        if (k < 4) qo.x |= q << ((k & 3) * 8); else qo.y |= q << ((k & 3) * 8);
-    }
-}
-
-template <bool SC>
-__device__ __forceinline__ void agree_rows(const uint8_t *__restrict__ r1, const uint8_t *__restrict__ r2,
-                                           uint8_t *__restrict__ out, uint32_t lpad, uint32_t stride,
-                                           uint32_t g, uint32_t groups)
-{
-    const uint32_t half = lpad >> 1;
-    if (g < (lpad >> 3)) {
-        uint32_t s1 = *reinterpret_cast<const uint32_t *>(r1 + g * 4);
-        uint32_t s2 = *reinterpret_cast<const uint32_t *>(r2 + g * 4);
-        uint2 q1 = *reinterpret_cast<const uint2 *>(r1 + half + g * 8);
-        uint2 q2 = *reinterpret_cast<const uint2 *>(r2 + half + g * 8);
-        uint32_t so; uint2 qo;
-        agree8<SC>(s1, s2, q1, q2, so, qo);
-        *reinterpret_cast<uint32_t *>(out + g * 4) = so;
-        *reinterpret_cast<uint2 *>(out + half + g * 8) = qo;
-    }
-    for (uint32_t x = half + lpad + g * 4; x < stride; x += groups * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
-}
-
 // mode of two records (create_aligned_segment on [lead, partner]): equal -> value, else the
 // lead's value (first appearance); flags prefer 99 > 83 > 147 > 163
 __device__ __forceinline__ uint32_t pair_mode(uint32_t a, uint32_t b, bool is_flag)
@@ -559,64 +517,6 @@ struct RowSources {
     const int32_t *corr_row;
     uint32_t stride;
 };
-
-// singleton rescue: row r <-> singleton family corr_list[r]; partner SSCS consensus if the
-// partner family has one, else the partner singleton's original read
-__global__ void __launch_bounds__(256)
-rescue_kernel(RowSources src, const uint32_t *__restrict__ corr_list, const int32_t *__restrict__ partner,
-              uint32_t n_rows, uint32_t lpad, uint32_t groups, uint8_t *__restrict__ out_rows)
-{
-    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t row = (uint32_t)(t / groups), g = (uint32_t)(t % groups);
-    if (row >= n_rows) return;
-    uint32_t c = corr_list[row];
-    uint32_t p = (uint32_t)partner[c];
-    const uint8_t *mine = src.payload + (uint64_t)src.tmpl[c] * src.stride;
-    const uint8_t *other = src.fam_size[p] >= 2 ? src.sscs_rows + (uint64_t)src.sscs_row[p] * src.stride
-                                                : src.payload + (uint64_t)src.tmpl[p] * src.stride;
-    agree_rows<true>(mine, other, out_rows + (uint64_t)row * src.stride, lpad, src.stride, g, groups);
-}
-
-// DCS (after_sc = 0: both rows are SSCS consensus) or DCS over SSCS + corrected singletons
-__global__ void __launch_bounds__(256)
-duplex_kernel(RowSources src, const uint32_t *__restrict__ lead_list, const int32_t *__restrict__ partner,
-              uint32_t n_rows, uint32_t lpad, uint32_t groups, int after_sc, uint8_t *__restrict__ out_rows,
-              const uint8_t *__restrict__ fam_mapq, const uint16_t *__restrict__ fam_flag,
-              const int32_t *__restrict__ fam_tlen, const uint8_t *__restrict__ fam_rg,
-              uint8_t *__restrict__ o_mapq, uint16_t *__restrict__ o_flag, int32_t *__restrict__ o_tlen,
-              uint8_t *__restrict__ o_rg)
-{
-    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t row = (uint32_t)(t / groups), g = (uint32_t)(t % groups);
-    if (row >= n_rows) return;
-    uint32_t c = lead_list[row];
-    uint32_t p = (uint32_t)partner[c];
-    auto row_of = [&](uint32_t x) -> const uint8_t * {
-        if (!after_sc || src.fam_size[x] >= 2) return src.sscs_rows + (uint64_t)src.sscs_row[x] * src.stride;
-        return src.corr_rows + (uint64_t)src.corr_row[x] * src.stride;
-    };
-    agree_rows<false>(row_of(c), row_of(p), out_rows + (uint64_t)row * src.stride, lpad, src.stride, g, groups);
-    if (g == 0) {
-        o_mapq[row] = (uint8_t)pair_mode(fam_mapq[c], fam_mapq[p], false);
-        o_tlen[row] = (int32_t)pair_mode((uint32_t)fam_tlen[c], (uint32_t)fam_tlen[p], false);
-        o_flag[row] = (uint16_t)pair_mode(fam_flag[c], fam_flag[p], true);
-        uint32_t ra = fam_rg[c], rb = fam_rg[p];
-        o_rg[row] = (ra == 0xFFu || rb == 0xFFu) ? 0xFFu : (uint8_t)pair_mode(ra, rb, false);
-    }
-}
-
-// stand-alone duplex_consensus over independent row pairs (cc_duplex_consensus)
-template <bool SC>
-__global__ void __launch_bounds__(256)
-agree_pairs_kernel(const uint8_t *__restrict__ rows1, const uint8_t *__restrict__ rows2, uint64_t n_pairs,
-                   uint32_t lpad, uint32_t stride, uint32_t groups, uint8_t *__restrict__ out_rows)
-{
-    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint64_t row = t / groups;
-    uint32_t g = (uint32_t)(t % groups);
-    if (row >= n_pairs) return;
-    agree_rows<SC>(rows1 + row * stride, rows2 + row * stride, out_rows + row * stride, lpad, stride, g, groups);
-}
 
 __global__ void fill_i32_kernel(int32_t *p, uint64_t n, int32_t v)
 {

@@ -493,4 +493,106 @@ vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ pa
     }
 }
 
+
+// ---- K7: duplex_consensus on two rows, 16 positions per thread --------------------------------
+// DCS_maker.py:107-119: equal bases -> base, min(60, q1+q2); else N, 0 (no quality filter).
+// singleton_correction.py:69-82: additionally both qualities must be > 29 - and then the sum is
+// at least 60, so the quality is 60 wherever the base survives.
+template <bool SC>
+__device__ __forceinline__ void quad_agree(uint32_t n1, uint32_t q1, uint32_t n2, uint32_t q2, uint32_t &code, uint32_t &qual)
+{
+    uint32_t eq = ~bytes_of(nz7(n1 ^ n2));
+    if (SC) {
+        eq &= bytes_of(pass7_of(q1)) & bytes_of(pass7_of(q2));
+        qual = eq & 0x3C3C3C3Cu;
+    } else {
+        qual = eq & cap60(cap60(q1) + cap60(q2));          // min(60, q1+q2) == min(60, min(60,q1) + min(60,q2))
+    }
+    code = sel(n1, 0x0F0F0F0Fu, eq);
+}
+
+template <bool SC>
+__device__ __forceinline__ void agree_lane(const uint8_t *__restrict__ r1, const uint8_t *__restrict__ r2,
+                                           uint8_t *__restrict__ out, uint32_t lpad, uint32_t stride, uint32_t lane,
+                                           uint32_t lanes)
+{
+    const uint32_t half = lpad >> 1, pos0 = lane * 16;
+    if (pos0 < lpad) {
+        LaneRow a{__ldg(reinterpret_cast<const uint2 *>(r1 + (pos0 >> 1))), __ldg(reinterpret_cast<const uint4 *>(r1 + half + pos0))};
+        LaneRow b{__ldg(reinterpret_cast<const uint2 *>(r2 + (pos0 >> 1))), __ldg(reinterpret_cast<const uint4 *>(r2 + half + pos0))};
+        uint32_t n1[4], q1[4], n2[4], q2[4], code[4], qual[4];
+        split_row(a, n1, q1);
+        split_row(b, n2, q2);
+#pragma unroll
+        for (int g = 0; g < 4; g++) quad_agree<SC>(n1[g], q1[g], n2[g], q2[g], code[g], qual[g]);
+        uint2 so;
+        uint4 qo;
+        so.x = (code[0] << 4) | code[1];
+        so.y = (code[2] << 4) | code[3];
+        qo.x = __byte_perm(qual[0], qual[1], 0x5140); qo.y = __byte_perm(qual[0], qual[1], 0x7362);
+        qo.z = __byte_perm(qual[2], qual[3], 0x5140); qo.w = __byte_perm(qual[2], qual[3], 0x7362);
+        *reinterpret_cast<uint2 *>(out + (pos0 >> 1)) = so;
+        *reinterpret_cast<uint4 *>(out + half + pos0) = qo;
+    }
+    for (uint32_t x = half + lpad + lane * 4; x < stride; x += lanes * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
+}
+
+// singleton rescue: row r <-> singleton family corr_list[r]; partner SSCS consensus if the
+// partner family has one, else the partner singleton's original read
+__global__ void __launch_bounds__(256)
+rescue16_kernel(RowSources src, const uint32_t *__restrict__ corr_list, const int32_t *__restrict__ partner,
+                uint32_t n_rows, uint32_t lpad, uint32_t lanes, uint8_t *__restrict__ out_rows)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t row = (uint32_t)(t / lanes), lane = (uint32_t)(t % lanes);
+    if (row >= n_rows) return;
+    uint32_t c = corr_list[row];
+    uint32_t p = (uint32_t)partner[c];
+    const uint8_t *mine = src.payload + (uint64_t)src.tmpl[c] * src.stride;
+    const uint8_t *other = src.fam_size[p] >= 2 ? src.sscs_rows + (uint64_t)src.sscs_row[p] * src.stride
+                                                : src.payload + (uint64_t)src.tmpl[p] * src.stride;
+    agree_lane<true>(mine, other, out_rows + (uint64_t)row * src.stride, lpad, src.stride, lane, lanes);
+}
+
+// DCS (after_sc = 0: both rows are SSCS consensus) or DCS over SSCS + corrected singletons
+__global__ void __launch_bounds__(256)
+duplex16_kernel(RowSources src, const uint32_t *__restrict__ lead_list, const int32_t *__restrict__ partner,
+                uint32_t n_rows, uint32_t lpad, uint32_t lanes, int after_sc, uint8_t *__restrict__ out_rows,
+                const uint8_t *__restrict__ fam_mapq, const uint16_t *__restrict__ fam_flag,
+                const int32_t *__restrict__ fam_tlen, const uint8_t *__restrict__ fam_rg,
+                uint8_t *__restrict__ o_mapq, uint16_t *__restrict__ o_flag, int32_t *__restrict__ o_tlen,
+                uint8_t *__restrict__ o_rg)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t row = (uint32_t)(t / lanes), lane = (uint32_t)(t % lanes);
+    if (row >= n_rows) return;
+    uint32_t c = lead_list[row];
+    uint32_t p = (uint32_t)partner[c];
+    auto row_of = [&](uint32_t x) -> const uint8_t * {
+        if (!after_sc || src.fam_size[x] >= 2) return src.sscs_rows + (uint64_t)src.sscs_row[x] * src.stride;
+        return src.corr_rows + (uint64_t)src.corr_row[x] * src.stride;
+    };
+    agree_lane<false>(row_of(c), row_of(p), out_rows + (uint64_t)row * src.stride, lpad, src.stride, lane, lanes);
+    if (lane == 0) {
+        o_mapq[row] = (uint8_t)pair_mode(fam_mapq[c], fam_mapq[p], false);
+        o_tlen[row] = (int32_t)pair_mode((uint32_t)fam_tlen[c], (uint32_t)fam_tlen[p], false);
+        o_flag[row] = (uint16_t)pair_mode(fam_flag[c], fam_flag[p], true);
+        uint32_t ra = fam_rg[c], rb = fam_rg[p];
+        o_rg[row] = (ra == 0xFFu || rb == 0xFFu) ? 0xFFu : (uint8_t)pair_mode(ra, rb, false);
+    }
+}
+
+// stand-alone duplex_consensus over independent row pairs (cc_duplex_consensus)
+template <bool SC>
+__global__ void __launch_bounds__(256)
+agree_pairs16_kernel(const uint8_t *__restrict__ rows1, const uint8_t *__restrict__ rows2, uint64_t n_pairs,
+                     uint32_t lpad, uint32_t stride, uint32_t lanes, uint8_t *__restrict__ out_rows)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t row = t / lanes;
+    uint32_t lane = (uint32_t)(t % lanes);
+    if (row >= n_pairs) return;
+    agree_lane<SC>(rows1 + row * stride, rows2 + row * stride, out_rows + row * stride, lpad, stride, lane, lanes);
+}
+
 }  // namespace ccgpu
