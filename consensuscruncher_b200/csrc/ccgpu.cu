@@ -55,6 +55,7 @@ struct cc_ctx {
     // families
     uint32_t n_fam = 0, n_sscs = 0, n_dcs = 0, n_corr = 0, n_dcssc = 0;   // n_dcssc = n_dcs + n_extra when rescuing
     uint32_t n_extra = 0;                                                 // second-pass pairs with a row of their own
+    DevBuf bitmap, word_rank, first_read;
     DevBuf tmpl, c2hs, fam_start, fam_size, is_sscs, fam_mapq, fam_flag, fam_tlen, fam_rg;
     DevBuf partner, table, f_dcs, f_corr, f_dcssc;
     DevBuf sscs_list, dcs_list, corr_list, dcssc_list, sscs_row, dcs_row, corr_row, dcssc_row;
@@ -208,14 +209,15 @@ int compact_flags(cc_ctx *ctx, const uint8_t *flags, uint64_t n, uint32_t *list,
     return CC_OK;
 }
 
-int compact_marks(cc_ctx *ctx, const uint32_t *marks, uint64_t n, uint32_t *list, uint32_t *carry)
+// out[w] = number of set bits in words[0 .. w)
+int scan_popcounts(cc_ctx *ctx, const uint32_t *words, uint32_t *out, uint64_t n)
 {
     if (n == 0) return CC_OK;
     uint32_t *ticket;
     TRY(scan_prepare(ctx, n, &ticket));
-    auto kernel = scan_kernel<SCAN_MODE_COMPACT_CARRY, uint32_t>;
-    LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, marks, list,
-           carry, n, ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr);
+    auto kernel = scan_kernel<SCAN_MODE_POPC, uint32_t>;
+    LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, words, out, (uint32_t *)nullptr, n,
+           ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr);
     return CC_OK;
 }
 
@@ -288,30 +290,34 @@ int do_group(cc_ctx *ctx)
     uint32_t *mixed_list = ctx->spare_keys;        // dead after the sort; at most n/2 runs
     LAUNCH(boundary_kernel, blocks_for(n, 256), 256, ctx->fields, ctx->sorted_keys, ctx->perm, n,
            ptr<uint8_t>(ctx->head), mixed_list, ctr + CT_MIXED, (uint32_t)(n / 2 + 1));
-    TRY(read_counters(ctx));                        // number of mixed runs
-    if (ctx->host_ctr[CT_MIXED]) {
-        uint32_t nm = ctx->host_ctr[CT_MIXED];
-        LAUNCH(fix_mixed_runs_kernel, blocks_for((uint64_t)nm * 32, 128), 128, ctx->fields, ctx->sorted_keys, ctx->perm,
-               ctx->spare_vals, n, ptr<uint8_t>(ctx->head), mixed_list, nm);
-    }
+    // collided runs (if any) are regrouped by however many warps the device-side count asks for
+    LAUNCH(fix_mixed_runs_kernel, 592, 128, ctx->fields, ctx->sorted_keys, ctx->perm, ctx->spare_vals, n,
+           ptr<uint8_t>(ctx->head), mixed_list, ctr + CT_MIXED, (uint32_t)(n / 2 + 1));
     uint32_t *hs_start = ctx->spare_keys;          // reused again: start of every family in sorted order
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->head), n, hs_start, ctr + CT_NFAM));
     TRY(read_counters(ctx));
     const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
 
-    TRY(ensure(ctx, ctx->tmpl, (size_t)nf * 4)); TRY(ensure(ctx, ctx->c2hs, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->tmpl, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->fam_start, (size_t)nf * 4)); TRY(ensure(ctx, ctx->fam_size, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->is_sscs, nf)); TRY(ensure(ctx, ctx->fam_mapq, nf)); TRY(ensure(ctx, ctx->fam_rg, nf));
     TRY(ensure(ctx, ctx->fam_flag, (size_t)nf * 2)); TRY(ensure(ctx, ctx->fam_tlen, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4));
 
-    uint32_t *mark = ctx->spare_vals;              // dead after the fix-up
-    CK(cudaMemsetAsync(mark, 0, n * 4, ctx->stream));
-    LAUNCH(mark_first_kernel, blocks_for(nf, 256), 256, hs_start, ctx->perm, nf, mark);
-    TRY(compact_marks(ctx, mark, n, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->c2hs)));
-    LAUNCH(family_build_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->c2hs), hs_start,
-           ptr<uint32_t>(ctx->tmpl), ptr<uint8_t>(ctx->head), nf, (uint32_t)n, ptr<uint32_t>(ctx->fam_start),
-           ptr<uint32_t>(ctx->fam_size),
+    // creation order: bitmap of first members + rank queries (see family_build_kernel)
+    const uint64_t words = (n + 31) / 32;
+    TRY(ensure(ctx, ctx->bitmap, words * 4)); TRY(ensure(ctx, ctx->word_rank, words * 4));
+    TRY(ensure(ctx, ctx->first_read, (size_t)nf * 4));
+    CK(cudaMemsetAsync(ctx->bitmap.p, 0, words * 4, ctx->stream));
+    LAUNCH(mark_first_kernel, blocks_for(nf, 256), 256, hs_start, ctx->perm, nf, ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->first_read));
+    TRY(scan_popcounts(ctx, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), words));
+    TRY(ensure(ctx, ctx->c2hs, (size_t)nf * 4));
+    LAUNCH(creation_rank_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->first_read), ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->word_rank), nf, ptr<uint32_t>(ctx->c2hs));
+    LAUNCH(family_build_kernel, blocks_for(nf, 256), 256, ctx->fields, hs_start, ptr<uint32_t>(ctx->first_read),
+           ptr<uint32_t>(ctx->c2hs), ptr<uint8_t>(ctx->head), nf, (uint32_t)n,
+           ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
            ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
            (uint32_t)CC_HIST_BINS);
@@ -581,7 +587,8 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->f_dcssc, &ctx->sscs_list, &ctx->dcs_list, &ctx->corr_list, &ctx->dcssc_list, &ctx->sscs_row,
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
-                     &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->thr_table};
+                     &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
+                     &ctx->first_read};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);

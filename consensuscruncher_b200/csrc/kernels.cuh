@@ -103,11 +103,13 @@ boundary_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ k
 __global__ void __launch_bounds__(128)
 fix_mixed_runs_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ keys,
                       uint32_t *__restrict__ perm, uint32_t *__restrict__ tmp, uint64_t n,
-                      uint8_t *__restrict__ head, const uint32_t *__restrict__ mixed_list, uint32_t n_mixed)
+                      uint8_t *__restrict__ head, const uint32_t *__restrict__ mixed_list,
+                      const uint32_t *__restrict__ n_mixed_ptr, uint32_t mixed_cap)
 {
     const int lane = threadIdx.x & 31;
-    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (w >= n_mixed) return;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t n_mixed = min(*n_mixed_ptr, mixed_cap);
+    for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_mixed; w += warps) {
     const uint64_t s = mixed_list[w];
     const uint32_t k = keys[s];
     uint64_t e = s + 1;
@@ -145,24 +147,45 @@ fix_mixed_runs_kernel(const uint4 *__restrict__ fields, const uint32_t *__restri
         __syncwarp();
     }
     for (uint64_t x = s + lane; x < e; x += 32) perm[x] = tmp[x];
+    __syncwarp();
+    }
 }
 
 // ---- families in creation order -----------------------------------------------------
-// mark[first member of sorted family f] = f + 1   (stable sort => first member = min index)
+// A family is created by its first member (stable sort => the first element of its segment).
+// One bit per read marks the first members; a family's creation number is the number of marks
+// below its own, i.e. a rank query in that bitmap (N / 8 bytes, resident in L2).
 __global__ void __launch_bounds__(256)
 mark_first_kernel(const uint32_t *__restrict__ hs_start, const uint32_t *__restrict__ perm,
-                  uint32_t n_fam, uint32_t *__restrict__ mark)
+                  uint32_t n_fam, uint32_t *__restrict__ bitmap, uint32_t *__restrict__ first_read)
 {
     uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < n_fam) mark[perm[hs_start[f]]] = f + 1;
+    if (f >= n_fam) return;
+    uint32_t first = perm[hs_start[f]];
+    first_read[f] = first;
+    atomicOr(&bitmap[first >> 5], 1u << (first & 31));
 }
 
-// family c (creation order) -> its segment of perm, size, singleton meta, size histogram
+// c2hs[creation number of sorted family f] = f
 __global__ void __launch_bounds__(256)
-family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ c2hs,
-                    const uint32_t *__restrict__ hs_start, const uint32_t *__restrict__ tmpl,
-                    const uint8_t *__restrict__ head, uint32_t n_fam, uint32_t n_reads,
-                    uint32_t *__restrict__ fam_start, uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
+creation_rank_kernel(const uint32_t *__restrict__ first_read, const uint32_t *__restrict__ bitmap,
+                     const uint32_t *__restrict__ word_rank, uint32_t n_fam, uint32_t *__restrict__ c2hs)
+{
+    uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= n_fam) return;
+    uint32_t first = first_read[f];
+    uint32_t c = word_rank[first >> 5] + __popc(bitmap[first >> 5] & ((1u << (first & 31)) - 1u));
+    c2hs[c] = f;
+}
+
+// family c in creation order: segment of perm, size, template, singleton fields,
+// "mode fields differ" flag, size histogram
+__global__ void __launch_bounds__(256)
+family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ hs_start,
+                    const uint32_t *__restrict__ first_read, const uint32_t *__restrict__ c2hs,
+                    const uint8_t *__restrict__ head, uint32_t n_fam,
+                    uint32_t n_reads, uint32_t *__restrict__ tmpl, uint32_t *__restrict__ fam_start,
+                    uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
                     uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag,
                     int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
                     unsigned long long *__restrict__ hist, uint32_t hist_bins)
@@ -173,21 +196,23 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < n_fam) {
         uint32_t f = c2hs[c];
+        uint32_t first = first_read[f];
         uint32_t s = hs_start[f];
         uint32_t e = (f + 1 < n_fam) ? hs_start[f + 1] : n_reads;
         uint32_t size = e - s;
         uint32_t mixed = 0;                           // do the members' mode fields differ anywhere?
         for (uint32_t j = s + 1; j < e; j++) mixed |= head[j];
+        tmpl[c] = first;
         fam_start[c] = s;
         fam_size[c] = size;
         is_sscs[c] = size >= 2 ? ((mixed & 2) ? 3 : 1) : 0;   // bit 0: has a consensus row, bit 1: mode fields differ
-        // a singleton keeps its own fields (SSCS_maker.py:278-282); larger families are
-        // overwritten by the vote kernel's mode fields
-        Rec r = load_rec(fields, tmpl[c]);
-        fam_tlen[c] = (int32_t)r.b.z;
-        fam_flag[c] = (uint16_t)(r.b.w & 0xFFFF);
-        fam_mapq[c] = (uint8_t)((r.b.w >> 16) & 0xFF);
-        fam_rg[c] = (uint8_t)(r.b.w >> 24);
+        // a singleton keeps its own fields (SSCS_maker.py:278-282); larger families with differing
+        // fields are overwritten by the vote kernel's mode fields
+        uint4 b = __ldg(&fields[2 * (uint64_t)first + 1]);
+        fam_tlen[c] = (int32_t)b.z;
+        fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
+        fam_mapq[c] = (uint8_t)((b.w >> 16) & 0xFF);
+        fam_rg[c] = (uint8_t)(b.w >> 24);
         uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
         if (bin < 256) atomicAdd(&small_hist[bin], 1u);
         else atomicAdd(&hist[bin], 1ull);

@@ -3,7 +3,7 @@
 // Three flavours share one kernel body:
 //   exclusive scan of u32 values                       -> out[i]
 //   compaction of the indices whose flag has bit 0 set -> list[rank] = i
-//   compaction that also carries the flag value        -> list[rank] = i, carry[rank] = flag - 1
+//   exclusive scan of the popcounts of u32 words       -> out[i]  (ranks inside a bitmap)
 // Tiles take their number from an atomic ticket so that a tile only ever waits
 // on tiles that have already started.
 #pragma once
@@ -34,9 +34,9 @@ __device__ __forceinline__ void st_status(unsigned long long *p, unsigned long l
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-enum { SCAN_MODE_EXCL = 0, SCAN_MODE_COMPACT = 1, SCAN_MODE_COMPACT_CARRY = 2 };
+enum { SCAN_MODE_EXCL = 0, SCAN_MODE_COMPACT = 1, SCAN_MODE_POPC = 2 };   // POPC: exclusive scan of popcounts
 
-// In: u32 values (MODE_EXCL), u8 flags (MODE_COMPACT) or u32 marks (MODE_COMPACT_CARRY).
+// In: u32 values (MODE_EXCL), u8 flags (MODE_COMPACT) or u32 bitmap words (MODE_POPC).
 template <int MODE, typename InT>
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
@@ -57,7 +57,7 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
         v[i] = (base + i < n) ? in[base + i] : (InT)0;
-        w[i] = (MODE == SCAN_MODE_EXCL) ? (uint32_t)v[i] : (MODE == SCAN_MODE_COMPACT ? ((uint32_t)v[i] & 1u) : (v[i] != 0 ? 1u : 0u));
+        w[i] = (MODE == SCAN_MODE_EXCL) ? (uint32_t)v[i] : (MODE == SCAN_MODE_COMPACT ? ((uint32_t)v[i] & 1u) : (uint32_t)__popc((uint32_t)v[i]));
         sum += w[i];
     }
     // block-wide exclusive prefix of the per-thread sums
@@ -99,11 +99,10 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
         if (base + i < n) {
-            if (MODE == SCAN_MODE_EXCL) {
+            if (MODE != SCAN_MODE_COMPACT) {
                 out[base + i] = run;
             } else if (w[i]) {
                 out[run] = (uint32_t)(base + i);
-                if (MODE == SCAN_MODE_COMPACT_CARRY) carry[run] = (uint32_t)v[i] - 1u;
             }
         }
         run += w[i];
