@@ -9,7 +9,7 @@
 #include <vector>
 
 #include "kernels.cuh"
-#include "radix.cuh"
+#include "radix_onesweep.cuh"
 #include "scan.cuh"
 #include "vote.cuh"
 
@@ -257,8 +257,8 @@ int do_group(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
     TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
     TRY(ensure(ctx, ctx->head, n));
-    const uint32_t ntiles = (uint32_t)radix_tiles(n);
-    TRY(ensure(ctx, ctx->radix_counts, (size_t)ntiles * RADIX_BINS * 4));
+    const uint32_t ntiles = (uint32_t)os_tiles(n);
+    TRY(ensure(ctx, ctx->radix_counts, ((size_t)ntiles * OS_BINS + OS_MAX_PASSES * OS_BINS + 64) * 4));
 
     const int bits = sort_bits_for(n);
     const uint32_t key_mask = bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
@@ -267,22 +267,24 @@ int do_group(cc_ctx *ctx)
     TRY(phase_end(ctx, CC_PH_HASH));
 
     TRY(phase_begin(ctx, CC_PH_SORT));
+    const int passes = bits / 8;
+    uint32_t *ghist = ptr<uint32_t>(ctx->radix_counts);                 // [passes][256] digit totals, then bases
+    uint32_t *tickets = ghist + OS_MAX_PASSES * OS_BINS;                // one tile ticket per pass
+    uint32_t *status = tickets + 64;                                    // [tiles][256] look-back words
+    CK(cudaMemsetAsync(ghist, 0, (OS_MAX_PASSES * OS_BINS + 64) * sizeof(uint32_t), ctx->stream));
+    LAUNCH(os_histogram_kernel, 148 * 4, 256, ptr<uint32_t>(ctx->key_a), n, passes, ghist);
+    LAUNCH(os_scan_hist_kernel, 1, 32 * OS_MAX_PASSES, ghist, passes);
     uint32_t *kin = ptr<uint32_t>(ctx->key_a), *kout = ptr<uint32_t>(ctx->key_b);
     uint32_t *vin = nullptr, *vout = ptr<uint32_t>(ctx->val_a), *vother = ptr<uint32_t>(ctx->val_b);
-    uint32_t *counts = ptr<uint32_t>(ctx->radix_counts);
-    for (int shift = 0; shift < bits; shift += 8) {
-        LAUNCH(radix_hist_kernel, ntiles, RADIX_THREADS, kin, n, shift, ntiles, counts);
-        ctx->next_ticket = 0;   // scans inside the sort reuse ticket 0 (zeroed below)
-        CK(cudaMemsetAsync(ptr<uint32_t>(ctx->counters) + CT_TICKET0, 0, sizeof(uint32_t), ctx->stream));
-        TRY(scan_exclusive(ctx, counts, counts, (uint64_t)ntiles * RADIX_BINS));
-        LAUNCH(radix_scatter_kernel, ntiles, RADIX_THREADS, kin, vin, kout, vout, n, shift, ntiles, counts);
+    for (int pass = 0; pass < passes; pass++) {
+        CK(cudaMemsetAsync(status, 0, (size_t)ntiles * OS_BINS * sizeof(uint32_t), ctx->stream));
+        LAUNCH(os_pass_kernel, ntiles, OS_THREADS, kin, vin, kout, vout, n, 8 * pass, ghist + pass * OS_BINS, status,
+               tickets + pass);
         uint32_t *t = kin; kin = kout; kout = t;
         vin = vout; vout = vother; vother = vin;
     }
     ctx->sorted_keys = kin; ctx->spare_keys = kout;
     ctx->perm = vin; ctx->spare_vals = vout;
-    ctx->next_ticket = 0;
-    CK(cudaMemsetAsync(ptr<uint32_t>(ctx->counters) + CT_TICKET0, 0, sizeof(uint32_t), ctx->stream));
     TRY(phase_end(ctx, CC_PH_SORT));
 
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
@@ -533,7 +535,7 @@ int check_geometry(cc_ctx *ctx, const void *fields, const void *payload, uint64_
     if (n && (!fields || !payload)) return fail(ctx, CC_ERR_ARG, "NULL fields/payload");
     if (lpad == 0 || lpad % 32 || stride % 64 || stride < lpad / 2 + lpad)
         return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride % 64 == 0, stride >= 3*lpad/2");
-    if (n >= (1ull << 31)) return fail(ctx, CC_ERR_TOO_LARGE, "a batch holds at most 2^31-1 reads");
+    if (n >= (1ull << 30)) return fail(ctx, CC_ERR_TOO_LARGE, "a batch holds at most 2^30-1 reads");
     if (n & 1) return fail(ctx, CC_ERR_ARG, "reads come in pairs (2k, 2k+1)");
     return CC_OK;
 }
