@@ -12,8 +12,14 @@
 namespace ccgpu {
 
 constexpr int OS_THREADS = 256;
-constexpr int OS_ITEMS = 16;
-constexpr int OS_TILE = OS_THREADS * OS_ITEMS;      // 4096 keys per CTA
+#ifndef OS_ITEMS_CFG
+#define OS_ITEMS_CFG 16
+#endif
+#ifndef OS_BLOCKS_CFG
+#define OS_BLOCKS_CFG 3
+#endif
+constexpr int OS_ITEMS = OS_ITEMS_CFG;
+constexpr int OS_TILE = OS_THREADS * OS_ITEMS;      // keys per CTA
 constexpr int OS_WARPS = OS_THREADS / 32;
 constexpr int OS_BINS = 256;
 constexpr int OS_MAX_PASSES = 4;
@@ -72,7 +78,7 @@ __device__ __forceinline__ void os_st(uint32_t *p, uint32_t v)
 
 // status[tile][digit]: top 2 bits = 0 empty, 1 tile count, 2 inclusive prefix; low 30 bits = value
 // vals_in == nullptr means "value = position" (first pass over the hashed keys)
-__global__ void __launch_bounds__(OS_THREADS)
+__global__ void __launch_bounds__(OS_THREADS, OS_BLOCKS_CFG)
 os_pass_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, int shift,
                const uint32_t *__restrict__ digit_base, uint32_t *__restrict__ status, uint32_t *__restrict__ ticket)
