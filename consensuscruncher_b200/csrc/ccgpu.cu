@@ -63,6 +63,7 @@ struct cc_ctx {
     DevBuf dcs_mapq, dcs_flag, dcs_tlen, dcs_rg;
     DevBuf vstart, vsize, big_list, thr_table;
     uint8_t thr_host[128];
+    ThrMagic thr_magic{0, 0, 1};
     bool thr_valid = false;
     DevBuf tmp_a, tmp_b, tmp_c;   // stand-alone primitives
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
@@ -411,6 +412,14 @@ int upload_thresholds(cc_ctx *ctx)
         ctx->thr_host[p] = (uint8_t)t;
     }
     CK(cudaMemcpyAsync(ctx->thr_table.p, ctx->thr_host, 128, cudaMemcpyHostToDevice, ctx->stream));
+    // closed form of the table for the sizes vote_small_kernel handles: thr[p] == (p*k + r) >> 8
+    ctx->thr_magic = ThrMagic{0, 0, 1};
+    for (uint32_t k = 0; k <= 512 && ctx->thr_magic.use_table; k++)
+        for (uint32_t r = 0; r < 256; r++) {
+            bool ok = true;
+            for (uint32_t p2 = 1; p2 <= VOTE_SMALL_MAX && ok; p2++) ok = ((p2 * k + r) >> 8) == ctx->thr_host[p2];
+            if (ok) { ctx->thr_magic = ThrMagic{k, r | (r << 16), 0}; break; }
+        }
     ctx->thr_valid = true;
     return CC_OK;
 }
@@ -426,7 +435,7 @@ int launch_vote_small(cc_ctx *ctx, uint32_t rows)
     }
     kernel<<<blocks_for(rows, VOTE_CHUNK), 256, VOTE_RING_BYTES, ctx->stream>>>( ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
            ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list), rows,
-           ptr<uint8_t>(ctx->thr_table), (1.0 >= ctx->params.cutoff) ? 1 : 0, ptr<uint8_t>(ctx->sscs_rows),
+           ptr<uint8_t>(ctx->thr_table), (1.0 >= ctx->params.cutoff) ? 1 : 0, ctx->thr_magic, ptr<uint8_t>(ctx->sscs_rows),
            ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
            ptr<uint8_t>(ctx->fam_rg), ptr<uint32_t>(ctx->counters) + CT_ERR);
     ctx->launches++;

@@ -28,7 +28,7 @@
 
 namespace ccgpu {
 
-constexpr uint32_t VOTE_SMALL_MAX = 31;      // T counts are kept times 8 in a byte lane
+constexpr uint32_t VOTE_SMALL_MAX = 127;     // byte-lane compares below need counts < 128
 constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows per staged batch
 constexpr int VOTE_DEPTH = VOTE_DEPTH_CFG;                // ring slots per lane: VOTE_DEPTH - 1 batches in flight
 constexpr int VOTE_RING_BYTES = VOTE_DEPTH * VOTE_ROWS_PER_BATCH * 256 * 24;   // dynamic shared memory per block
@@ -43,6 +43,16 @@ __device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
 {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem)
                  : "memory");
+}
+
+__device__ __forceinline__ void cp_async_16_sh(uint32_t smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem), "l"(gmem) : "memory");
+}
+
+__device__ __forceinline__ void cp_async_8_sh(uint32_t smem, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem), "l"(gmem) : "memory");
 }
 
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
@@ -75,22 +85,53 @@ __device__ __forceinline__ uint32_t sel(uint32_t a, uint32_t b, uint32_t mask) {
 // into an add, so it issues on the FMA pipe instead of the (saturated) ALU pipe.
 __device__ __forceinline__ uint32_t fadd(uint32_t x, uint32_t y, uint32_t one) { return x * one + y; }
 
-struct Quad {            // accumulators of 4 positions (one byte lane each)
-    uint32_t cA, cC, cG, cT, pc;     // cC, cG, cT hold 2x, 4x, 8x the count (no shifts in the row loop)
-    uint32_t qany;                   // OR of the passing qualities: the supporter's quality when one read passes
+__device__ __forceinline__ uint32_t prmt(uint32_t lo, uint32_t hi, uint32_t selector)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(selector));
+    return r;
+}
+
+// A quad is 4 consecutive positions = 2 sequence bytes = one 16-bit group of 4 base codes.  That
+// group is used directly as a PRMT selector, so a quad's byte lanes are in nibble order:
+// lane 0 <-> position 1, lane 1 <-> position 0, lane 2 <-> position 3, lane 3 <-> position 2.
+struct Quad {
+    uint32_t ac;        // per byte lane: count of A in the low nibble, of C in the high nibble
+    uint32_t gt;        // per byte lane: count of G plus T in the low nibble, of T in the high nibble
+    uint32_t pc;        // number of passing reads
+    uint32_t qany;      // OR of the passing qualities: the supporter's quality when one read passes
+    uint32_t tA, tC, tG, tT;   // counts flushed out of the nibbles (families of more than 15 reads)
 };
 
-__device__ __forceinline__ void quad_add(Quad &a, uint32_t nib, uint32_t q, uint32_t &err, uint32_t one)
+// One read, 4 positions.  The base codes select their increments from two byte tables:
+//   A (1) -> ac += 0x01, C (2) -> ac += 0x10, G (4) -> gt += 0x01, T (8) -> gt += 0x11
+// (T reaches the table through PRMT's sign-replicate mode: entry 0 of the G/T table has its
+// top bit set, so selector 8 yields 0xFF, masked to 0x11).  Every other code, N and IUPAC
+// included, selects 0: it is counted in pc but in no base, which quad_finish reports.
+__device__ __forceinline__ void quad_add(Quad &a, uint32_t sel16, uint32_t q, uint32_t one)
 {
     uint32_t m = bytes_of(fadd(q & 0x7F7F7F7Fu, 0x62626262u, one) | q);    // 0xFF where q >= 30
-    uint32_t b = nib & m;
-    err |= fadd(b | 0x80808080u, 0xFEFEFEFFu, one) & b;  // (b | 0x80..) - 0x01..: more than one bit set in a passing base
-    a.cA = fadd(b & 0x01010101u, a.cA, one);
-    a.cC = fadd(b & 0x02020202u, a.cC, one);
-    a.cG = fadd(b & 0x04040404u, a.cG, one);
-    a.cT = fadd(b & 0x08080808u, a.cT, one);
+    a.ac = fadd(prmt(0x00100100u, 0u, sel16) & m, a.ac, one);
+    a.gt = fadd(prmt(0x00000080u, 0x00000001u, sel16) & m & 0x11111111u, a.gt, one);
     a.pc = fadd(m & 0x01010101u, a.pc, one);
     a.qany |= q & m;
+}
+
+// every 12 reads the nibble counters are emptied into byte counters
+__device__ __forceinline__ void quad_flush(Quad &a)
+{
+    uint32_t t = (a.gt >> 4) & 0x0F0F0F0Fu;
+    a.tA += a.ac & 0x0F0F0F0Fu;
+    a.tC += (a.ac >> 4) & 0x0F0F0F0Fu;
+    a.tT += t;
+    a.tG += (a.gt & 0x0F0F0F0Fu) - t;
+    a.ac = 0; a.gt = 0;
+}
+
+// 4 base codes of a 16-bit group, one per byte lane (nibble order)
+__device__ __forceinline__ uint32_t expand_sel(uint32_t sel16)
+{
+    return __byte_perm(sel16 & 0x0F0Fu, (sel16 >> 4) & 0x0F0Fu, 0x5140);
 }
 
 __device__ __forceinline__ uint32_t cap60(uint32_t q)
@@ -109,11 +150,18 @@ struct QuadOut {
 
 // Winner, cutoff decision and quality of 4 positions.  thr[p] = smallest count c with
 // (double)c / (double)p >= cutoff, built on the host with the same IEEE division Python does.
-__device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr, bool unanimous_ok, uint32_t &err)
+struct ThrMagic {       // thr[p] == (p * k + r) >> 8 for every p the kernel can meet (found on the host), or use_table
+    uint32_t k, r2;      // r2 = r | r << 16
+    int use_table;
+};
+
+__device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr, bool unanimous_ok, ThrMagic tm,
+                                               uint32_t &err)
 {
     QuadOut o;
-    const uint32_t cA = a.cA, cC = (a.cC >> 1) & 0x7F7F7F7Fu, cG = (a.cG >> 2) & 0x3F3F3F3Fu,
-                   cT = (a.cT >> 3) & 0x1F1F1F1Fu;
+    const uint32_t tnow = (a.gt >> 4) & 0x0F0F0F0Fu;
+    const uint32_t cA = a.tA + (a.ac & 0x0F0F0F0Fu), cC = a.tC + ((a.ac >> 4) & 0x0F0F0F0Fu),
+                   cT = a.tT + tnow, cG = a.tG + (a.gt & 0x0F0F0F0Fu) - tnow;
     uint32_t m1 = bytes_of(ge7(cA, cC));                  // ties keep the earlier base: A,C,G,T order
     uint32_t m2 = bytes_of(ge7(cG, cT));
     uint32_t bAC = sel(cA, cC, m1), wAC = sel(0x01010101u, 0x02020202u, m1);
@@ -122,16 +170,24 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
     uint32_t best = sel(bAC, bGT, m3);
     o.win = sel(wAC, wGT, m3);
     uint32_t sum = cA + cC + cG + cT;
-    err |= sum ^ a.pc;                                     // a passing base that is none of A,C,G,T
+    err |= sum ^ a.pc;                                     // a passing base that is none of A,C,G,T (N, IUPAC, '=')
     uint32_t pass = a.pc;
-    uint32_t split = nz7(best ^ pass);                     // not unanimous
-    uint32_t ok = bytes_of(nz7(best)) & ~bytes_of(split);  // unanimous and at least one passing read
-    if (!unanimous_ok) ok = 0;
-    while (split) {                                        // rare: look the threshold up per position
-        int k = (__ffs(split) - 1) >> 3;
-        uint32_t c = (best >> (8 * k)) & 0xFFu, p = (pass >> (8 * k)) & 0xFFu;
-        if (c >= thr[p]) ok |= 0xFFu << (8 * k);
-        split &= ~(0x80u << (8 * k));
+    uint32_t ok;
+    if (!tm.use_table) {
+        // threshold of every position at once: two 16-bit lanes per multiply, no table, no divergence
+        uint32_t te = (((pass & 0x00FF00FFu) * tm.k + tm.r2) >> 8) & 0x00FF00FFu;
+        uint32_t to = (((pass >> 8) & 0x00FF00FFu) * tm.k + tm.r2) & 0xFF00FF00u;
+        ok = bytes_of(ge7(best, te | to)) & bytes_of(nz7(best));
+    } else {
+        uint32_t split = nz7(best ^ pass);                 // not unanimous
+        ok = bytes_of(nz7(best)) & ~bytes_of(split);       // unanimous and at least one passing read
+        if (!unanimous_ok) ok = 0;
+        while (split) {                                    // look the threshold up per position
+            int k = (__ffs(split) - 1) >> 3;
+            uint32_t c = (best >> (8 * k)) & 0xFFu, p = (pass >> (8 * k)) & 0xFFu;
+            if (c >= thr[p]) ok |= 0xFFu << (8 * k);
+            split &= ~(0x80u << (8 * k));
+        }
     }
     o.code = sel(o.win, 0x0F0F0F0Fu, ok);
     uint32_t two = bytes_of(ge7(best, 0x02020202u));
@@ -165,13 +221,23 @@ __device__ __forceinline__ LaneRow load_lane_row(const uint8_t *__restrict__ pay
     return r;
 }
 
-// quads of a lane: (even positions of word 0, odd of word 0, even of word 1, odd of word 1)
-__device__ __forceinline__ void split_row(const LaneRow &r, uint32_t nib[4], uint32_t q[4])
+// quads of a lane: positions 0-3, 4-7, 8-11, 12-15, each in nibble order (see Quad)
+__device__ __forceinline__ void split_row(const LaneRow &r, uint32_t sel[4], uint32_t q[4])
 {
-    nib[0] = (r.s.x >> 4) & 0x0F0F0F0Fu; nib[1] = r.s.x & 0x0F0F0F0Fu;
-    nib[2] = (r.s.y >> 4) & 0x0F0F0F0Fu; nib[3] = r.s.y & 0x0F0F0F0Fu;
-    q[0] = __byte_perm(r.q.x, r.q.y, 0x6420); q[1] = __byte_perm(r.q.x, r.q.y, 0x7531);
-    q[2] = __byte_perm(r.q.z, r.q.w, 0x6420); q[3] = __byte_perm(r.q.z, r.q.w, 0x7531);
+    sel[0] = r.s.x; sel[1] = r.s.x >> 16; sel[2] = r.s.y; sel[3] = r.s.y >> 16;     // PRMT reads the low 16 bits
+    q[0] = __byte_perm(r.q.x, 0, 0x2301); q[1] = __byte_perm(r.q.y, 0, 0x2301);
+    q[2] = __byte_perm(r.q.z, 0, 0x2301); q[3] = __byte_perm(r.q.w, 0, 0x2301);
+}
+
+// consensus codes / qualities of the 4 quads -> the lane's 8 sequence bytes and 16 quality bytes
+__device__ __forceinline__ void join_row(const uint32_t code[4], const uint32_t qual[4], uint2 &so, uint4 &qo)
+{
+    uint32_t x0 = code[0] | (code[0] >> 4), x1 = code[1] | (code[1] >> 4);
+    uint32_t x2 = code[2] | (code[2] >> 4), x3 = code[3] | (code[3] >> 4);
+    so.x = __byte_perm(x0, x1, 0x6420);
+    so.y = __byte_perm(x2, x3, 0x6420);
+    qo.x = __byte_perm(qual[0], 0, 0x2301); qo.y = __byte_perm(qual[1], 0, 0x2301);
+    qo.z = __byte_perm(qual[2], 0, 0x2301); qo.w = __byte_perm(qual[3], 0, 0x2301);
 }
 
 // mode of one field over a family held by a lane group (slow path: fields differ inside the family)
@@ -231,7 +297,7 @@ __global__ void __launch_bounds__(256, VOTE_BLOCKS_CFG)
 vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
                   uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
                   const uint32_t *__restrict__ vsize, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
-                  const uint8_t *__restrict__ thr_table, int unanimous_ok, uint8_t *__restrict__ out_rows,
+                  const uint8_t *__restrict__ thr_table, int unanimous_ok, ThrMagic tm, uint8_t *__restrict__ out_rows,
                   uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen,
                   uint8_t *__restrict__ fam_rg, uint32_t *__restrict__ err_flag)
 {
@@ -292,13 +358,17 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
     // keeps VOTE_DEPTH - 1 batches in flight while it votes the oldest one.  Bytes in flight
     // no longer occupy registers, which is what bounds the achieved HBM bandwidth here.
     extern __shared__ __align__(16) uint8_t ring[];
-    uint4 *ring_q = reinterpret_cast<uint4 *>(ring);                                        // [depth][row][thread]
-    uint2 *ring_s = reinterpret_cast<uint2 *>(ring + VOTE_DEPTH * VOTE_ROWS_PER_BATCH * 256 * 16);
-    auto slot_q = [&](uint32_t batch, int k) { return &ring_q[((batch % VOTE_DEPTH) * VOTE_ROWS_PER_BATCH + k) * 256 + tid]; };
-    auto slot_s = [&](uint32_t batch, int k) { return &ring_s[((batch % VOTE_DEPTH) * VOTE_ROWS_PER_BATCH + k) * 256 + tid]; };
+    constexpr uint32_t ROW_Q = 256 * 16, ROW_S = 256 * 8;                       // bytes between rows of a slot
+    constexpr uint32_t SLOT_Q = VOTE_ROWS_PER_BATCH * ROW_Q, SLOT_S = VOTE_ROWS_PER_BATCH * ROW_S;
+    uint8_t *const ring_q = ring + tid * 16;                                     // [depth][row][thread] uint4
+    uint8_t *const ring_s = ring + VOTE_DEPTH * SLOT_Q + tid * 8;                // [depth][row][thread] uint2
+    const uint32_t ring_q_sh = (uint32_t)__cvta_generic_to_shared(ring_q);
+    const uint32_t ring_s_sh = (uint32_t)__cvta_generic_to_shared(ring_s);
+    const uint8_t *const lane_src = payload + (pos0 >> 1);                       // this lane's 8 sequence bytes of read 0
+    const uint32_t q_off = half + pos0 - (pos0 >> 1);                            // ... and from there to its 16 qualities
 
     // producer cursor: the batch that will be issued next
-    uint32_t p_t = my_slot, p_start = 0, p_n = 0, p_j0 = 0, p_batch = 0;
+    uint32_t p_t = my_slot, p_start = 0, p_n = 0, p_j0 = 0, p_slot = 0;
     uint32_t p_idx[VOTE_ROWS_PER_BATCH];
     auto p_load_family = [&]() {
         p_start = 0; p_n = 0; p_j0 = 0;
@@ -318,14 +388,14 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
 #pragma unroll
             for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
                 if (p_j0 + k < p_n) {
-                    const uint8_t *src = payload + (uint64_t)p_idx[k] * stride;
-                    cp_async_8(slot_s(p_batch, k), src + (pos0 >> 1));
-                    cp_async_16(slot_q(p_batch, k), src + half + pos0);
+                    const uint8_t *src = lane_src + (uint64_t)p_idx[k] * stride;
+                    cp_async_8_sh(ring_s_sh + p_slot * SLOT_S + k * ROW_S, src);
+                    cp_async_16_sh(ring_q_sh + p_slot * SLOT_Q + k * ROW_Q, src + q_off);
                 }
             }
         }
         cp_async_commit();
-        p_batch++;
+        p_slot = p_slot + 1 == VOTE_DEPTH ? 0 : p_slot + 1;
         p_j0 += VOTE_ROWS_PER_BATCH;
         if (p_j0 >= p_n) { p_t += BLOCK_GROUPS; p_load_family(); }
         p_load_idx();
@@ -335,7 +405,10 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
 #pragma unroll 1
     for (int d = 0; d < VOTE_DEPTH - 1; d++) p_issue();
 
-    uint32_t c_batch = 0;                                  // consumer: oldest batch still in the ring
+    uint32_t c_slot = 0;                                   // consumer: slot of the oldest batch still in the ring
+    auto slot_q = [&](uint32_t slot, int k) { return reinterpret_cast<const uint4 *>(ring_q + slot * SLOT_Q + k * ROW_Q); };
+    auto slot_s = [&](uint32_t slot, int k) { return reinterpret_cast<const uint2 *>(ring_s + slot * SLOT_S + k * ROW_S); };
+    auto next_slot = [&](uint32_t slot) { return slot + 1 == VOTE_DEPTH ? 0u : slot + 1; };
     for (uint32_t t0 = 0; t0 < todo; t0 += BLOCK_GROUPS) {
         const uint32_t t = t0 + my_slot;
         uint32_t start = 0, n = 0, row = 0;
@@ -355,19 +428,20 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
                 p_issue();
                 cp_async_wait<VOTE_DEPTH - 1>();
                 if (lane_on) {
-                    LaneRow r1{*slot_s(c_batch, 0), *slot_q(c_batch, 0)}, r2{*slot_s(c_batch, 1), *slot_q(c_batch, 1)};
+                    LaneRow r1{*slot_s(c_slot, 0), *slot_q(c_slot, 0)}, r2{*slot_s(c_slot, 1), *slot_q(c_slot, 1)};
                     uint32_t n1[4], q1[4], n2[4], q2[4];
                     split_row(r1, n1, q1);
                     split_row(r2, n2, q2);
 #pragma unroll
-                    for (int g = 0; g < 4; g++) quad_pair(n1[g], q1[g], n2[g], q2[g], tie_ok, unanimous_ok != 0, code[g], qual[g], err);
+                    for (int g = 0; g < 4; g++)
+                        quad_pair(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], tie_ok, unanimous_ok != 0, code[g], qual[g], err);
                 }
-                c_batch++;
+                c_slot = next_slot(c_slot);
             } else {
                 Quad acc[4];
 #pragma unroll
-                for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0, 0};
-                const uint32_t first_batch = c_batch;
+                for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0, 0, 0, 0};
+                const uint32_t first_slot = c_slot;
                 for (uint32_t j0 = 0; j0 < n; j0 += VOTE_ROWS_PER_BATCH) {
                     p_issue();
                     cp_async_wait<VOTE_DEPTH - 1>();
@@ -375,22 +449,26 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
 #pragma unroll
                         for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
                             if (j0 + k < n) {
-                                LaneRow r{*slot_s(c_batch, k), *slot_q(c_batch, k)};
+                                LaneRow r{*slot_s(c_slot, k), *slot_q(c_slot, k)};
                                 uint32_t nib[4], q[4];
                                 split_row(r, nib, q);
 #pragma unroll
-                                for (int g = 0; g < 4; g++) quad_add(acc[g], nib[g], q[g], err, one);
+                                for (int g = 0; g < 4; g++) quad_add(acc[g], nib[g], q[g], one);
                             }
                         }
                     }
-                    c_batch++;
+                    c_slot = next_slot(c_slot);
+                    if ((j0 + VOTE_ROWS_PER_BATCH) % 12 == 0 && j0 + VOTE_ROWS_PER_BATCH < n) {
+#pragma unroll
+                        for (int g = 0; g < 4; g++) quad_flush(acc[g]);
+                    }
                 }
                 if (lane_on) {
                     QuadOut o[4];
                     uint32_t any_single = 0;
 #pragma unroll
                     for (int g = 0; g < 4; g++) {
-                        o[g] = quad_finish(acc[g], thr, unanimous_ok != 0, err);
+                        o[g] = quad_finish(acc[g], thr, unanimous_ok != 0, tm, err);
                         any_single |= o[g].single;
                     }
 #ifdef VOTE_EXP_NO_PICK
@@ -403,12 +481,12 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
                         const bool in_ring = n <= VOTE_ROWS_PER_BATCH;
                         for (uint32_t j = 0; j < n; j++) {
                             LaneRow rr;
-                            if (in_ring) { rr.s = *slot_s(first_batch, j); rr.q = *slot_q(first_batch, j); }
+                            if (in_ring) { rr.s = *slot_s(first_slot, j); rr.q = *slot_q(first_slot, j); }
                             else rr = load_lane_row(payload, stride, half, __ldg(&perm[start + j]), pos0);
                             uint32_t nib[4], q[4];
                             split_row(rr, nib, q);
 #pragma unroll
-                            for (int g = 0; g < 4; g++) pick[g] |= quad_pick(nib[g], q[g], o[g].win, o[g].single);
+                            for (int g = 0; g < 4; g++) pick[g] |= quad_pick(expand_sel(nib[g]), q[g], o[g].win, o[g].single);
                         }
 #pragma unroll
                         for (int g = 0; g < 4; g++) o[g].qual |= cap60(pick[g]) & o[g].single;
@@ -420,10 +498,7 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
             if (lane_on) {
                 uint2 so;
                 uint4 qo;
-                so.x = (code[0] << 4) | code[1];
-                so.y = (code[2] << 4) | code[3];
-                qo.x = __byte_perm(qual[0], qual[1], 0x5140); qo.y = __byte_perm(qual[0], qual[1], 0x7362);
-                qo.z = __byte_perm(qual[2], qual[3], 0x5140); qo.w = __byte_perm(qual[2], qual[3], 0x7362);
+                join_row(code, qual, so, qo);
                 *reinterpret_cast<uint2 *>(out + (pos0 >> 1)) = so;
                 *reinterpret_cast<uint4 *>(out + half + pos0) = qo;
             }
@@ -524,13 +599,10 @@ __device__ __forceinline__ void agree_lane(const uint8_t *__restrict__ r1, const
         split_row(a, n1, q1);
         split_row(b, n2, q2);
 #pragma unroll
-        for (int g = 0; g < 4; g++) quad_agree<SC>(n1[g], q1[g], n2[g], q2[g], code[g], qual[g]);
+        for (int g = 0; g < 4; g++) quad_agree<SC>(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], code[g], qual[g]);
         uint2 so;
         uint4 qo;
-        so.x = (code[0] << 4) | code[1];
-        so.y = (code[2] << 4) | code[3];
-        qo.x = __byte_perm(qual[0], qual[1], 0x5140); qo.y = __byte_perm(qual[0], qual[1], 0x7362);
-        qo.z = __byte_perm(qual[2], qual[3], 0x5140); qo.w = __byte_perm(qual[2], qual[3], 0x7362);
+        join_row(code, qual, so, qo);
         *reinterpret_cast<uint2 *>(out + (pos0 >> 1)) = so;
         *reinterpret_cast<uint4 *>(out + half + pos0) = qo;
     }
