@@ -42,7 +42,7 @@ CPU_SAMPLE_PAIRS = 2_000_000
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="read pairs per GPU")
@@ -72,7 +72,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
@@ -249,49 +249,78 @@ def main():
         h_dup = torch.empty(batch.dup_bc.shape, dtype=batch.dup_bc.dtype, pin_memory=True)
         h_fields.copy_(batch.fields); h_payload.copy_(batch.payload); h_dup.copy_(batch.dup_bc)
         torch.cuda.synchronize(dev)
+        # every result array a caller needs to write the output files; the DCS rows / fields are the
+        # first n_dcs entries of the DCS-after-rescue arrays, so they are not fetched twice
         out_names = ("fam_size", "fam_tmpl", "fam_mapq", "fam_flag", "fam_tlen", "fam_rg", "partner",
-                     "sscs_row", "corr_row", "dcs_row", "dcssc_row", "sscs_rows", "corr_rows", "dcs_rows",
-                     "dcssc_rows", "dcs_mapq", "dcs_flag", "dcs_tlen", "dcs_rg", "dcssc_mapq", "dcssc_flag",
-                     "dcssc_tlen", "dcssc_rg", "stats", "fam_hist")
+                     "sscs_row", "corr_row", "dcs_row", "dcssc_row", "sscs_rows", "corr_rows",
+                     "dcssc_rows", "dcssc_mapq", "dcssc_flag", "dcssc_tlen", "dcssc_rg", "stats", "fam_hist")
         from consensuscruncher_b200.engine import ARRAYS
-        h_out = {}
+        from concurrent.futures import ThreadPoolExecutor
+        # Two contexts alternate (double buffering): while one batch's results travel back to the
+        # host, the next batch is already being uploaded, so both PCIe directions stay busy.
+        # Each context works on its own stream; each step is still one cc_run_host call plus
+        # the read-back of every result array.
+        engines = [eng, GpuConsensus(local, cutoff=CUTOFF, scorrect=True)]
+        eng.set_stream(0)
+        h_outs = [{}, {}]
+        turn = {"next": 0}
+        turn_cv = threading.Condition()
 
-        def e2e_step():
-            eng._check(eng.lib.cc_run_host(eng.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
-                                           batch.stride, h_dup.data_ptr(), batch.n_bc))
-            reduce_stats()
+        def e2e_step(which, step_no):
+            e = engines[which]
+            e._check(e.lib.cc_run_host(e.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
+                                       batch.stride, h_dup.data_ptr(), batch.n_bc))
+            if world > 1:                      # the collective is issued in step order on every rank
+                with turn_cv:
+                    turn_cv.wait_for(lambda: turn["next"] == step_no)
+                    from consensuscruncher_b200.shard import device_tensor
+                    for name, dt, count in (("stats", torch.int64, 16), ("fam_hist", torch.int64, 65536)):
+                        dist.all_reduce(device_tensor(e.device_ptr(name), count, dt, local))
+                    torch.cuda.current_stream(dev).synchronize()
+                    turn["next"] = step_no + 1
+                    turn_cv.notify_all()
             total = 0
             for nm in out_names:
                 what = ARRAYS[nm][0]
-                nbytes = eng.lib.cc_array_bytes(eng.ctx, what)
+                nbytes = e.lib.cc_array_bytes(e.ctx, what)
                 if nbytes == 0:
                     continue
-                buf = h_out.get(nm)
+                buf = h_outs[which].get(nm)
                 if buf is None or buf.numel() < nbytes:
-                    buf = h_out[nm] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8, pin_memory=True)
-                eng._check(eng.lib.cc_fetch(eng.ctx, what, buf.data_ptr(), nbytes))
+                    buf = h_outs[which][nm] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8, pin_memory=True)
+                e._check(e.lib.cc_fetch(e.ctx, what, buf.data_ptr(), nbytes))
                 total += nbytes
             return total
 
-        # free the device-resident copy of the inputs' consumer state is not needed; warm up once
-        d2h = e2e_step()
-        e2e_step()
+        def worker(which, first, count):
+            torch.cuda.set_device(local)
+            out = 0
+            for k in range(count):
+                out = e2e_step(which, first + 2 * k)
+            return out
+
+        def run_steps(count):                  # `count` steps in total, alternating between the contexts
+            turn["next"] = 0
+            with ThreadPoolExecutor(max_workers=2) as ex:
+                futs = [ex.submit(worker, w, w, (count + 1 - w) // 2) for w in (0, 1)]
+                return max(f.result() for f in futs)
+
+        run_steps(4)                           # warm-up: allocations, pinning of the result buffers
         barrier()
+        e2e_steps = max(4, min(args.steps, 8))
         t0 = time.perf_counter()
-        e0.record(stream)
-        e2e_steps = max(2, min(args.steps, 3))
-        for _ in range(e2e_steps):
-            d2h = e2e_step()
-        e1.record(stream)
-        barrier()
+        d2h = run_steps(e2e_steps)
+        torch.cuda.synchronize(dev)
         wall = (time.perf_counter() - t0) * 1e3
-        ems = max(e0.elapsed_time(e1), wall)          # host-side fetches serialise with the stream
-        t = torch.tensor([ems], dtype=torch.float64, device=dev)
+        barrier()
+        t = torch.tensor([wall], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": n_reads * world * e2e_steps / (float(t.item()) * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(batch.nbytes()), "d2h_bytes_per_step": int(d2h),
-               "steps": e2e_steps, "ms_per_step": float(t.item()) / e2e_steps}
+               "steps": e2e_steps, "ms_per_step": float(t.item()) / e2e_steps,
+               "pipeline": "2 contexts alternate: read-back of batch k overlaps upload of batch k+1; host wall clock"}
+        engines[1].close()
 
     if rank != 0:
         if world > 1:
@@ -314,9 +343,10 @@ def main():
             traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": "vote_kernel (SSCS vote + family mode fields)",
+    roofline = {"bound": "hbm", "kernel": "vote_small_kernel (SSCS vote: consensus_maker over every family of 2..127 reads)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "traffic": traffic, "traffic_source": "profiles/vote_traffic.json (ncu --set full, dram__bytes_read+write per launch)",
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "ms_per_launch": vote_ms / max(1, vote_runs),
                 "phase_ms_per_step": {k: v[0] / max(1, v[1]) for k, v in phases.items() if v[1]}}
 
