@@ -32,7 +32,7 @@ struct PhaseTimer {
 };
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
-           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NBIG = 30, CT_COUNT = 32 };
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_COUNT = 32 };
 
 }  // namespace
 
@@ -61,7 +61,7 @@ struct cc_ctx {
     DevBuf sscs_list, dcs_list, corr_list, dcssc_list, sscs_row, dcs_row, corr_row, dcssc_row;
     DevBuf sscs_rows, corr_rows, dcs_rows;                 // dcs_rows: pool of all duplex rows (see do_duplex)
     DevBuf dcs_mapq, dcs_flag, dcs_tlen, dcs_rg;
-    DevBuf vstart, vsize, big_list, thr_table;
+    DevBuf vstart, vsize, big_list, mid_list, thr_table;
     uint8_t thr_host[128];
     ThrMagic thr_magic{0, 0, 1};
     bool thr_valid = false;
@@ -182,7 +182,7 @@ int scan_prepare(cc_ctx *ctx, uint64_t n, uint32_t **ticket)
     uint64_t tiles = scan_tiles(n);
     TRY(ensure(ctx, ctx->scan_status, (tiles + 1) * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (tiles + 1) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_NBIG - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
     *ticket = ptr<uint32_t>(ctx->counters) + CT_TICKET0 + ctx->next_ticket++;
     return CC_OK;
 }
@@ -323,7 +323,7 @@ int do_group(cc_ctx *ctx)
            ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
            ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
-           (uint32_t)CC_HIST_BINS);
+           (uint32_t)CC_HIST_BINS, ctr + CT_NMID);
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS));
@@ -424,22 +424,36 @@ int upload_thresholds(cc_ctx *ctx)
     return CC_OK;
 }
 
-template <int G>
-int launch_vote_small(cc_ctx *ctx, uint32_t rows)
+// one launch of vote_small_kernel over the families of n_lo..n_hi reads
+template <int G, int CH, int DEPTH, bool FLUSH>
+int launch_vote_small(cc_ctx *ctx, uint32_t rows, uint32_t n_lo, uint32_t n_hi, const uint32_t *row_list)
 {
-    auto kernel = vote_small_kernel<G>;
+    auto kernel = vote_small_kernel<G, CH, DEPTH, FLUSH>;
+    constexpr int ring = vote_ring_bytes(CH, DEPTH);
     static bool configured = false;      // per template instance
     if (!configured) {
-        CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VOTE_RING_BYTES));
+        CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
         configured = true;
     }
-    kernel<<<blocks_for(rows, VOTE_CHUNK), 256, VOTE_RING_BYTES, ctx->stream>>>( ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
-           ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list), rows,
-           ptr<uint8_t>(ctx->thr_table), (1.0 >= ctx->params.cutoff) ? 1 : 0, ctx->thr_magic, ptr<uint8_t>(ctx->sscs_rows),
-           ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
-           ptr<uint8_t>(ctx->fam_rg), ptr<uint32_t>(ctx->counters) + CT_ERR);
+    kernel<<<blocks_for(rows, VOTE_CHUNK), 256, ring, ctx->stream>>>(
+        ctx->payload, ctx->stride, ctx->lpad, ctx->perm, ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize),
+        ptr<uint32_t>(ctx->sscs_list), row_list, rows, n_lo, n_hi, ptr<uint8_t>(ctx->thr_table),
+        (1.0 >= ctx->params.cutoff) ? 1 : 0, ctx->thr_magic, ctx->fields, ptr<uint8_t>(ctx->sscs_rows),
+        ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
+        ptr<uint32_t>(ctx->counters) + CT_ERR);
     ctx->launches++;
     CK(cudaGetLastError());
+    return CC_OK;
+}
+
+// Families of 2..15 reads (the bulk) and families of 16..127 reads (nibble counters need flushing)
+// are voted by separate launches; the second one is skipped when the batch has no such family.
+template <int G>
+int launch_vote_pair(cc_ctx *ctx, uint32_t rows)
+{
+    TRY((launch_vote_small<G, 1, 3, false>(ctx, rows, 2, 15, nullptr)));
+    const uint32_t n_mid = ctx->host_ctr[CT_NMID];       // counted by family_build_kernel, listed by vote_segments_kernel
+    if (n_mid) TRY((launch_vote_small<G, 1, 3, true>(ctx, n_mid, 16, VOTE_SMALL_MAX, ptr<uint32_t>(ctx->mid_list))));
     return CC_OK;
 }
 
@@ -449,6 +463,7 @@ int do_vote(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->sscs_rows, (size_t)rows * ctx->stride));
     TRY(ensure(ctx, ctx->vstart, (size_t)rows * 4)); TRY(ensure(ctx, ctx->vsize, (size_t)rows * 4));
     TRY(ensure(ctx, ctx->big_list, (size_t)rows * 4));
+    TRY(ensure(ctx, ctx->mid_list, ((size_t)ctx->host_ctr[CT_NMID] + 1) * 4));
     if (!ctx->thr_valid) TRY(upload_thresholds(ctx));
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     if (rows) {
@@ -457,17 +472,18 @@ int do_vote(cc_ctx *ctx)
                ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), ptr<uint8_t>(ctx->is_sscs), rows,
                ptr<uint32_t>(ctx->vstart),
                ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG,
-               ctx->lpad <= 512 ? VOTE_SMALL_MAX : 0u);   // a lane group covers at most 512 positions
+               ctx->lpad <= 512 ? VOTE_SMALL_MAX : 0u,    // a lane group covers at most 512 positions
+               ptr<uint32_t>(ctx->mid_list), ctr + CT_NMIDLIST);
         TRY(phase_end(ctx, CC_PH_VOTE_AUX));
     }
     TRY(phase_begin(ctx, CC_PH_VOTE));
     if (rows && ctx->lpad <= 512) {
         const uint32_t lanes = (ctx->lpad + 15) / 16;
-        if (lanes <= 2) TRY(launch_vote_small<2>(ctx, rows));
-        else if (lanes <= 4) TRY(launch_vote_small<4>(ctx, rows));
-        else if (lanes <= 8) TRY(launch_vote_small<8>(ctx, rows));
-        else if (lanes <= 16) TRY(launch_vote_small<16>(ctx, rows));
-        else TRY(launch_vote_small<32>(ctx, rows));
+        if (lanes <= 2) TRY(launch_vote_pair<2>(ctx, rows));
+        else if (lanes <= 4) TRY(launch_vote_pair<4>(ctx, rows));
+        else if (lanes <= 8) TRY(launch_vote_pair<8>(ctx, rows));
+        else if (lanes <= 16) TRY(launch_vote_pair<16>(ctx, rows));
+        else TRY(launch_vote_pair<32>(ctx, rows));
     }
     TRY(phase_end(ctx, CC_PH_VOTE));
     if (rows) {
@@ -598,7 +614,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->f_dcssc, &ctx->sscs_list, &ctx->dcs_list, &ctx->corr_list, &ctx->dcssc_list, &ctx->sscs_row,
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
-                     &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
+                     &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->mid_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
                      &ctx->first_read};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)

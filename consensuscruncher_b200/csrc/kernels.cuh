@@ -188,7 +188,7 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
                     uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
                     uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag,
                     int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-                    unsigned long long *__restrict__ hist, uint32_t hist_bins)
+                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid)
 {
     __shared__ uint32_t small_hist[256];           // sizes < 256 are counted per block first
     small_hist[threadIdx.x] = 0;
@@ -220,6 +220,7 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
     __syncthreads();
     uint32_t v = small_hist[threadIdx.x];
     if (v) atomicAdd(&hist[threadIdx.x], (unsigned long long)v);
+    if (v && threadIdx.x >= 16 && threadIdx.x < 128) atomicAdd(n_mid, v);   // families of 16..127 reads
 }
 
 // Pair symmetry check (SSCS_maker.py:275 emits a pair name only with exactly two tags):

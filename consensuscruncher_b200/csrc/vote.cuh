@@ -30,8 +30,6 @@ namespace ccgpu {
 
 constexpr uint32_t VOTE_SMALL_MAX = 127;     // byte-lane compares below need counts < 128
 constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows per staged batch
-constexpr int VOTE_DEPTH = VOTE_DEPTH_CFG;                // ring slots per lane: VOTE_DEPTH - 1 batches in flight
-constexpr int VOTE_RING_BYTES = VOTE_DEPTH * VOTE_ROWS_PER_BATCH * 256 * 24;   // dynamic shared memory per block
 
 __device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
 {
@@ -155,13 +153,14 @@ struct ThrMagic {       // thr[p] == (p * k + r) >> 8 for every p the kernel can
     int use_table;
 };
 
+template <bool TOTALS>
 __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr, bool unanimous_ok, ThrMagic tm,
                                                uint32_t &err)
 {
     QuadOut o;
     const uint32_t tnow = (a.gt >> 4) & 0x0F0F0F0Fu;
-    const uint32_t cA = a.tA + (a.ac & 0x0F0F0F0Fu), cC = a.tC + ((a.ac >> 4) & 0x0F0F0F0Fu),
-                   cT = a.tT + tnow, cG = a.tG + (a.gt & 0x0F0F0F0Fu) - tnow;
+    uint32_t cA = a.ac & 0x0F0F0F0Fu, cC = (a.ac >> 4) & 0x0F0F0F0Fu, cT = tnow, cG = (a.gt & 0x0F0F0F0Fu) - tnow;
+    if (TOTALS) { cA += a.tA; cC += a.tC; cT += a.tT; cG += a.tG; }
     uint32_t m1 = bytes_of(ge7(cA, cC));                  // ties keep the earlier base: A,C,G,T order
     uint32_t m2 = bytes_of(ge7(cG, cT));
     uint32_t bAC = sel(cA, cC, m1), wAC = sel(0x01010101u, 0x02020202u, m1);
@@ -288,26 +287,36 @@ __device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t n
 
 constexpr int VOTE_CHUNK = 1024;    // SSCS rows a block sorts by family size and then votes
 
+// dynamic shared memory of vote_small_kernel<G, CH, DEPTH>: the lanes' staging rings
+constexpr int vote_ring_bytes(int ch, int depth) { return depth * VOTE_ROWS_PER_BATCH * ch * 256 * 24; }
+
 // vstart / vsize: segment of `perm` of every SSCS row (filled by vote_segments_kernel).
-// A block takes VOTE_CHUNK consecutive rows, orders them by family size in shared memory and
-// hands them to its lane groups in that order, so the groups of a warp walk families of
-// (nearly) equal size and their row loops stay in step.
-template <int G>
-__global__ void __launch_bounds__(256, VOTE_BLOCKS_CFG)
-vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
-                  uint32_t lpad, const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
-                  const uint32_t *__restrict__ vsize, const uint32_t *__restrict__ sscs_list, uint32_t n_rows,
-                  const uint8_t *__restrict__ thr_table, int unanimous_ok, ThrMagic tm, uint8_t *__restrict__ out_rows,
-                  uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen,
-                  uint8_t *__restrict__ fam_rg, uint32_t *__restrict__ err_flag)
+// A block takes VOTE_CHUNK consecutive rows, orders the families of n_lo..n_hi reads by size in
+// shared memory and hands them to its lane groups in that order, so the groups of a warp walk
+// families of (nearly) equal size and their row loops stay in step.
+//   G      lanes per family           CH     16-position chunks per lane (G * CH * 16 >= lpad)
+//   DEPTH  staging ring slots         FLUSH  families may exceed 15 reads (nibble counters are
+//                                            emptied into byte counters every 12 reads)
+template <int G, int CH, int DEPTH, bool FLUSH>
+__global__ void __launch_bounds__(256, 2)
+vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t lpad,
+                  const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
+                  const uint32_t *__restrict__ vsize, const uint32_t *__restrict__ sscs_list,
+                  const uint32_t *__restrict__ row_list, uint32_t n_rows, uint32_t n_lo, uint32_t n_hi,
+                  const uint8_t *__restrict__ thr_table, int unanimous_ok, ThrMagic tm,
+                  const uint4 *__restrict__ fields, uint8_t *__restrict__ out_rows, uint8_t *__restrict__ fam_mapq,
+                  uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
+                  uint32_t *__restrict__ err_flag)
 {
     __shared__ uint8_t thr[128];
     __shared__ uint32_t s_start[VOTE_CHUNK];
     __shared__ uint8_t s_size[VOTE_CHUNK];
     __shared__ uint16_t s_order[VOTE_CHUNK];
+    __shared__ uint32_t s_row[VOTE_CHUNK];      // SSCS row of every entry (row_list given: only listed rows are voted)
     __shared__ uint32_t s_bin[128];
     constexpr int GROUPS = 32 / G;
     constexpr int BLOCK_GROUPS = 8 * GROUPS;
+    constexpr int RB = VOTE_ROWS_PER_BATCH;
     const int tid = threadIdx.x, lane = tid & 31, gl = lane % G, grp = lane / G;
     const uint32_t gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << (grp * G);
     const uint32_t half = lpad >> 1;
@@ -317,10 +326,12 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
     if (tid < 128) { thr[tid] = thr_table[tid]; s_bin[tid] = 0; }
     __syncthreads();
     for (uint32_t i = tid; i < rows_here; i += 256) {
-        const uint32_t v = __ldg(&vsize[row0 + i]);
+        const uint32_t r = row_list ? __ldg(&row_list[row0 + i]) : row0 + i;
+        const uint32_t v = __ldg(&vsize[r]);
         uint32_t n = v & 0x7FFFFFFFu;
-        if (n > VOTE_SMALL_MAX) n = 0;                     // large families go to vote_big_kernel
-        s_start[i] = __ldg(&vstart[row0 + i]);
+        if (n < n_lo || n > n_hi) n = 0;                   // voted by another launch (other sizes)
+        s_row[i] = r;
+        s_start[i] = __ldg(&vstart[r]);
         s_size[i] = (uint8_t)(n | ((v >> 31) << 7));       // bit 7: mode fields differ inside the family
         atomicAdd(&s_bin[n], 1u);
     }
@@ -340,8 +351,9 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
         for (int k = 0; k < 4; k++) { s_bin[tid * 4 + k] = run; run += v[k]; }
     }
     __syncthreads();
-    const uint32_t skipped = s_bin[1];                     // bin 0 = rows this kernel does not vote
+    const uint32_t skipped = s_bin[1];                     // bin 0 = rows this launch does not vote
     __syncthreads();
+    if (skipped == rows_here) return;
     for (uint32_t i = tid; i < rows_here; i += 256) s_order[atomicAdd(&s_bin[s_size[i] & 0x7F], 1u)] = (uint16_t)i;
     __syncthreads();
 
@@ -350,26 +362,27 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
     const uint32_t one = (uint32_t)unanimous_ok | 1u;      // 1, but only known at run time (see fadd)
     const uint32_t todo = rows_here - skipped;
     const uint32_t my_slot = (tid >> 5) * GROUPS + grp;
-    const uint32_t pos0 = gl * 16;
-    const bool lane_on = pos0 < lpad;                      // this lane owns 16 positions of the rows
+    const uint32_t pos0 = gl * (16 * CH);                  // this lane owns CH chunks of 16 positions
+    const bool lane_on = pos0 < lpad;
 
     // Lane-private staging ring in shared memory, filled with cp.async: every lane copies its
-    // own 8 sequence bytes + 16 quality bytes of up to VOTE_ROWS_PER_BATCH rows per batch and
-    // keeps VOTE_DEPTH - 1 batches in flight while it votes the oldest one.  Bytes in flight
-    // no longer occupy registers, which is what bounds the achieved HBM bandwidth here.
+    // own 8 sequence bytes + 16 quality bytes per chunk of up to RB rows per batch and keeps
+    // DEPTH - 1 batches in flight while it votes the oldest one.  Bytes in flight do not
+    // occupy registers.
     extern __shared__ __align__(16) uint8_t ring[];
-    constexpr uint32_t ROW_Q = 256 * 16, ROW_S = 256 * 8;                       // bytes between rows of a slot
-    constexpr uint32_t SLOT_Q = VOTE_ROWS_PER_BATCH * ROW_Q, SLOT_S = VOTE_ROWS_PER_BATCH * ROW_S;
-    uint8_t *const ring_q = ring + tid * 16;                                     // [depth][row][thread] uint4
-    uint8_t *const ring_s = ring + VOTE_DEPTH * SLOT_Q + tid * 8;                // [depth][row][thread] uint2
+    constexpr uint32_t CH_Q = 256 * 16, CH_S = 256 * 8;                         // bytes between chunks of a row
+    constexpr uint32_t ROW_Q = CH * CH_Q, ROW_S = CH * CH_S;                    // ... between rows of a slot
+    constexpr uint32_t SLOT_Q = RB * ROW_Q, SLOT_S = RB * ROW_S;
+    uint8_t *const ring_q = ring + tid * 16;                                     // [depth][row][chunk][thread] uint4
+    uint8_t *const ring_s = ring + DEPTH * SLOT_Q + tid * 8;                     // [depth][row][chunk][thread] uint2
     const uint32_t ring_q_sh = (uint32_t)__cvta_generic_to_shared(ring_q);
     const uint32_t ring_s_sh = (uint32_t)__cvta_generic_to_shared(ring_s);
-    const uint8_t *const lane_src = payload + (pos0 >> 1);                       // this lane's 8 sequence bytes of read 0
-    const uint32_t q_off = half + pos0 - (pos0 >> 1);                            // ... and from there to its 16 qualities
+    const uint8_t *const lane_src = payload + (pos0 >> 1);                       // this lane's first sequence bytes of read 0
+    const uint32_t q_off = half + pos0 - (pos0 >> 1);                            // ... and from there to its qualities
 
     // producer cursor: the batch that will be issued next
     uint32_t p_t = my_slot, p_start = 0, p_n = 0, p_j0 = 0, p_slot = 0;
-    uint32_t p_idx[VOTE_ROWS_PER_BATCH];
+    uint32_t p_idx[RB];
     auto p_load_family = [&]() {
         p_start = 0; p_n = 0; p_j0 = 0;
         if (p_t < todo) {
@@ -380,35 +393,43 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
     };
     auto p_load_idx = [&]() {                              // member indices of the producer's batch
 #pragma unroll
-        for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++)
+        for (int k = 0; k < RB; k++)
             p_idx[k] = (p_n != 0) ? __ldg(&perm[p_start + min(p_j0 + k, p_n - 1)]) : 0u;
     };
     auto p_issue = [&]() {                                 // copy the producer's batch, then move on
         if (p_n != 0 && lane_on) {
 #pragma unroll
-            for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
+            for (int k = 0; k < RB; k++) {
                 if (p_j0 + k < p_n) {
                     const uint8_t *src = lane_src + (uint64_t)p_idx[k] * stride;
-                    cp_async_8_sh(ring_s_sh + p_slot * SLOT_S + k * ROW_S, src);
-                    cp_async_16_sh(ring_q_sh + p_slot * SLOT_Q + k * ROW_Q, src + q_off);
+#pragma unroll
+                    for (int h = 0; h < CH; h++) {
+                        if (h == 0 || pos0 + 16 * h < lpad) {
+                            cp_async_8_sh(ring_s_sh + p_slot * SLOT_S + k * ROW_S + h * CH_S, src + 8 * h);
+                            cp_async_16_sh(ring_q_sh + p_slot * SLOT_Q + k * ROW_Q + h * CH_Q, src + q_off + 16 * h);
+                        }
+                    }
                 }
             }
         }
         cp_async_commit();
-        p_slot = p_slot + 1 == VOTE_DEPTH ? 0 : p_slot + 1;
-        p_j0 += VOTE_ROWS_PER_BATCH;
+        p_slot = p_slot + 1 == DEPTH ? 0 : p_slot + 1;
+        p_j0 += RB;
         if (p_j0 >= p_n) { p_t += BLOCK_GROUPS; p_load_family(); }
         p_load_idx();
     };
     p_load_family();
     p_load_idx();
 #pragma unroll 1
-    for (int d = 0; d < VOTE_DEPTH - 1; d++) p_issue();
+    for (int d = 0; d < DEPTH - 1; d++) p_issue();
 
     uint32_t c_slot = 0;                                   // consumer: slot of the oldest batch still in the ring
-    auto slot_q = [&](uint32_t slot, int k) { return reinterpret_cast<const uint4 *>(ring_q + slot * SLOT_Q + k * ROW_Q); };
-    auto slot_s = [&](uint32_t slot, int k) { return reinterpret_cast<const uint2 *>(ring_s + slot * SLOT_S + k * ROW_S); };
-    auto next_slot = [&](uint32_t slot) { return slot + 1 == VOTE_DEPTH ? 0u : slot + 1; };
+    auto slot_row = [&](uint32_t slot, int k, int h) {
+        return LaneRow{*reinterpret_cast<const uint2 *>(ring_s + slot * SLOT_S + k * ROW_S + h * CH_S),
+                       *reinterpret_cast<const uint4 *>(ring_q + slot * SLOT_Q + k * ROW_Q + h * CH_Q)};
+    };
+    auto next_slot = [&](uint32_t slot) { return slot + 1 == DEPTH ? 0u : slot + 1; };
+
     for (uint32_t t0 = 0; t0 < todo; t0 += BLOCK_GROUPS) {
         const uint32_t t = t0 + my_slot;
         uint32_t start = 0, n = 0, row = 0;
@@ -418,89 +439,102 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
             start = s_start[i];
             n = s_size[i] & 0x7F;
             mixed = (s_size[i] & 0x80) != 0;
-            row = row0 + i;
+            row = s_row[i];
         }
         uint8_t *out = out_rows + (uint64_t)row * stride;
 
         if (n != 0) {
-            uint32_t code[4] = {0, 0, 0, 0}, qual[4] = {0, 0, 0, 0};
             if (n == 2) {
                 p_issue();
-                cp_async_wait<VOTE_DEPTH - 1>();
+                cp_async_wait<DEPTH - 1>();
                 if (lane_on) {
-                    LaneRow r1{*slot_s(c_slot, 0), *slot_q(c_slot, 0)}, r2{*slot_s(c_slot, 1), *slot_q(c_slot, 1)};
-                    uint32_t n1[4], q1[4], n2[4], q2[4];
-                    split_row(r1, n1, q1);
-                    split_row(r2, n2, q2);
 #pragma unroll
-                    for (int g = 0; g < 4; g++)
-                        quad_pair(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], tie_ok, unanimous_ok != 0, code[g], qual[g], err);
+                    for (int h = 0; h < CH; h++) {
+                        if (h != 0 && pos0 + 16 * h >= lpad) break;
+                        LaneRow r1 = slot_row(c_slot, 0, h), r2 = slot_row(c_slot, 1, h);
+                        uint32_t n1[4], q1[4], n2[4], q2[4], code[4], qual[4];
+                        split_row(r1, n1, q1);
+                        split_row(r2, n2, q2);
+#pragma unroll
+                        for (int g = 0; g < 4; g++)
+                            quad_pair(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], tie_ok, unanimous_ok != 0, code[g], qual[g], err);
+                        uint2 so;
+                        uint4 qo;
+                        join_row(code, qual, so, qo);
+                        *reinterpret_cast<uint2 *>(out + ((pos0 + 16 * h) >> 1)) = so;
+                        *reinterpret_cast<uint4 *>(out + half + pos0 + 16 * h) = qo;
+                    }
                 }
                 c_slot = next_slot(c_slot);
             } else {
-                Quad acc[4];
+                Quad acc[CH][4];
 #pragma unroll
-                for (int g = 0; g < 4; g++) acc[g] = Quad{0, 0, 0, 0, 0, 0, 0, 0};
+                for (int h = 0; h < CH; h++)
+#pragma unroll
+                    for (int g = 0; g < 4; g++) acc[h][g] = Quad{0, 0, 0, 0, 0, 0, 0, 0};
                 const uint32_t first_slot = c_slot;
-                for (uint32_t j0 = 0; j0 < n; j0 += VOTE_ROWS_PER_BATCH) {
+                for (uint32_t j0 = 0; j0 < n; j0 += RB) {
                     p_issue();
-                    cp_async_wait<VOTE_DEPTH - 1>();
+                    cp_async_wait<DEPTH - 1>();
                     if (lane_on) {
 #pragma unroll
-                        for (int k = 0; k < VOTE_ROWS_PER_BATCH; k++) {
+                        for (int k = 0; k < RB; k++) {
                             if (j0 + k < n) {
-                                LaneRow r{*slot_s(c_slot, k), *slot_q(c_slot, k)};
-                                uint32_t nib[4], q[4];
-                                split_row(r, nib, q);
 #pragma unroll
-                                for (int g = 0; g < 4; g++) quad_add(acc[g], nib[g], q[g], one);
+                                for (int h = 0; h < CH; h++) {
+                                    if (h == 0 || pos0 + 16 * h < lpad) {
+                                        uint32_t sel4[4], q[4];
+                                        split_row(slot_row(c_slot, k, h), sel4, q);
+#pragma unroll
+                                        for (int g = 0; g < 4; g++) quad_add(acc[h][g], sel4[g], q[g], one);
+                                    }
+                                }
                             }
                         }
                     }
                     c_slot = next_slot(c_slot);
-                    if ((j0 + VOTE_ROWS_PER_BATCH) % 12 == 0 && j0 + VOTE_ROWS_PER_BATCH < n) {
+                    if (FLUSH && (j0 + RB) % 12 == 0 && j0 + RB < n) {
 #pragma unroll
-                        for (int g = 0; g < 4; g++) quad_flush(acc[g]);
+                        for (int h = 0; h < CH; h++)
+#pragma unroll
+                            for (int g = 0; g < 4; g++) quad_flush(acc[h][g]);
                     }
                 }
                 if (lane_on) {
-                    QuadOut o[4];
-                    uint32_t any_single = 0;
 #pragma unroll
-                    for (int g = 0; g < 4; g++) {
-                        o[g] = quad_finish(acc[g], thr, unanimous_ok != 0, tm, err);
-                        any_single |= o[g].single;
-                    }
-#ifdef VOTE_EXP_NO_PICK
-                    any_single = 0;
-#endif
-                    if (any_single) {                      // lane-local: re-walk the rows for the lone supporters
-                        uint32_t pick[4] = {0, 0, 0, 0};
-                        // the ring still holds the last VOTE_DEPTH - 1 batches that were consumed... but
-                        // the producer has already reused older slots, so only short families re-read it
-                        const bool in_ring = n <= VOTE_ROWS_PER_BATCH;
-                        for (uint32_t j = 0; j < n; j++) {
-                            LaneRow rr;
-                            if (in_ring) { rr.s = *slot_s(first_slot, j); rr.q = *slot_q(first_slot, j); }
-                            else rr = load_lane_row(payload, stride, half, __ldg(&perm[start + j]), pos0);
-                            uint32_t nib[4], q[4];
-                            split_row(rr, nib, q);
+                    for (int h = 0; h < CH; h++) {
+                        if (h != 0 && pos0 + 16 * h >= lpad) break;
+                        QuadOut o[4];
+                        uint32_t any_single = 0;
 #pragma unroll
-                            for (int g = 0; g < 4; g++) pick[g] |= quad_pick(expand_sel(nib[g]), q[g], o[g].win, o[g].single);
+                        for (int g = 0; g < 4; g++) {
+                            o[g] = quad_finish<FLUSH>(acc[h][g], thr, unanimous_ok != 0, tm, err);
+                            any_single |= o[g].single;
                         }
+                        if (any_single) {                  // lane-local: re-walk the rows for the lone supporters
+                            uint32_t pick[4] = {0, 0, 0, 0};
+                            const bool in_ring = n <= RB;  // longer families have left the ring: re-read them
+                            for (uint32_t j = 0; j < n; j++) {
+                                LaneRow rr = in_ring ? slot_row(first_slot, (int)j, h)
+                                                     : load_lane_row(payload, stride, half, __ldg(&perm[start + j]), pos0 + 16 * h);
+                                uint32_t sel4[4], q[4];
+                                split_row(rr, sel4, q);
 #pragma unroll
-                        for (int g = 0; g < 4; g++) o[g].qual |= cap60(pick[g]) & o[g].single;
+                                for (int g = 0; g < 4; g++) pick[g] |= quad_pick(expand_sel(sel4[g]), q[g], o[g].win, o[g].single);
+                            }
+#pragma unroll
+                            for (int g = 0; g < 4; g++) o[g].qual |= cap60(pick[g]) & o[g].single;
+                        }
+                        uint32_t code[4], qual[4];
+#pragma unroll
+                        for (int g = 0; g < 4; g++) { code[g] = o[g].code; qual[g] = o[g].qual; }
+                        uint2 so;
+                        uint4 qo;
+                        join_row(code, qual, so, qo);
+                        *reinterpret_cast<uint2 *>(out + ((pos0 + 16 * h) >> 1)) = so;
+                        *reinterpret_cast<uint4 *>(out + half + pos0 + 16 * h) = qo;
                     }
-#pragma unroll
-                    for (int g = 0; g < 4; g++) { code[g] = o[g].code; qual[g] = o[g].qual; }
                 }
-            }
-            if (lane_on) {
-                uint2 so;
-                uint4 qo;
-                join_row(code, qual, so, qo);
-                *reinterpret_cast<uint2 *>(out + (pos0 >> 1)) = so;
-                *reinterpret_cast<uint4 *>(out + half + pos0) = qo;
             }
             for (uint32_t x = half + lpad + gl * 4; x < stride; x += G * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
         }
@@ -532,13 +566,13 @@ vote_small_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ 
     if (err) atomicOr(err_flag, 1u);
 }
 
-// segment of every SSCS row, and the list of rows too large for vote_small_kernel
+// segment of every SSCS row, and the lists of rows for the mid-size launch and for vote_big_kernel
 __global__ void __launch_bounds__(256)
 vote_segments_kernel(const uint32_t *__restrict__ sscs_list, const uint32_t *__restrict__ fam_start,
                      const uint32_t *__restrict__ fam_size, const uint8_t *__restrict__ fam_class, uint32_t n_rows,
                      uint32_t *__restrict__ vstart,
                      uint32_t *__restrict__ vsize, uint32_t *__restrict__ big_list, uint32_t *__restrict__ n_big,
-                     uint32_t small_max)
+                     uint32_t small_max, uint32_t *__restrict__ mid_list, uint32_t *__restrict__ n_mid)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
@@ -546,7 +580,8 @@ vote_segments_kernel(const uint32_t *__restrict__ sscs_list, const uint32_t *__r
     uint32_t n = fam_size[c];
     vstart[r] = fam_start[c];
     vsize[r] = n | ((uint32_t)(fam_class[c] & 2) << 30);   // bit 31: members' mode fields differ
-    if (n > VOTE_SMALL_MAX) big_list[atomicAdd(n_big, 1u)] = r;
+    if (n > small_max) big_list[atomicAdd(n_big, 1u)] = r;           // one warp per family (vote_big_kernel)
+    else if (n > 15) mid_list[atomicAdd(n_mid, 1u)] = r;             // 16..127 reads: the launch with counter flushes
 }
 
 // one warp per large family, looping over however many the device-side counter says

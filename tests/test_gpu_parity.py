@@ -39,6 +39,12 @@ def test_gpu_reproduces_reference_outputs(engine, name):
     dict(seed=26, n_molecules=1500, L=250, mapq_mixed=True),
     dict(seed=27, n_molecules=2, L=32, dist="const", fam_mean=700, p_duplex=1.0, err=0.05),   # > 255 reads / family
     dict(seed=28, n_molecules=40, L=40, dist="const", fam_mean=40, p_duplex=1.0, mapq_mixed=True),  # mode over > 32 reads
+    dict(seed=29, n_molecules=60, L=600, fam_mean=3.0),                # lpad > 512: every family on the warp-per-family kernel
+    dict(seed=30, n_molecules=300, L=100, dist="const", fam_mean=14),  # just below / above the counter-flush boundary
+    dict(seed=31, n_molecules=300, L=100, dist="const", fam_mean=17),
+    dict(seed=32, n_molecules=200, L=160, dist="lognormal", fam_mean=30.0, err=0.02),   # 10 of 16 lanes active, mid sizes
+    dict(seed=33, n_molecules=30, L=128, dist="const", fam_mean=127, p_duplex=1.0),     # largest small-kernel family
+    dict(seed=34, n_molecules=30, L=128, dist="const", fam_mean=128, p_duplex=1.0),     # smallest warp-per-family one
 ])
 def test_gpu_equals_oracle_on_synthetic(engine, kw):
     packed = synth.generate(**kw).to_packed()
