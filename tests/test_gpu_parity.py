@@ -190,3 +190,39 @@ def test_primitives_equal_oracle_on_random_rows(engine):
             got = engine.duplex_consensus_rows(rows[:18], rows[18:36], lpad, sc)
             for i in range(18):
                 assert (got[i] == oracle.duplex_consensus_rows(rows[i], rows[18 + i], lpad, sc)).all()
+
+
+def test_region_shards_on_the_gpu_equal_the_whole(engine):
+    """Multi-GPU semantics on the device path: split a batch by genomic regions into 8 shards the
+    way `bench.py --gpus 8` / shard.py would, run every shard through the CUDA path, and compare
+    the union with the unsharded run (families never straddle shards)."""
+    from consensuscruncher_b200 import shard
+    s = synth.generate(seed=95, n_molecules=6000, L=64, n_tid=4, region=(0, 200000), dist="wgs", p_duplex=0.4)
+    packed = s.to_packed()
+    engine.set_params(cutoff=0.7, scorrect=True)
+    whole = engine.consensus(packed)
+    regions = [(t, a, a + 25000) for t in range(4) for a in range(0, 200000, 25000)]
+    owner, _ = shard.shard_pairs(packed.fields, regions, 8)
+    assert (owner >= 0).all() and len(set(owner.tolist())) == 8
+    stats = np.zeros(16, np.int64)
+    hist = np.zeros(65536, np.uint64)
+    seen = {}
+    for r in range(8):
+        mine = shard.take_pairs(packed, owner == r)
+        res = engine.consensus(mine)
+        stats += res.stats
+        hist += engine.fetch("fam_hist")
+        keys = mine.fields[res.fam_tmpl][["bc", "tid", "pos", "mtid", "mpos", "flag"]]
+        for g, k in enumerate(keys.tolist()):
+            row = bytes(res.sscs_rows[res.sscs_row[g]]) if res.sscs_row[g] >= 0 else None
+            corr = bytes(res.corr_rows[res.corr_row[g]]) if res.corr_row[g] >= 0 else None
+            seen[tuple(k)] = (int(res.fam_size[g]), row, corr, int(res.partner[g]) >= 0)
+    assert (stats == whole.stats).all()
+    assert (hist[:64] == np.bincount(whole.fam_size, minlength=64)[:64].astype(np.uint64)).all()
+    keys = packed.fields[whole.fam_tmpl][["bc", "tid", "pos", "mtid", "mpos", "flag"]]
+    assert len(seen) == whole.n_fam
+    for g, k in enumerate(keys.tolist()):
+        size, row, corr, has_partner = seen[tuple(k)]
+        assert size == whole.fam_size[g] and has_partner == (whole.partner[g] >= 0)
+        assert row == (bytes(whole.sscs_rows[whole.sscs_row[g]]) if whole.sscs_row[g] >= 0 else None)
+        assert corr == (bytes(whole.corr_rows[whole.corr_row[g]]) if whole.corr_row[g] >= 0 else None)
