@@ -77,6 +77,10 @@ __device__ __forceinline__ uint32_t ge7(uint32_t a, uint32_t b) { return ((a | 0
 // bit 7 of each byte: byte != 0, for bytes < 128
 __device__ __forceinline__ uint32_t nz7(uint32_t x) { return (x + 0x7F7F7F7Fu) & 0x80808080u; }
 
+// the same tests with garbage in bits 0-6: enough when the result only feeds bytes_of()
+__device__ __forceinline__ uint32_t ge7u(uint32_t a, uint32_t b) { return (a | 0x80808080u) - b; }
+__device__ __forceinline__ uint32_t nz7u(uint32_t x) { return x + 0x7F7F7F7Fu; }
+
 __device__ __forceinline__ uint32_t sel(uint32_t a, uint32_t b, uint32_t mask) { return (a & mask) | (b & ~mask); }
 
 // x + y as an integer multiply-add: with `one` a run-time 1 the compiler cannot fold it back
@@ -135,7 +139,7 @@ __device__ __forceinline__ uint32_t expand_sel(uint32_t sel16)
 __device__ __forceinline__ uint32_t cap60(uint32_t q)
 {
     uint32_t lo = q & 0x7F7F7F7Fu;
-    uint32_t big = bytes_of(ge7(lo, 0x3C3C3C3Cu) | (q & 0x80808080u));
+    uint32_t big = bytes_of(ge7u(lo, 0x3C3C3C3Cu) | q);
     return sel(0x3C3C3C3Cu, lo, big);
 }
 
@@ -161,11 +165,11 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
     const uint32_t tnow = (a.gt >> 4) & 0x0F0F0F0Fu;
     uint32_t cA = a.ac & 0x0F0F0F0Fu, cC = (a.ac >> 4) & 0x0F0F0F0Fu, cT = tnow, cG = (a.gt & 0x0F0F0F0Fu) - tnow;
     if (TOTALS) { cA += a.tA; cC += a.tC; cT += a.tT; cG += a.tG; }
-    uint32_t m1 = bytes_of(ge7(cA, cC));                  // ties keep the earlier base: A,C,G,T order
-    uint32_t m2 = bytes_of(ge7(cG, cT));
+    uint32_t m1 = bytes_of(ge7u(cA, cC));                  // ties keep the earlier base: A,C,G,T order
+    uint32_t m2 = bytes_of(ge7u(cG, cT));
     uint32_t bAC = sel(cA, cC, m1), wAC = sel(0x01010101u, 0x02020202u, m1);
     uint32_t bGT = sel(cG, cT, m2), wGT = sel(0x04040404u, 0x08080808u, m2);
-    uint32_t m3 = bytes_of(ge7(bAC, bGT));
+    uint32_t m3 = bytes_of(ge7u(bAC, bGT));
     uint32_t best = sel(bAC, bGT, m3);
     o.win = sel(wAC, wGT, m3);
     uint32_t sum = cA + cC + cG + cT;
@@ -176,10 +180,10 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
         // threshold of every position at once: two 16-bit lanes per multiply, no table, no divergence
         uint32_t te = (((pass & 0x00FF00FFu) * tm.k + tm.r2) >> 8) & 0x00FF00FFu;
         uint32_t to = (((pass >> 8) & 0x00FF00FFu) * tm.k + tm.r2) & 0xFF00FF00u;
-        ok = bytes_of(ge7(best, te | to)) & bytes_of(nz7(best));
+        ok = bytes_of(ge7u(best, te | to)) & bytes_of(nz7u(best));
     } else {
         uint32_t split = nz7(best ^ pass);                 // not unanimous
-        ok = bytes_of(nz7(best)) & ~bytes_of(split);       // unanimous and at least one passing read
+        ok = bytes_of(nz7u(best)) & ~bytes_of(split);       // unanimous and at least one passing read
         if (!unanimous_ok) ok = 0;
         while (split) {                                    // look the threshold up per position
             int k = (__ffs(split) - 1) >> 3;
@@ -189,9 +193,9 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
         }
     }
     o.code = sel(o.win, 0x0F0F0F0Fu, ok);
-    uint32_t two = bytes_of(ge7(best, 0x02020202u));
-    uint32_t lone = bytes_of(nz7(best)) & ~two;            // winner has exactly one supporter
-    uint32_t one_pass = lone & ~bytes_of(ge7(pass, 0x02020202u));   // ... and it is the only passing read
+    uint32_t two = bytes_of(ge7u(best, 0x02020202u));
+    uint32_t lone = bytes_of(nz7u(best)) & ~two;            // winner has exactly one supporter
+    uint32_t one_pass = lone & ~bytes_of(ge7u(pass, 0x02020202u));   // ... and it is the only passing read
     o.single = lone & ~one_pass;                           // several passing reads, all different: needs a re-walk
     o.qual = (two & 0x3C3C3C3Cu) | (cap60(a.qany) & one_pass);     // 60 where two or more passing reads agree
     return o;
@@ -201,7 +205,7 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
 __device__ __forceinline__ uint32_t quad_pick(uint32_t nib, uint32_t q, uint32_t win, uint32_t single)
 {
     uint32_t b = nib & bytes_of(pass7_of(q));
-    uint32_t same = ~bytes_of(nz7(b ^ win)) & single;      // win is never 0, so `same` implies passing
+    uint32_t same = ~bytes_of(nz7u(b ^ win)) & single;      // win is never 0, so `same` implies passing
     return q & same;
 }
 
@@ -273,10 +277,10 @@ __device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t n
     uint32_t m1 = bytes_of(pass7_of(q1)), m2 = bytes_of(pass7_of(q2));
     uint32_t b1 = nib1 & m1, b2 = nib2 & m2;
     err |= (((b1 | 0x80808080u) - 0x01010101u) & b1) | (((b2 | 0x80808080u) - 0x01010101u) & b2);
-    err |= (m1 & ~bytes_of(nz7(b1))) | (m2 & ~bytes_of(nz7(b2)));      // passing base that is none of A,C,G,T
-    uint32_t both = m1 & m2, differ = bytes_of(nz7(b1 ^ b2));
+    err |= (m1 & ~bytes_of(nz7u(b1))) | (m2 & ~bytes_of(nz7u(b2)));      // passing base that is none of A,C,G,T
+    uint32_t both = m1 & m2, differ = bytes_of(nz7u(b1 ^ b2));
     uint32_t agree = both & ~differ, clash = both & differ;
-    uint32_t first = bytes_of(ge7(b2, b1));                              // read 1 holds the earlier base
+    uint32_t first = bytes_of(ge7u(b2, b1));                              // read 1 holds the earlier base
     uint32_t win = sel(b1, b2, (m1 & ~m2) | (clash & first) | agree);
     uint32_t wq = sel(q1, q2, (m1 & ~m2) | (clash & first));
     uint32_t ok = (agree | (m1 ^ m2)) & (unanimous_ok ? 0xFFFFFFFFu : 0u);
@@ -378,7 +382,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
     const uint32_t ring_q_sh = (uint32_t)__cvta_generic_to_shared(ring_q);
     const uint32_t ring_s_sh = (uint32_t)__cvta_generic_to_shared(ring_s);
     const uint8_t *const lane_src = payload + (pos0 >> 1);                       // this lane's first sequence bytes of read 0
-    const uint32_t q_off = half + pos0 - (pos0 >> 1);                            // ... and from there to its qualities
+    const uint8_t *const lane_src_q = payload + half + pos0;                     // ... and its first quality bytes
 
     // producer cursor: the batch that will be issued next
     uint32_t p_t = my_slot, p_start = 0, p_n = 0, p_j0 = 0, p_slot = 0;
@@ -402,11 +406,12 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
             for (int k = 0; k < RB; k++) {
                 if (p_j0 + k < p_n) {
                     const uint8_t *src = lane_src + (uint64_t)p_idx[k] * stride;
+                    const uint8_t *src_q = lane_src_q + (uint64_t)p_idx[k] * stride;
 #pragma unroll
                     for (int h = 0; h < CH; h++) {
                         if (h == 0 || pos0 + 16 * h < lpad) {
                             cp_async_8_sh(ring_s_sh + p_slot * SLOT_S + k * ROW_S + h * CH_S, src + 8 * h);
-                            cp_async_16_sh(ring_q_sh + p_slot * SLOT_Q + k * ROW_Q + h * CH_Q, src + q_off + 16 * h);
+                            cp_async_16_sh(ring_q_sh + p_slot * SLOT_Q + k * ROW_Q + h * CH_Q, src_q + 16 * h);
                         }
                     }
                 }
@@ -611,7 +616,7 @@ vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ pa
 template <bool SC>
 __device__ __forceinline__ void quad_agree(uint32_t n1, uint32_t q1, uint32_t n2, uint32_t q2, uint32_t &code, uint32_t &qual)
 {
-    uint32_t eq = ~bytes_of(nz7(n1 ^ n2));
+    uint32_t eq = ~bytes_of(nz7u(n1 ^ n2));
     if (SC) {
         eq &= bytes_of(pass7_of(q1)) & bytes_of(pass7_of(q2));
         qual = eq & 0x3C3C3C3Cu;
