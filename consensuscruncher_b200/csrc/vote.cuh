@@ -30,6 +30,7 @@ namespace ccgpu {
 
 constexpr uint32_t VOTE_SMALL_MAX = 127;     // byte-lane compares below need counts < 128
 constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows per staged batch
+static_assert(12 % VOTE_ROWS_PER_BATCH == 0, "nibble counters are flushed every 12 reads");
 
 __device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
 {
