@@ -68,6 +68,42 @@ def _row_seq_qual(rows, idx, lpad, n):
     return codes_to_seq(codes), qual
 
 
+def sscs_stage_records(reads, packed, arrays, lpad, with_family=False):
+    """Records of the SSCS stage in the reference's emission order (SSCS_maker.py:274-298):
+    (consensus records, singleton records).  `arrays` holds fam_size, fam_tmpl, fam_mapq,
+    fam_flag, fam_tlen, fam_rg, sscs_row, sscs_rows and read_fam of one GPU run."""
+    f, src = packed.fields, packed.src
+    size = arrays["fam_size"]
+    tmpl = arrays["fam_tmpl"].astype(np.int64)
+    nf = len(size)
+    if nf:
+        mate_fam = arrays["read_fam"][tmpl ^ 1].astype(np.int64)
+        if np.any(arrays["fam_tmpl"][mate_fam] != (tmpl ^ 1)) or np.any(size[mate_fam] != size):
+            raise DomainError("a read pair does not found/join its two families together "
+                              "(orientation edge case, SURVEY.md App. B Q8/Q9): outside the GPU path's domain")
+    names = {}
+    sscs, singleton = [], []
+    for g in range(nf):
+        k = int(tmpl[g]) >> 1
+        if k not in names:
+            names[k] = keys.sscs_qname(reads[src[2 * k]], reads[src[2 * k + 1]], packed.barcodes[f["bc"][2 * k]],
+                                       packed.cigar_pairs[f["cig"][2 * k]])
+        t = reads[src[tmpl[g]]]
+        qn = "%s:%d" % (names[k], size[g])
+        if size[g] == 1:
+            r = t.copy()
+            r.qname = qn
+            singleton.append((r, g) if with_family else r)
+        else:
+            seq, qual = _row_seq_qual(arrays["sscs_rows"], arrays["sscs_row"][g], lpad, len(t.seq))
+            code = arrays["fam_rg"][g]
+            r = Read(qn, int(arrays["fam_flag"][g]), t.tid, t.pos, int(arrays["fam_mapq"][g]), t.cigar, t.mtid,
+                     t.mpos, int(arrays["fam_tlen"][g]), seq, qual, rg=None if code == NO_RG else packed.rgs[code],
+                     aux=b"")
+            sscs.append((r, g) if with_family else r)
+    return sscs, singleton
+
+
 def emit_all(reads, packed, res, scorrect=True):
     """-> (files: {name: [Read]}, stats_text, read_families_text).
 
@@ -111,18 +147,11 @@ def emit_all(reads, packed, res, scorrect=True):
                     seq, qual, rg=rg, aux=b"")
 
     # ---- SSCS stage ---------------------------------------------------------
-    sscs, singleton = [], []
-    for g in range(nf):
-        t = reads[src[tmpl[g]]]
-        qn = "%s:%d" % (family_ctag(g), size[g])
-        if size[g] == 1:
-            r = t.copy()
-            r.qname = qn
-            singleton.append(_Out(r, g))
-        else:
-            sscs.append(_Out(consensus_record(g, qn, res.sscs_rows, res.sscs_row[g], int(res.fam_mapq[g]),
-                                              int(res.fam_tlen[g]), int(res.fam_flag[g]),
-                                              rg_of(res.fam_rg[g]), t), g))
+    arrays = {k: getattr(res, k) for k in ("fam_size", "fam_tmpl", "fam_mapq", "fam_flag", "fam_tlen", "fam_rg",
+                                           "sscs_row", "sscs_rows", "read_fam")}
+    sscs_pairs, singleton_pairs = sscs_stage_records(reads, packed, arrays, lpad, with_family=True)
+    sscs = [_Out(r, g) for r, g in sscs_pairs]
+    singleton = [_Out(r, g) for r, g in singleton_pairs]
     sscs_sorted, singleton_sorted = _sorted(sscs), _sorted(singleton)
 
     def dcs_stage(inp, in_set, row_of, rows, mq, fl, tl, rgc):
