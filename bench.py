@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--cpu-pairs", type=int, default=CPU_SAMPLE_PAIRS, help="read pairs of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"],
+                    help="c2 = BASELINE.json configs[1] (the bench line); c3 / c4: panel / WGS-like batches for profiling")
     return ap.parse_args()
 
 
@@ -213,7 +215,10 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     build.build_lib()
 
-    batch = generate_device(seed=1234 + rank, n_pairs=args.pairs, L=L, device=str(dev))
+    gen_kw = {"c2": {},
+              "c3": dict(dist="lognormal", fam_mean=12.0, region=(0, 200_000), umi_len=4, p_duplex=0.9),
+              "c4": dict(dist="wgs", p_duplex=0.3, region=(0, 240_000_000))}[args.workload]
+    batch = generate_device(seed=1234 + rank, n_pairs=args.pairs, L=L, device=str(dev), **gen_kw)
     n_reads = batch.n
     eng = GpuConsensus(local, cutoff=CUTOFF, scorrect=True)
     stream = torch.cuda.current_stream(dev)
@@ -395,7 +400,7 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": workload_config(args.pairs), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
+            "config": dict(workload_config(args.pairs), **({} if args.workload == "c2" else {"workload": "profiling batch " + args.workload})), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu,
             "counts": {k: int(v) for k, v in counts.items()},
             "stats": {"sscs": int(stats_once[0]), "singletons": int(stats_once[1]), "dcs": int(stats_once[2]),

@@ -13,7 +13,10 @@
 namespace ccgpu {
 
 constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 8;
+#ifndef SCAN_ITEMS_CFG
+#define SCAN_ITEMS_CFG 32
+#endif
+constexpr int SCAN_ITEMS = SCAN_ITEMS_CFG;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 struct ScanScratch {
@@ -76,23 +79,31 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
         if (k < warp) warp_off += t;
         block_total += t;
     }
-    if (tid == 0) {
+    if (warp == 0) {
+        // look-back by a whole warp: 32 predecessors per round, nearest first
         uint32_t excl = 0;
-        if (tile == 0) {
-            st_status(&status[0], (2ull << 32) | block_total);
-        } else {
-            st_status(&status[tile], (1ull << 32) | block_total);
-            for (int64_t p = (int64_t)tile - 1;; --p) {
-                unsigned long long s;
-                do { s = ld_status(&status[p]); } while ((s >> 32) == 0);
-                excl += (uint32_t)s;
-                if ((s >> 32) == 2) break;
+        if (tile != 0) {
+            if (lane == 0) st_status(&status[tile], (1ull << 32) | block_total);
+            for (int64_t p = (int64_t)tile - 1;; p -= 32) {
+                const int64_t idx = p - lane;
+                unsigned long long s = idx >= 0 ? ld_status(&status[idx]) : (2ull << 32);   // before tile 0: prefix 0
+                while (__any_sync(0xffffffffu, (s >> 32) == 0))
+                    if ((s >> 32) == 0) s = ld_status(&status[idx]);
+                const uint32_t done = __ballot_sync(0xffffffffu, (s >> 32) == 2);
+                const int first = done ? __ffs(done) - 1 : 31;          // nearest tile that already knows its prefix
+                uint32_t v = lane <= first ? (uint32_t)s : 0u;
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+                excl += v;
+                if (done) break;
             }
-            st_status(&status[tile], (2ull << 32) | (uint32_t)(excl + block_total));
         }
-        s_prefix = excl;
-        if (total != nullptr && tile == gridDim.x - 1)
-            *total = excl + block_total;      // the last tile publishes the grand total
+        if (lane == 0) {
+            st_status(&status[tile], (2ull << 32) | (uint32_t)(excl + block_total));
+            s_prefix = excl;
+            if (total != nullptr && tile == gridDim.x - 1)
+                *total = excl + block_total;  // the last tile publishes the grand total
+        }
     }
     __syncthreads();
     uint32_t run = s_prefix + warp_off + (incl - sum);
