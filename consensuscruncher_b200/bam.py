@@ -232,27 +232,32 @@ def read_bam(path):
     n = len(data)
     view = np.frombuffer(data, np.uint8)
     while off + 4 <= n:
-        block_size = struct.unpack_from("<i", data, off)[0]
-        (tid, pos, l_name, mapq, _bin, n_cig, flag, l_seq, mtid, mpos, tlen) = struct.unpack_from(
-            "<iiBBHHHiiii", data, off + 4)
-        p = off + 36
-        qname = data[p:p + l_name - 1].decode()
-        p += l_name
-        cigar = _cigar_string(struct.unpack_from("<%dI" % n_cig, data, p)) if n_cig else ""
-        p += 4 * n_cig
-        packed = view[p:p + (l_seq + 1) // 2]
-        codes = np.empty(2 * len(packed), np.uint8)
-        codes[0::2] = packed >> 4
-        codes[1::2] = packed & 15
-        seq = _SEQ_LUT[codes[:l_seq]].tobytes().decode()
-        p += (l_seq + 1) // 2
-        qual = view[p:p + l_seq].copy()
-        p += l_seq
-        aux = data[p:off + 4 + block_size]
-        reads.append(Read(qname, flag, tid, pos, mapq, cigar, mtid, mpos, tlen, seq, qual,
-                          rg=_find_rg(aux), aux=_strip_rg(aux)))
-        off += 4 + block_size
+        r, off = decode_record(data, view, off)
+        reads.append(r)
     return header, reads
+
+
+def decode_record(data, view, off):
+    """The alignment record whose block_size field sits at `off` -> (Read, offset of the next one)."""
+    block_size = struct.unpack_from("<i", data, off)[0]
+    (tid, pos, l_name, mapq, _bin, n_cig, flag, l_seq, mtid, mpos, tlen) = struct.unpack_from(
+        "<iiBBHHHiiii", data, off + 4)
+    p = off + 36
+    qname = bytes(data[p:p + l_name - 1]).decode()
+    p += l_name
+    cigar = _cigar_string(struct.unpack_from("<%dI" % n_cig, data, p)) if n_cig else ""
+    p += 4 * n_cig
+    packed = view[p:p + (l_seq + 1) // 2]
+    codes = np.empty(2 * len(packed), np.uint8)
+    codes[0::2] = packed >> 4
+    codes[1::2] = packed & 15
+    seq = _SEQ_LUT[codes[:l_seq]].tobytes().decode()
+    p += (l_seq + 1) // 2
+    qual = view[p:p + l_seq].copy()
+    p += l_seq
+    aux = bytes(data[p:off + 4 + block_size])
+    return (Read(qname, flag, tid, pos, mapq, cigar, mtid, mpos, tlen, seq, qual,
+                 rg=_find_rg(aux), aux=_strip_rg(aux)), off + 4 + block_size)
 
 
 def encode_record(r: Read) -> bytes:

@@ -44,5 +44,22 @@ def build_lib(force=False, verbose=False):
     return LIB
 
 
+PACK_LIB = os.path.join(HERE, "libccpack.so")
+PACK_SRC = os.path.join(CSRC, "ccpack.cpp")
+
+
+def build_pack_lib(force=False):
+    """Compile csrc/ccpack.cpp (host-only: BGZF inflate + packing) into libccpack.so."""
+    if not force and os.path.exists(PACK_LIB) and os.path.getmtime(PACK_LIB) >= os.path.getmtime(PACK_SRC):
+        return PACK_LIB
+    cxx = shutil.which("g++") or "g++"
+    cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", "-o", PACK_LIB, PACK_SRC, "-lz", "-lpthread"]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    if out.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + out.stdout + out.stderr)
+    return PACK_LIB
+
+
 if __name__ == "__main__":
     print(build_lib(force=True, verbose=True))
+    print(build_pack_lib(force=True))

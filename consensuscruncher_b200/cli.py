@@ -27,7 +27,7 @@ import os
 import sys
 import time
 
-from . import bam, emit, keys, pack
+from . import bam, emit, fastpack, keys, pack
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -65,9 +65,9 @@ def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bd
     identifier = os.path.basename(bam_path).split(".bam", 1)[0]
     sample_dir = os.path.join(out_dir, identifier)
     os.makedirs(os.path.join(sample_dir, "sscs"))          # like the reference: fails if it exists (Q19)
-    header, reads = bam.read_bam(bam_path)
+    header, reads = fastpack.open_bam(bam_path)            # native inflate + pack; records decode lazily
     regions = None if bedfile in (None, "False", False) else regions_from_bed(bedfile, header)
-    packed = pack.pack_reads(reads, "sscs", bdelim, regions)
+    packed = fastpack.pack_reads(reads, "sscs", bdelim, regions)
     t_pack = time.time()
     own = engine is None
     eng = engine or GpuConsensus(device, cutoff=cutoff, scorrect=scorrect)

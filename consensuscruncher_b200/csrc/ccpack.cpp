@@ -1,0 +1,470 @@
+// libccpack.so - native host side of the packing step (no CUDA): BGZF inflate on all cores,
+// BAM record index, and the filter / mate-pairing / dictionary-encoding half of read_bam
+// (consensus_helper.py:376-441) straight into the SoA that libccgpu.so consumes.
+// It produces byte-for-byte what consensuscruncher_b200/pack.py:pack_reads produces
+// (tests/test_fastpack.py); pack.py remains the readable statement of the rules.
+// Build: g++ -O2 -std=c++17 -shared -fPIC ccpack.cpp -lz -lpthread
+#include <zlib.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <string_view>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+namespace {
+
+struct Fields {            // cc_fields of include/ccgpu.h
+    uint32_t bc, cig;
+    int32_t tid, pos, mtid, mpos, tlen;
+    uint16_t flag;
+    uint8_t mapq, rg;
+};
+static_assert(sizeof(Fields) == 32, "cc_fields is 32 bytes");
+
+inline uint32_t rd32(const uint8_t *p) { uint32_t v; memcpy(&v, p, 4); return v; }
+inline int32_t rdi32(const uint8_t *p) { int32_t v; memcpy(&v, p, 4); return v; }
+inline uint16_t rd16(const uint8_t *p) { uint16_t v; memcpy(&v, p, 2); return v; }
+
+void set_err(char *err, int len, const std::string &msg)
+{
+    if (err && len > 0) snprintf(err, len, "%s", msg.c_str());
+}
+
+}  // namespace
+
+struct ccp_bam {
+    std::vector<uint8_t> data;            // the whole uncompressed BAM stream
+    std::string text;
+    std::vector<std::string> ref_names;
+    std::vector<int32_t> ref_lens;
+    std::vector<uint64_t> offsets;        // offset of every record's block_size field
+};
+
+struct ccp_pack {
+    std::vector<Fields> fields;
+    std::vector<uint8_t> payload;
+    std::vector<int64_t> src;
+    std::vector<int32_t> lens;
+    std::vector<int64_t> bad, leftover;
+    std::vector<uint32_t> dup_bc;
+    std::string barcodes, cigars, rgs;    // NUL-separated dictionaries in id order
+    uint32_t n_bc = 0, n_cig = 0, n_rg = 0, lpad = 32, stride = 64;
+    int64_t counters[5] = {0, 0, 0, 0, 0};   // total, unmapped, unmapped_mate, multiple_mapping, bad_spacer
+};
+
+namespace {
+
+struct Block { uint64_t coff, clen, uoff, ulen; };
+
+bool inflate_block(const uint8_t *src, uint64_t clen, uint8_t *dst, uint64_t ulen)
+{
+    z_stream zs;
+    memset(&zs, 0, sizeof(zs));
+    if (inflateInit2(&zs, -15) != Z_OK) return false;
+    zs.next_in = const_cast<uint8_t *>(src);
+    zs.avail_in = (uInt)clen;
+    zs.next_out = dst;
+    zs.avail_out = (uInt)ulen;
+    int rc = inflate(&zs, Z_FINISH);
+    inflateEnd(&zs);
+    return rc == Z_STREAM_END && zs.total_out == ulen;
+}
+
+}  // namespace
+
+extern "C" {
+
+ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
+{
+    FILE *fh = fopen(path, "rb");
+    if (!fh) { set_err(err, errlen, std::string("cannot open ") + path); return nullptr; }
+    fseek(fh, 0, SEEK_END);
+    long size = ftell(fh);
+    fseek(fh, 0, SEEK_SET);
+    std::vector<uint8_t> comp((size_t)size);
+    if (size && fread(comp.data(), 1, (size_t)size, fh) != (size_t)size) {
+        fclose(fh);
+        set_err(err, errlen, "short read");
+        return nullptr;
+    }
+    fclose(fh);
+    // block table: the BC extra field gives the compressed size, the trailer the uncompressed one
+    std::vector<Block> blocks;
+    uint64_t off = 0, total = 0;
+    while (off + 18 <= (uint64_t)size) {
+        const uint8_t *p = comp.data() + off;
+        if (!(p[0] == 0x1f && p[1] == 0x8b && p[2] == 8 && (p[3] & 4))) { set_err(err, errlen, "not a BGZF block"); return nullptr; }
+        uint32_t xlen = rd16(p + 10), bsize = 0;
+        bool found = false;
+        for (uint32_t q = 0; q + 4 <= xlen;) {
+            uint32_t slen = rd16(p + 12 + q + 2);
+            if (p[12 + q] == 'B' && p[12 + q + 1] == 'C') { bsize = rd16(p + 12 + q + 4); found = true; }
+            q += 4 + slen;
+        }
+        if (!found || off + bsize + 1 > (uint64_t)size) { set_err(err, errlen, "damaged BGZF block"); return nullptr; }
+        uint64_t blen = (uint64_t)bsize + 1;
+        uint32_t isize = rd32(p + blen - 4);
+        blocks.push_back({off + 12 + xlen, blen - 12 - xlen - 8, total, isize});
+        total += isize;
+        off += blen;
+    }
+    ccp_bam *b = new ccp_bam();
+    b->data.resize(total);
+    std::atomic<size_t> next{0};
+    std::atomic<bool> ok{true};
+    int nt = std::max(1, std::min(threads, 64));
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; t++)
+        pool.emplace_back([&]() {
+            for (size_t i; (i = next.fetch_add(1)) < blocks.size();) {
+                const Block &k = blocks[i];
+                if (k.ulen && !inflate_block(comp.data() + k.coff, k.clen, b->data.data() + k.uoff, k.ulen)) ok = false;
+            }
+        });
+    for (auto &t : pool) t.join();
+    if (!ok) { delete b; set_err(err, errlen, "inflate failed"); return nullptr; }
+    const uint8_t *d = b->data.data();
+    const uint64_t n = b->data.size();
+    if (n < 12 || memcmp(d, "BAM\1", 4) != 0) { delete b; set_err(err, errlen, "not a BAM file"); return nullptr; }
+    uint32_t l_text = rd32(d + 4);
+    b->text.assign(reinterpret_cast<const char *>(d + 8), strnlen(reinterpret_cast<const char *>(d + 8), l_text));
+    uint64_t p = 8 + (uint64_t)l_text;
+    uint32_t n_ref = rd32(d + p);
+    p += 4;
+    for (uint32_t i = 0; i < n_ref; i++) {
+        uint32_t l_name = rd32(d + p);
+        b->ref_names.emplace_back(reinterpret_cast<const char *>(d + p + 4), l_name ? l_name - 1 : 0);
+        b->ref_lens.push_back(rdi32(d + p + 4 + l_name));
+        p += 8 + l_name;
+    }
+    while (p + 4 <= n) {
+        b->offsets.push_back(p);
+        p += 4 + (uint64_t)rd32(d + p);
+    }
+    return b;
+}
+
+void ccp_bam_close(ccp_bam *b) { delete b; }
+uint64_t ccp_bam_n_records(ccp_bam *b) { return b->offsets.size(); }
+const uint8_t *ccp_bam_data(ccp_bam *b, uint64_t *len) { *len = b->data.size(); return b->data.data(); }
+const uint64_t *ccp_bam_offsets(ccp_bam *b) { return b->offsets.data(); }
+const char *ccp_bam_header_text(ccp_bam *b) { return b->text.c_str(); }
+int ccp_bam_n_refs(ccp_bam *b) { return (int)b->ref_names.size(); }
+const char *ccp_bam_ref_name(ccp_bam *b, int i) { return b->ref_names[i].c_str(); }
+int32_t ccp_bam_ref_len(ccp_bam *b, int i) { return b->ref_lens[i]; }
+
+}  // extern "C"
+
+// ---- record access and the key helpers of consensus_helper.py ------------------------------------
+namespace {
+
+struct Rec {
+    const uint8_t *p;       // points at block_size
+    int32_t tid() const { return rdi32(p + 4); }
+    int32_t pos() const { return rdi32(p + 8); }
+    uint32_t l_name() const { return p[12]; }
+    uint8_t mapq() const { return p[13]; }
+    uint32_t n_cigar() const { return rd16(p + 16); }
+    uint16_t flag() const { return rd16(p + 18); }
+    uint32_t l_seq() const { return rd32(p + 20); }
+    int32_t mtid() const { return rdi32(p + 24); }
+    int32_t mpos() const { return rdi32(p + 28); }
+    int32_t tlen() const { return rdi32(p + 32); }
+    std::string_view qname() const { return {reinterpret_cast<const char *>(p + 36), l_name() ? l_name() - 1 : 0}; }
+    const uint8_t *cigar() const { return p + 36 + l_name(); }
+    const uint8_t *seq() const { return cigar() + 4 * n_cigar(); }
+    const uint8_t *qual() const { return seq() + (l_seq() + 1) / 2; }
+    const uint8_t *aux() const { return qual() + l_seq(); }
+    const uint8_t *end() const { return p + 4 + rd32(p); }
+};
+
+std::string cigar_string(const Rec &r)
+{
+    static const char ops[] = "MIDNSHP=X";
+    std::string s;
+    for (uint32_t i = 0; i < r.n_cigar(); i++) {
+        uint32_t w = rd32(r.cigar() + 4 * i);
+        s += std::to_string(w >> 4);
+        s += ops[w & 15];
+    }
+    return s;
+}
+
+// which_read (consensus_helper.py:57-81): 1 = R1, 2 = R2, 0 = none of the 16 paired flags
+int read_number(uint16_t f)
+{
+    switch (f) {
+    case 99: case 83: case 67: case 115: case 81: case 97: case 65: case 113: return 1;
+    case 147: case 163: case 131: case 179: case 161: case 145: case 129: case 177: return 2;
+    default: return 0;
+    }
+}
+
+// which_strand (consensus_helper.py:84-155): 1 = pos, 0 = neg
+int strand_of(const Rec &r)
+{
+    uint16_t f = r.flag();
+    if (f == 99 || f == 147 || f == 67 || f == 131) return 1;
+    if (f == 83 || f == 163 || f == 115 || f == 179) return 0;
+    bool first = read_number(f) == 1;
+    if (r.tid() != r.mtid()) return ((r.tid() < r.mtid()) == first) ? 1 : 0;
+    if (r.pos() == r.mpos()) return 0;
+    return ((r.pos() < r.mpos()) == first) ? 1 : 0;
+}
+
+bool is_mate_unmapped_flag(uint16_t f) { return f == 73 || f == 89 || f == 121 || f == 153 || f == 185 || f == 137; }
+
+// value of the RG:Z tag, empty view with data() == nullptr when absent
+std::string_view find_rg(const Rec &r)
+{
+    const uint8_t *p = r.aux(), *e = r.end();
+    auto size_of = [](char t) { return t == 'A' || t == 'c' || t == 'C' ? 1 : t == 's' || t == 'S' ? 2 : 4; };
+    while (p + 3 <= e) {
+        char t = (char)p[2];
+        const uint8_t *v = p + 3;
+        if (t == 'Z' || t == 'H') {
+            const uint8_t *z = v;
+            while (z < e && *z) z++;
+            if (p[0] == 'R' && p[1] == 'G' && t == 'Z') return {reinterpret_cast<const char *>(v), (size_t)(z - v)};
+            p = z + 1;
+        } else if (t == 'B') {
+            uint32_t cnt = rd32(v + 1);
+            p = v + 5 + (size_t)cnt * size_of((char)v[0]);
+        } else {
+            p = v + size_of(t);
+        }
+    }
+    return {};
+}
+
+std::string duplex_barcode(const std::string &b)
+{
+    size_t dot = b.find('.');
+    if (dot != std::string::npos) return b.substr(dot + 1) + "." + b.substr(0, dot);
+    size_t h = b.size() / 2;
+    return b.substr(h) + b.substr(0, h);
+}
+
+struct Dict {
+    std::unordered_map<std::string, uint32_t> ids;
+    std::vector<std::string> names;
+    uint32_t get(const std::string &s)
+    {
+        auto it = ids.find(s);
+        if (it != ids.end()) return it->second;
+        uint32_t id = (uint32_t)names.size();
+        ids.emplace(s, id);
+        names.push_back(s);
+        return id;
+    }
+    std::string joined() const
+    {
+        std::string out;
+        for (auto &n : names) { out += n; out.push_back('\0'); }
+        return out;
+    }
+};
+
+}  // namespace
+
+// ---- pack: the rules of pack.py:pair_reads / pack_reads -------------------------------------------
+namespace {
+
+// pack.py:visit_order - record indices in the order read_bam (consensus_helper.py:376-381) sees them
+std::vector<int64_t> visit_order(const ccp_bam *b, const int32_t *regions, int n_regions)
+{
+    const uint8_t *d = b->data.data();
+    const int64_t n = (int64_t)b->offsets.size();
+    std::vector<int64_t> out;
+    if (n_regions < 0) {
+        out.resize(n);
+        for (int64_t i = 0; i < n; i++) out[i] = i;
+        return out;
+    }
+    struct Contig { std::vector<int64_t> idx; std::vector<int32_t> pos; bool sorted = true; };
+    std::unordered_map<int32_t, Contig> by_tid;
+    for (int64_t i = 0; i < n; i++) {
+        Rec r{d + b->offsets[i]};
+        Contig &c = by_tid[r.tid()];
+        if (!c.pos.empty() && c.pos.back() > r.pos()) c.sorted = false;
+        c.idx.push_back(i);
+        c.pos.push_back(r.pos());
+    }
+    for (int g = 0; g < n_regions; g++) {
+        const int32_t tid = regions[3 * g], start = regions[3 * g + 1], end = regions[3 * g + 2];
+        auto it = by_tid.find(tid);
+        if (it == by_tid.end()) continue;
+        const Contig &c = it->second;
+        if (c.sorted) {
+            size_t lo = std::lower_bound(c.pos.begin(), c.pos.end(), start) - c.pos.begin();
+            size_t hi = std::lower_bound(c.pos.begin(), c.pos.end(), end) - c.pos.begin();
+            for (size_t k = lo; k < hi; k++) out.push_back(c.idx[k]);
+        } else {
+            for (size_t k = 0; k < c.idx.size(); k++)
+                if (start <= c.pos[k] && c.pos[k] < end) out.push_back(c.idx[k]);
+        }
+    }
+    return out;
+}
+
+// qname.split(delim)[1] (sscs stage) / qname.split('_')[0] (dcs stage), consensus_helper.py:423-431
+std::string barcode_of(std::string_view q, bool sscs, std::string_view delim)
+{
+    if (!sscs) return std::string(q.substr(0, q.find('_')));
+    size_t a = q.find(delim);
+    if (a == std::string_view::npos) return std::string();
+    a += delim.size();
+    size_t e = q.find(delim, a);
+    return std::string(q.substr(a, e == std::string_view::npos ? e : e - a));
+}
+
+}  // namespace
+
+extern "C" {
+
+// stage 0 = sscs (bad reads diverted, barcode after `delim`), 1 = dcs.  regions: n_regions x
+// (tid, start, end), n_regions < 0 for file order.  nullptr + message on error; a message that
+// starts with "domain:" is pack.DomainError on the Python side.
+ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t *regions, int n_regions,
+                       int threads, char *err, int errlen)
+{
+    const bool sscs = stage == 0;
+    const std::string_view delim(delim_c ? delim_c : "");
+    const uint8_t *d = b->data.data();
+    ccp_pack *out = new ccp_pack();
+    int64_t *ct = out->counters;
+    std::vector<int64_t> order = visit_order(b, regions, n_regions);
+    struct Waiting { int64_t idx, step; };
+    std::unordered_map<std::string_view, Waiting> waiting;
+    waiting.reserve(order.size() / 2 + 16);
+    std::vector<int64_t> &src = out->src;
+    src.reserve(order.size());
+    int64_t step = 0;
+    for (int64_t i : order) {
+        Rec r{d + b->offsets[i]};
+        const uint16_t f = r.flag();
+        std::string_view q = r.qname();
+        ct[0]++;
+        bool is_bad = true;
+        if (sscs && q.find(delim) == std::string_view::npos) ct[4]++;
+        else if (f & 0x4) { ct[1]++; ct[0]--; }
+        else if (is_mate_unmapped_flag(f)) ct[2]++;
+        else if (f & 0x900) ct[3]++;
+        else is_bad = false;
+        step++;
+        if (is_bad && sscs) { out->bad.push_back(i); continue; }
+        auto it = waiting.find(q);
+        if (it == waiting.end()) { waiting.emplace(q, Waiting{i, step}); continue; }
+        src.push_back(it->second.idx);
+        src.push_back(i);
+        waiting.erase(it);
+    }
+    {
+        std::vector<Waiting> left;
+        for (auto &kv : waiting) left.push_back(kv.second);
+        std::sort(left.begin(), left.end(), [](const Waiting &x, const Waiting &y) { return x.step < y.step; });
+        for (auto &w : left) out->leftover.push_back(w.idx);
+    }
+    const int64_t n = (int64_t)src.size();
+    out->fields.resize(n);
+    out->lens.resize(n);
+    Dict bcs, cigs, rgs;
+    uint32_t max_len = 0;
+    std::string ckey;
+    for (int64_t k = 0; k < n; k += 2) {
+        Rec read{d + b->offsets[src[k]]}, mate{d + b->offsets[src[k + 1]]};
+        for (const Rec *r : {&read, &mate})
+            if (!read_number(r->flag())) {
+                set_err(err, errlen, "domain: flag " + std::to_string(r->flag()) + " of " + std::string(r->qname()) +
+                                         " is not one of the 16 paired flags the reference can key "
+                                         "(consensus_helper.py:69-70)");
+                delete out;
+                return nullptr;
+            }
+        const uint32_t bc = bcs.get(barcode_of(read.qname(), sscs, delim));
+        // cigar_order (consensus_helper.py:158-172): the read's cigar leads iff (pos and R1) or (neg and R2)
+        const bool lead = (strand_of(read) == 1) == (read_number(read.flag()) == 1);
+        ckey = lead ? cigar_string(read) + "_" + cigar_string(mate) : cigar_string(mate) + "_" + cigar_string(read);
+        const uint32_t cg = cigs.get(ckey);
+        for (int j = 0; j < 2; j++) {
+            const Rec &r = j ? mate : read;
+            Fields &f = out->fields[k + j];
+            f.bc = bc; f.cig = cg;
+            f.tid = r.tid(); f.pos = r.pos(); f.mtid = r.mtid(); f.mpos = r.mpos();
+            f.tlen = r.tlen(); f.flag = r.flag(); f.mapq = r.mapq();
+            std::string_view g = find_rg(r);
+            if (g.data() == nullptr) f.rg = 0xff;
+            else {
+                uint32_t id = rgs.get(std::string(g));
+                if (id >= 0xff) { set_err(err, errlen, "domain: more than 255 distinct read groups"); delete out; return nullptr; }
+                f.rg = (uint8_t)id;
+            }
+            out->lens[k + j] = (int32_t)r.l_seq();
+            max_len = std::max(max_len, r.l_seq());
+        }
+    }
+    out->lpad = std::max(32u, (max_len + 31) / 32 * 32);
+    out->stride = (out->lpad / 2 + out->lpad + 63) / 64 * 64;
+    out->payload.assign((size_t)n * out->stride, 0);
+    {
+        // BAM stores bases exactly as the payload wants them (4 bits, high nibble first)
+        const uint32_t lpad = out->lpad, stride = out->stride;
+        std::atomic<int64_t> next{0};
+        const int64_t chunk = 4096;
+        auto work = [&]() {
+            for (int64_t lo; (lo = next.fetch_add(chunk)) < n;)
+                for (int64_t x = lo; x < std::min(n, lo + chunk); x++) {
+                    Rec r{d + b->offsets[src[x]]};
+                    uint8_t *row = out->payload.data() + (size_t)x * stride;
+                    const uint32_t L = r.l_seq();
+                    memcpy(row, r.seq(), (L + 1) / 2);
+                    if (L & 1) row[L / 2] &= 0xf0;
+                    memcpy(row + lpad / 2, r.qual(), L);
+                }
+        };
+        int nt = std::max(1, std::min(threads, 64));
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nt; t++) pool.emplace_back(work);
+        for (auto &t : pool) t.join();
+    }
+    out->n_bc = (uint32_t)bcs.names.size();
+    out->n_cig = (uint32_t)cigs.names.size();
+    out->n_rg = (uint32_t)rgs.names.size();
+    out->dup_bc.assign(out->n_bc, 0xffffffffu);
+    for (uint32_t i = 0; i < out->n_bc; i++) {   // duplex_tag's barcode half swap (consensus_helper.py:629-639)
+        auto it = bcs.ids.find(duplex_barcode(bcs.names[i]));
+        if (it != bcs.ids.end()) out->dup_bc[i] = it->second;
+    }
+    out->barcodes = bcs.joined();
+    out->cigars = cigs.joined();
+    out->rgs = rgs.joined();
+    return out;
+}
+
+void ccp_pack_free(ccp_pack *p) { delete p; }
+uint64_t ccp_pack_n(ccp_pack *p) { return p->fields.size(); }
+void ccp_pack_geometry(ccp_pack *p, uint32_t *lpad, uint32_t *stride) { *lpad = p->lpad; *stride = p->stride; }
+const void *ccp_pack_fields(ccp_pack *p) { return p->fields.data(); }
+const uint8_t *ccp_pack_payload(ccp_pack *p) { return p->payload.data(); }
+const int64_t *ccp_pack_src(ccp_pack *p) { return p->src.data(); }
+const int32_t *ccp_pack_lens(ccp_pack *p) { return p->lens.data(); }
+const int64_t *ccp_pack_counters(ccp_pack *p) { return p->counters; }
+const int64_t *ccp_pack_bad(ccp_pack *p, uint64_t *n) { *n = p->bad.size(); return p->bad.data(); }
+const int64_t *ccp_pack_leftover(ccp_pack *p, uint64_t *n) { *n = p->leftover.size(); return p->leftover.data(); }
+const uint32_t *ccp_pack_dup_bc(ccp_pack *p, uint32_t *n) { *n = p->n_bc; return p->dup_bc.data(); }
+// which: 0 barcodes, 1 cigar pairs, 2 read groups; NUL-separated, in id order
+const char *ccp_pack_dict(ccp_pack *p, int which, uint32_t *count, uint64_t *bytes)
+{
+    const std::string &s = which == 0 ? p->barcodes : which == 1 ? p->cigars : p->rgs;
+    *count = which == 0 ? p->n_bc : which == 1 ? p->n_cig : p->n_rg;
+    *bytes = s.size();
+    return s.data();
+}
+
+}  // extern "C"

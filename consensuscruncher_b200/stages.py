@@ -23,7 +23,7 @@ from collections import OrderedDict
 
 import numpy as np
 
-from . import bam, keys, pack
+from . import bam, fastpack, keys, pack
 from .api import row_to_seq_qual, rows_of
 from .pack import NO_RG, row_geometry
 from .records import Read, codes_to_seq
@@ -145,11 +145,11 @@ def _get_engine(engine, device=0):
 def run_sscs(infile, outfile, cutoff, bdelim="|", bedfile=None, engine=None):
     t0 = time.time()
     from .emit import sscs_stage_records
-    header, reads = bam.read_bam(infile)
+    header, reads = fastpack.open_bam(infile)
     regions = None
     if bedfile is not None:
         regions = [(tid, a, b) for _, _, tid, a, b in _regions(bedfile, header)]
-    packed = pack.pack_reads(reads, "sscs", bdelim, regions)
+    packed = fastpack.pack_reads(reads, "sscs", bdelim, regions)
     eng, own = _get_engine(engine)
     try:
         eng.set_params(cutoff=cutoff, scorrect=False)
