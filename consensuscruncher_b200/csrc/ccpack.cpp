@@ -413,7 +413,7 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
     out->stride = (out->lpad / 2 + out->lpad + 63) / 64 * 64;
     out->payload.assign((size_t)n * out->stride, 0);
     {
-        // BAM stores bases exactly as the payload wants them (4 bits, high nibble first)
+        // BAM's 4-bit codes with the nibbles of every byte swapped (payload: even position low)
         const uint32_t lpad = out->lpad, stride = out->stride;
         std::atomic<int64_t> next{0};
         const int64_t chunk = 4096;
@@ -423,8 +423,9 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
                     Rec r{d + b->offsets[src[x]]};
                     uint8_t *row = out->payload.data() + (size_t)x * stride;
                     const uint32_t L = r.l_seq();
-                    memcpy(row, r.seq(), (L + 1) / 2);
-                    if (L & 1) row[L / 2] &= 0xf0;
+                    const uint8_t *sq = r.seq();
+                    for (uint32_t y = 0; y < L / 2; y++) row[y] = (uint8_t)((sq[y] << 4) | (sq[y] >> 4));
+                    if (L & 1) row[L / 2] = (uint8_t)(sq[L / 2] >> 4);
                     memcpy(row + lpad / 2, r.qual(), L);
                 }
         };

@@ -360,10 +360,10 @@ struct VoteAcc {
 
 __device__ __forceinline__ uint32_t expand_nibbles(uint32_t s16)
 {
-    // s16 = two sequence bytes (4 bases, high nibble first) -> one base per byte, position order
-    uint32_t hi = (s16 >> 4) & 0x0F0Fu;      // positions 0 and 2
-    uint32_t lo = s16 & 0x0F0Fu;             // positions 1 and 3
-    return __byte_perm(hi, lo, 0x5140);
+    // s16 = two sequence bytes (4 bases, even position in the low nibble) -> one base per byte, position order
+    uint32_t lo = s16 & 0x0F0Fu;             // positions 0 and 2
+    uint32_t hi = (s16 >> 4) & 0x0F0Fu;      // positions 1 and 3
+    return __byte_perm(lo, hi, 0x5140);
 }
 
 __device__ __forceinline__ void vote_row(VoteAcc &a, uint32_t q, uint32_t s16, uint32_t &err)
@@ -475,8 +475,8 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
                 uint32_t mq = best == 0 ? 0u : (best == 1 ? min(qw, (uint32_t)Q_CAP) : (uint32_t)Q_CAP);
                 uint32_t code = 15u;
                 if (pass != 0 && ((double)best / (double)pass) >= cutoff) code = 1u << w;
-                // positions 0,1 -> first sequence byte (high, low nibble); 2,3 -> second byte
-                seq_out |= code << ((k >> 1) * 8 + ((k & 1) ? 0 : 4));
+                // positions 0,1 -> first sequence byte (low, high nibble); 2,3 -> second byte
+                seq_out |= code << ((k >> 1) * 8 + ((k & 1) ? 4 : 0));
                 q_out |= mq << (8 * k);
             }
             *reinterpret_cast<uint16_t *>(out + (p0 >> 1)) = (uint16_t)seq_out;

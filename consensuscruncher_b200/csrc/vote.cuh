@@ -96,8 +96,8 @@ __device__ __forceinline__ uint32_t prmt(uint32_t lo, uint32_t hi, uint32_t sele
 }
 
 // A quad is 4 consecutive positions = 2 sequence bytes = one 16-bit group of 4 base codes.  That
-// group is used directly as a PRMT selector, so a quad's byte lanes are in nibble order:
-// lane 0 <-> position 1, lane 1 <-> position 0, lane 2 <-> position 3, lane 3 <-> position 2.
+// group is used directly as a PRMT selector: the payload keeps the even position of a byte in the
+// LOW nibble, so selector nibble i, byte lane i and the i-th quality byte are all position i.
 struct Quad {
     uint32_t ac;        // per byte lane: count of A in the low nibble, of C in the high nibble
     uint32_t gt;        // per byte lane: count of G plus T in the low nibble, of T in the high nibble
@@ -131,7 +131,7 @@ __device__ __forceinline__ void quad_flush(Quad &a)
     a.ac = 0; a.gt = 0;
 }
 
-// 4 base codes of a 16-bit group, one per byte lane (nibble order)
+// 4 base codes of a 16-bit group, one per byte lane (position order)
 __device__ __forceinline__ uint32_t expand_sel(uint32_t sel16)
 {
     return __byte_perm(sel16 & 0x0F0Fu, (sel16 >> 4) & 0x0F0Fu, 0x5140);
@@ -225,12 +225,11 @@ __device__ __forceinline__ LaneRow load_lane_row(const uint8_t *__restrict__ pay
     return r;
 }
 
-// quads of a lane: positions 0-3, 4-7, 8-11, 12-15, each in nibble order (see Quad)
+// quads of a lane: positions 0-3, 4-7, 8-11, 12-15 (see Quad)
 __device__ __forceinline__ void split_row(const LaneRow &r, uint32_t sel[4], uint32_t q[4])
 {
     sel[0] = r.s.x; sel[1] = r.s.x >> 16; sel[2] = r.s.y; sel[3] = r.s.y >> 16;     // PRMT reads the low 16 bits
-    q[0] = __byte_perm(r.q.x, 0, 0x2301); q[1] = __byte_perm(r.q.y, 0, 0x2301);
-    q[2] = __byte_perm(r.q.z, 0, 0x2301); q[3] = __byte_perm(r.q.w, 0, 0x2301);
+    q[0] = r.q.x; q[1] = r.q.y; q[2] = r.q.z; q[3] = r.q.w;
 }
 
 // consensus codes / qualities of the 4 quads -> the lane's 8 sequence bytes and 16 quality bytes
@@ -240,8 +239,7 @@ __device__ __forceinline__ void join_row(const uint32_t code[4], const uint32_t 
     uint32_t x2 = code[2] | (code[2] >> 4), x3 = code[3] | (code[3] >> 4);
     so.x = __byte_perm(x0, x1, 0x6420);
     so.y = __byte_perm(x2, x3, 0x6420);
-    qo.x = __byte_perm(qual[0], 0, 0x2301); qo.y = __byte_perm(qual[1], 0, 0x2301);
-    qo.z = __byte_perm(qual[2], 0, 0x2301); qo.w = __byte_perm(qual[3], 0, 0x2301);
+    qo.x = qual[0]; qo.y = qual[1]; qo.z = qual[2]; qo.w = qual[3];
 }
 
 // mode of one field over a family held by a lane group (slow path: fields differ inside the family)

@@ -17,9 +17,12 @@ Layout handed to the device (also described in DESIGN.md):
                 i32 tlen ; u16 flag ; u8 mapq ; u8 rg (0xff = no RG tag)
               The family key of `unique_tag` (`:293-301`) is the first 24 bytes
               plus flag bits 0x10 (orientation) and 0x40/0x80 (read number).
-  payload[N]  `stride` bytes per read: lpad/2 bytes of BAM 4-bit bases (high
-              nibble first, zero padded) followed by lpad quality bytes (zero
-              padded), lpad = L rounded up to 32, stride a multiple of 64.
+  payload[N]  `stride` bytes per read: lpad/2 bytes of BAM 4-bit base codes, two
+              per byte with the EVEN position in the LOW nibble (BAM itself
+              has it in the high nibble; the swap makes nibble i of a 16-bit
+              group position i, which the vote kernel uses as a PRMT selector),
+              zero padded, followed by lpad quality bytes (zero padded),
+              lpad = L rounded up to 32, stride a multiple of 64.
   dup_bc[B]   barcode id of the complementary strand's barcode (`duplex_tag`,
               `:629-639`), 0xffffffff when that barcode never occurs.
 """
@@ -54,7 +57,7 @@ def pack_row(codes, qual, lpad, out):
     n = len(codes)
     c = np.zeros(lpad, np.uint8)
     c[:n] = codes
-    out[:lpad // 2] = (c[0::2] << 4) | c[1::2]
+    out[:lpad // 2] = c[0::2] | (c[1::2] << 4)
     out[lpad // 2:lpad // 2 + n] = qual
     out[lpad // 2 + n:] = 0
 
@@ -63,8 +66,8 @@ def unpack_row(row, lpad, n):
     """Inverse of `pack_row`: (codes u8[n], qual u8[n])."""
     s = row[:lpad // 2]
     codes = np.empty(lpad, np.uint8)
-    codes[0::2] = s >> 4
-    codes[1::2] = s & 15
+    codes[0::2] = s & 15
+    codes[1::2] = s >> 4
     return codes[:n].copy(), row[lpad // 2:lpad // 2 + n].copy()
 
 

@@ -10,8 +10,8 @@ from __future__ import annotations
 
 import numpy as np
 
-# BAM 4-bit base codes ("=ACMGRSVTWYHKDBN"): the device payload keeps BAM's own
-# nibble layout, so A/C/G/T are one-hot (1,2,4,8) and N is 15.
+# BAM 4-bit base codes ("=ACMGRSVTWYHKDBN"): the device payload keeps BAM's codes
+# (A/C/G/T one-hot 1,2,4,8, N = 15) with the even position in the low nibble.
 BASE_CODES = "=ACMGRSVTWYHKDBN"
 _CODE_OF = np.full(256, 255, dtype=np.uint8)
 for _i, _c in enumerate(BASE_CODES):

@@ -131,7 +131,7 @@ class SynthReads:
         payload = np.zeros((n, stride), np.uint8)
         c = np.zeros((n, lpad), np.uint8)
         c[:, :self.L] = self.codes[s]
-        payload[:, :lpad // 2] = (c[:, 0::2] << 4) | c[:, 1::2]
+        payload[:, :lpad // 2] = c[:, 0::2] | (c[:, 1::2] << 4)
         payload[:, lpad // 2:lpad // 2 + self.L] = self.qual[s]
         cig = "%dM_%dM" % (self.L, self.L)
         return PackedReads(fields, payload, lpad, barcodes, dup_bc, [cig],

@@ -163,7 +163,7 @@ def generate_device(seed=1234, n_pairs=10_000_000, L=128, umi_len=2, dist="ztpoi
         c = torch.zeros((k, lpad), dtype=torch.uint8, device=dev)
         c[:, :L] = codes
         rows = payload[2 * p0:2 * p1]
-        rows[:, :lpad // 2] = (c[:, 0::2] << 4) | c[:, 1::2]
+        rows[:, :lpad // 2] = c[:, 0::2] | (c[:, 1::2] << 4)
         rows[:, lpad // 2:lpad // 2 + L] = qual
     if dev.type == "cuda":
         torch.cuda.synchronize(dev)

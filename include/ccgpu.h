@@ -23,7 +23,8 @@
  *   reads are in pair-completion order, read 2k = first-seen mate of pair k,
  *   read 2k+1 = second-seen mate.
  *   fields   n x 32-byte cc_fields records
- *   payload  n x stride bytes: lpad/2 bytes of BAM 4-bit bases (high nibble first),
+ *   payload  n x stride bytes: lpad/2 bytes of BAM 4-bit base codes, two per byte with
+ *            the EVEN position in the LOW nibble (the nibbles of BAM's own bytes swapped),
  *            then lpad quality bytes, zero padded; lpad % 32 == 0, stride % 64 == 0,
  *            stride >= 3*lpad/2
  *   dup_bc   n_bc x u32: barcode id of the complementary strand's barcode

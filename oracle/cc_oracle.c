@@ -171,14 +171,14 @@ static int group(cco_ctx *c)
 static inline int base_at(const uint8_t *row, uint32_t i)
 {
     uint8_t b = row[i >> 1];
-    return (i & 1) ? (b & 15) : (b >> 4);
+    return (i & 1) ? (b >> 4) : (b & 15);          /* even position in the low nibble */
 }
 
 static inline void set_base(uint8_t *row, uint32_t i, int code)
 {
     uint8_t *b = &row[i >> 1];
-    if (i & 1) *b = (uint8_t)((*b & 0xF0) | code);
-    else *b = (uint8_t)((*b & 0x0F) | (code << 4));
+    if (i & 1) *b = (uint8_t)((*b & 0x0F) | (code << 4));
+    else *b = (uint8_t)((*b & 0xF0) | code);
 }
 
 /* ---- SSCS vote: SSCS_maker.py:103-155 ------------------------------------------ */
