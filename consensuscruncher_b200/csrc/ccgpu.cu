@@ -440,7 +440,7 @@ int launch_vote_small(cc_ctx *ctx, uint32_t rows, uint32_t n_lo, uint32_t n_hi, 
         ptr<uint32_t>(ctx->sscs_list), row_list, rows, n_lo, n_hi, ptr<uint8_t>(ctx->thr_table),
         (1.0 >= ctx->params.cutoff) ? 1 : 0, ctx->thr_magic, ctx->fields, ptr<uint8_t>(ctx->sscs_rows),
         ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
-        ptr<uint32_t>(ctx->counters) + CT_ERR);
+        ptr<uint32_t>(ctx->counters) + CT_ERR, ptr<uint32_t>(ctx->big_list), ptr<uint32_t>(ctx->counters) + CT_NBIG);
     ctx->launches++;
     CK(cudaGetLastError());
     return CC_OK;
@@ -451,9 +451,9 @@ int launch_vote_small(cc_ctx *ctx, uint32_t rows, uint32_t n_lo, uint32_t n_hi, 
 template <int G>
 int launch_vote_pair(cc_ctx *ctx, uint32_t rows)
 {
-    TRY((launch_vote_small<G, 1, 3, false>(ctx, rows, 2, 15, nullptr)));
+    TRY((launch_vote_small<G, 1, VOTE_DEPTH_CFG, false>(ctx, rows, 2, 15, nullptr)));
     const uint32_t n_mid = ctx->host_ctr[CT_NMID];       // counted by family_build_kernel, listed by vote_segments_kernel
-    if (n_mid) TRY((launch_vote_small<G, 1, 3, true>(ctx, n_mid, 16, VOTE_SMALL_MAX, ptr<uint32_t>(ctx->mid_list))));
+    if (n_mid) TRY((launch_vote_small<G, 1, VOTE_DEPTH_CFG, true>(ctx, n_mid, 16, VOTE_SMALL_MAX, ptr<uint32_t>(ctx->mid_list))));
     return CC_OK;
 }
 

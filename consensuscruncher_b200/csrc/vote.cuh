@@ -20,16 +20,22 @@
 #include "kernels.cuh"
 
 #ifndef VOTE_DEPTH_CFG
-#define VOTE_DEPTH_CFG 3
+#define VOTE_DEPTH_CFG 2
+#endif
+#ifndef VOTE_FASTMASK
+#define VOTE_FASTMASK 3
 #endif
 #ifndef VOTE_BLOCKS_CFG
-#define VOTE_BLOCKS_CFG 2
+#define VOTE_BLOCKS_CFG 3
 #endif
 
 namespace ccgpu {
 
 constexpr uint32_t VOTE_SMALL_MAX = 127;     // byte-lane compares below need counts < 128
-constexpr int VOTE_ROWS_PER_BATCH = 4;       // rows per staged batch
+#ifndef VOTE_RB_CFG
+#define VOTE_RB_CFG 4
+#endif
+constexpr int VOTE_ROWS_PER_BATCH = VOTE_RB_CFG;   // rows per staged batch
 static_assert(12 % VOTE_ROWS_PER_BATCH == 0, "nibble counters are flushed every 12 reads");
 
 __device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
@@ -111,12 +117,24 @@ struct Quad {
 // (T reaches the table through PRMT's sign-replicate mode: entry 0 of the G/T table has its
 // top bit set, so selector 8 yields 0xFF, masked to 0x11).  Every other code, N and IUPAC
 // included, selects 0: it is counted in pc but in no base, which quad_finish reports.
+//
+// The pass mask assumes qualities below 128 (SAM allows 0..93): q + 98 then cannot carry into the
+// next byte.  The caller ORs the qualities it feeds in; a family that shows a byte >= 128 is voted
+// again, exactly, by vote_big_kernel (see `hi` in vote_small_kernel).
 __device__ __forceinline__ void quad_add(Quad &a, uint32_t sel16, uint32_t q, uint32_t one)
 {
-    uint32_t m = bytes_of(fadd(q & 0x7F7F7F7Fu, 0x62626262u, one) | q);    // 0xFF where q >= 30
+#if VOTE_FASTMASK & 1
+    uint32_t m = bytes_of(fadd(q, 0x62626262u, one));                       // 0xFF where q >= 30
+#else
+    uint32_t m = bytes_of(fadd(q & 0x7F7F7F7Fu, 0x62626262u, one) | q);
+#endif
     a.ac = fadd(prmt(0x00100100u, 0u, sel16) & m, a.ac, one);
     a.gt = fadd(prmt(0x00000080u, 0x00000001u, sel16) & m & 0x11111111u, a.gt, one);
+#if VOTE_FASTMASK & 2
+    a.pc = m * 0xFEFEFEFFu + a.pc;         // 0xFF bytes -> 0x01 bytes: 0xFEFEFEFF is the inverse of 255 mod 2^32
+#else
     a.pc = fadd(m & 0x01010101u, a.pc, one);
+#endif
     a.qany |= q & m;
 }
 
@@ -271,9 +289,9 @@ __device__ uint32_t group_mode(Get get, uint32_t n, bool is_flag, int gl, int G,
 //   both pass, differ   -> tie: the earlier base in A,C,G,T order with its own quality,
 //                          emitted iff 1/2 >= cutoff;  none passes -> N, 0.
 __device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t nib2, uint32_t q2, bool tie_ok,
-                                          bool unanimous_ok, uint32_t &code, uint32_t &qual, uint32_t &err)
+                                          bool unanimous_ok, uint32_t one, uint32_t &code, uint32_t &qual, uint32_t &err)
 {
-    uint32_t m1 = bytes_of(pass7_of(q1)), m2 = bytes_of(pass7_of(q2));
+    uint32_t m1 = bytes_of(fadd(q1, 0x62626262u, one)), m2 = bytes_of(fadd(q2, 0x62626262u, one));   // q < 128, as in quad_add
     uint32_t b1 = nib1 & m1, b2 = nib2 & m2;
     err |= (((b1 | 0x80808080u) - 0x01010101u) & b1) | (((b2 | 0x80808080u) - 0x01010101u) & b2);
     err |= (m1 & ~bytes_of(nz7u(b1))) | (m2 & ~bytes_of(nz7u(b2)));      // passing base that is none of A,C,G,T
@@ -288,6 +306,11 @@ __device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t n
     qual = sel(0x3C3C3C3Cu, cap60(wq), agree) & (m1 | m2);
 }
 
+// vsize[row] = family size | flags
+constexpr uint32_t VSIZE_MIXED = 0x80000000u;     // members' mode fields differ (set by vote_segments_kernel)
+constexpr uint32_t VSIZE_QUEUED = 0x40000000u;    // row already queued for the exact kernel
+constexpr uint32_t VSIZE_COUNT = 0x3FFFFFFFu;
+
 constexpr int VOTE_CHUNK = 1024;    // SSCS rows a block sorts by family size and then votes
 
 // dynamic shared memory of vote_small_kernel<G, CH, DEPTH>: the lanes' staging rings
@@ -301,15 +324,15 @@ constexpr int vote_ring_bytes(int ch, int depth) { return depth * VOTE_ROWS_PER_
 //   DEPTH  staging ring slots         FLUSH  families may exceed 15 reads (nibble counters are
 //                                            emptied into byte counters every 12 reads)
 template <int G, int CH, int DEPTH, bool FLUSH>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, VOTE_BLOCKS_CFG)
 vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t lpad,
                   const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
-                  const uint32_t *__restrict__ vsize, const uint32_t *__restrict__ sscs_list,
+                  uint32_t *vsize, const uint32_t *__restrict__ sscs_list,
                   const uint32_t *__restrict__ row_list, uint32_t n_rows, uint32_t n_lo, uint32_t n_hi,
                   const uint8_t *__restrict__ thr_table, int unanimous_ok, ThrMagic tm,
                   const uint4 *__restrict__ fields, uint8_t *__restrict__ out_rows, uint8_t *__restrict__ fam_mapq,
                   uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-                  uint32_t *__restrict__ err_flag)
+                  uint32_t *__restrict__ err_flag, uint32_t *__restrict__ redo_list, uint32_t *__restrict__ n_redo)
 {
     __shared__ uint8_t thr[128];
     __shared__ uint32_t s_start[VOTE_CHUNK];
@@ -330,8 +353,8 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
     __syncthreads();
     for (uint32_t i = tid; i < rows_here; i += 256) {
         const uint32_t r = row_list ? __ldg(&row_list[row0 + i]) : row0 + i;
-        const uint32_t v = __ldg(&vsize[r]);
-        uint32_t n = v & 0x7FFFFFFFu;
+        const uint32_t v = vsize[r];
+        uint32_t n = v & VSIZE_COUNT;
         if (n < n_lo || n > n_hi) n = 0;                   // voted by another launch (other sizes)
         s_row[i] = r;
         s_start[i] = __ldg(&vstart[r]);
@@ -448,6 +471,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
         uint8_t *out = out_rows + (uint64_t)row * stride;
 
         if (n != 0) {
+            uint32_t hi = 0, ferr = 0;                     // OR of the family's quality words; its error bits
             if (n == 2) {
                 p_issue();
                 cp_async_wait<DEPTH - 1>();
@@ -459,9 +483,10 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                         uint32_t n1[4], q1[4], n2[4], q2[4], code[4], qual[4];
                         split_row(r1, n1, q1);
                         split_row(r2, n2, q2);
+                        hi |= q1[0] | q1[1]; hi |= q1[2] | q1[3]; hi |= q2[0] | q2[1]; hi |= q2[2] | q2[3];
 #pragma unroll
                         for (int g = 0; g < 4; g++)
-                            quad_pair(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], tie_ok, unanimous_ok != 0, code[g], qual[g], err);
+                            quad_pair(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], tie_ok, unanimous_ok != 0, one, code[g], qual[g], ferr);
                         uint2 so;
                         uint4 qo;
                         join_row(code, qual, so, qo);
@@ -489,6 +514,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                                     if (h == 0 || pos0 + 16 * h < lpad) {
                                         uint32_t sel4[4], q[4];
                                         split_row(slot_row(c_slot, k, h), sel4, q);
+                                        hi |= q[0] | q[1]; hi |= q[2] | q[3];
 #pragma unroll
                                         for (int g = 0; g < 4; g++) quad_add(acc[h][g], sel4[g], q[g], one);
                                     }
@@ -512,7 +538,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                         uint32_t any_single = 0;
 #pragma unroll
                         for (int g = 0; g < 4; g++) {
-                            o[g] = quad_finish<FLUSH>(acc[h][g], thr, unanimous_ok != 0, tm, err);
+                            o[g] = quad_finish<FLUSH>(acc[h][g], thr, unanimous_ok != 0, tm, ferr);
                             any_single |= o[g].single;
                         }
                         if (any_single) {                  // lane-local: re-walk the rows for the lone supporters
@@ -541,6 +567,14 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                 }
             }
             for (uint32_t x = half + lpad + gl * 4; x < stride; x += G * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
+            // A quality byte >= 128 breaks the byte-lane pass test above (and may have raised a false
+            // error in this lane): the family goes to vote_big_kernel, which runs after this launch,
+            // tests qualities exactly and overwrites the row.
+            if (hi & 0x80808080u) {                        // first lane to flag the row queues it
+                if (!(atomicOr(&vsize[row], VSIZE_QUEUED) & VSIZE_QUEUED)) redo_list[atomicAdd(n_redo, 1u)] = row;
+            } else {
+                err |= ferr;
+            }
         }
 
         // ---- mode fields (create_aligned_segment, consensus_helper.py:569-583) -------------------
@@ -601,7 +635,7 @@ vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ pa
     const uint32_t total = *n_big;
     for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
         const uint32_t row = big_list[i];
-        vote_family_warp(fields, payload, stride, lpad, perm, vstart[row], vsize[row] & 0x7FFFFFFFu, cutoff,
+        vote_family_warp(fields, payload, stride, lpad, perm, vstart[row], vsize[row] & VSIZE_COUNT, cutoff,
                          out_rows + (uint64_t)row * stride, sscs_list[row], fam_mapq, fam_flag, fam_tlen, fam_rg,
                          err_flag);
     }

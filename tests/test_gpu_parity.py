@@ -124,6 +124,23 @@ def test_n_base_with_high_quality_is_an_error(engine):
         oracle.run(packed)
 
 
+@pytest.mark.parametrize("fam_mean,dist", [(2, "const"), (4.0, "ztpoisson"), (24, "const")])
+def test_quality_bytes_above_127_take_the_exact_path(engine, fam_mean, dist):
+    # SAM stops at Q93, BAM bytes do not: the reference counts 128..255 as passing.  The byte-lane
+    # pass test of the bulk kernel assumes q < 128 and hands such families to the exact kernel.
+    s = synth.generate(seed=75, n_molecules=300, L=128, dist=dist, fam_mean=fam_mean, p_n=0.0)
+    rng = np.random.default_rng(5)
+    hit = rng.random(s.qual.shape) < 0.004
+    s.qual[hit] = rng.choice(np.array([128, 140, 157, 158, 200, 255], np.uint8), int(hit.sum()))
+    # a failing N right after a byte that overflows: a carry would make it look like a passing N
+    rows = rng.choice(len(s.qual), 40, replace=False)
+    s.qual[rows, 40] = 255
+    s.qual[rows, 41] = 29
+    s.codes[rows, 41] = 15
+    packed = s.to_packed()
+    _both(engine, packed)
+
+
 def test_domain_fault_is_reported(engine):
     # pair 99/147 and pair 65/129 with the same UMI and coordinates: R1 tags merge, R2 tags do not (F11)
     def pair(q, f1, f2):
