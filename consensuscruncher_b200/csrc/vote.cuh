@@ -191,7 +191,8 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
     uint32_t m3 = bytes_of(ge7u(bAC, bGT));
     uint32_t best = sel(bAC, bGT, m3);
     o.win = sel(wAC, wGT, m3);
-    uint32_t sum = cA + cC + cG + cT;
+    uint32_t sum = cA + cC + (a.gt & 0x0F0F0F0Fu);         // the G+T nibble already holds cG + cT
+    if (TOTALS) sum += a.tG + a.tT;
     err |= sum ^ a.pc;                                     // a passing base that is none of A,C,G,T (N, IUPAC, '=')
     uint32_t pass = a.pc;
     uint32_t ok;
@@ -403,8 +404,12 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
     uint8_t *const ring_s = ring + DEPTH * SLOT_Q + tid * 8;                     // [depth][row][chunk][thread] uint2
     const uint32_t ring_q_sh = (uint32_t)__cvta_generic_to_shared(ring_q);
     const uint32_t ring_s_sh = (uint32_t)__cvta_generic_to_shared(ring_s);
-    const uint8_t *const lane_src = payload + (pos0 >> 1);                       // this lane's first sequence bytes of read 0
-    const uint8_t *const lane_src_q = payload + half + pos0;                     // ... and its first quality bytes
+    // this lane's first sequence / quality bytes of read 0, kept as opaque 64-bit values so that a
+    // row's address is one multiply-add (IMAD.WIDE) instead of offset arithmetic on the kernel argument
+    uint64_t lane_src_u = (uint64_t)(payload + (pos0 >> 1)), lane_src_q_u = (uint64_t)(payload + half + pos0);
+    asm volatile("" : "+l"(lane_src_u), "+l"(lane_src_q_u));
+    const uint8_t *const lane_src = (const uint8_t *)lane_src_u;
+    const uint8_t *const lane_src_q = (const uint8_t *)lane_src_q_u;
 
     // producer cursor: the batch that will be issued next
     uint32_t p_t = my_slot, p_start = 0, p_n = 0, p_j0 = 0, p_slot = 0;
