@@ -74,11 +74,12 @@ def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bd
     try:
         eng.set_params(cutoff=cutoff, scorrect=scorrect)
         res = eng.consensus(packed)
+        t_gpu = time.time()
+        # the sort / merge steps between the stages (ConsensusCruncher.py:10-29,248,282) order on the GPU
+        files, stats, fam_txt = emit.emit_all(reads, packed, res, scorrect, sorter=eng.sort_records)
     finally:
         if own:
             eng.close()
-    t_gpu = time.time()
-    files, stats, fam_txt = emit.emit_all(reads, packed, res, scorrect)
     where = {"sscs.sorted": "sscs", "singleton.sorted": "sscs", "badReads": "sscs",
              "dcs.sorted": "dcs", "sscs.singleton.sorted": "dcs",
              "sscs.correction.sorted": "sscs_sc", "singleton.correction.sorted": "sscs_sc",

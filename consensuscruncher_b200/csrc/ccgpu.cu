@@ -66,6 +66,7 @@ struct cc_ctx {
     ThrMagic thr_magic{0, 0, 1};
     bool thr_valid = false;
     DevBuf tmp_a, tmp_b, tmp_c;   // stand-alone primitives
+    DevBuf cs_in, cs_k0, cs_k1, cs_v0, cs_v1;   // cc_sort_coordinates
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
     uint32_t host_ctr[CT_COUNT];
@@ -240,6 +241,36 @@ int sort_bits_for(uint64_t n)
 }
 
 // ---- stage 1: grouping ----------------------------------------------------------------------
+// Stable LSD sort of n (u32 key, u32 value) pairs on the low 8 * passes key bits (radix_onesweep.cuh).
+// vals_in == nullptr: values start as 0..n-1.  The pairs ping-pong between (k0, v0) and (k1, v1);
+// *k_out / *v_out say where the sorted ones ended up, *k_free / *v_free name the other buffer of each.
+int onesweep_pairs(cc_ctx *ctx, uint32_t *k0, uint32_t *k1, const uint32_t *vals_in, uint32_t *v0, uint32_t *v1,
+                   uint64_t n, int passes, uint32_t **k_out, uint32_t **v_out, uint32_t **k_free, uint32_t **v_free)
+{
+    const uint32_t ntiles = (uint32_t)os_tiles(n);
+    TRY(ensure(ctx, ctx->radix_counts, ((size_t)ntiles * OS_BINS + OS_MAX_PASSES * OS_BINS + 64) * 4));
+    uint32_t *ghist = ptr<uint32_t>(ctx->radix_counts);                 // [passes][256] digit totals, then bases
+    uint32_t *tickets = ghist + OS_MAX_PASSES * OS_BINS;                // one tile ticket per pass
+    uint32_t *status = tickets + 64;                                    // [tiles][256] look-back words
+    CK(cudaMemsetAsync(ghist, 0, (OS_MAX_PASSES * OS_BINS + 64) * sizeof(uint32_t), ctx->stream));
+    LAUNCH(os_histogram_kernel, 148 * 4, 256, k0, n, passes, ghist);
+    LAUNCH(os_scan_hist_kernel, 1, 32 * OS_MAX_PASSES, ghist, passes);
+    uint32_t *kin = k0, *kout = k1;
+    const uint32_t *vin = vals_in;
+    uint32_t *vout = v0, *vother = v1;
+    if (vals_in == v0) { vout = v1; vother = v0; }
+    for (int pass = 0; pass < passes; pass++) {
+        CK(cudaMemsetAsync(status, 0, (size_t)ntiles * OS_BINS * sizeof(uint32_t), ctx->stream));
+        LAUNCH(os_pass_kernel, ntiles, OS_THREADS, kin, vin, kout, vout, n, 8 * pass, ghist + pass * OS_BINS, status,
+               tickets + pass);
+        uint32_t *t = kin; kin = kout; kout = t;
+        vin = vout; t = vout; vout = vother; vother = t;
+    }
+    *k_out = kin; *k_free = kout;
+    *v_out = const_cast<uint32_t *>(vin); *v_free = vout;
+    return CC_OK;
+}
+
 int do_group(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
@@ -258,9 +289,6 @@ int do_group(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
     TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
     TRY(ensure(ctx, ctx->head, n));
-    const uint32_t ntiles = (uint32_t)os_tiles(n);
-    TRY(ensure(ctx, ctx->radix_counts, ((size_t)ntiles * OS_BINS + OS_MAX_PASSES * OS_BINS + 64) * 4));
-
     const int bits = sort_bits_for(n);
     const uint32_t key_mask = bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
     TRY(phase_begin(ctx, CC_PH_HASH));
@@ -268,24 +296,9 @@ int do_group(cc_ctx *ctx)
     TRY(phase_end(ctx, CC_PH_HASH));
 
     TRY(phase_begin(ctx, CC_PH_SORT));
-    const int passes = bits / 8;
-    uint32_t *ghist = ptr<uint32_t>(ctx->radix_counts);                 // [passes][256] digit totals, then bases
-    uint32_t *tickets = ghist + OS_MAX_PASSES * OS_BINS;                // one tile ticket per pass
-    uint32_t *status = tickets + 64;                                    // [tiles][256] look-back words
-    CK(cudaMemsetAsync(ghist, 0, (OS_MAX_PASSES * OS_BINS + 64) * sizeof(uint32_t), ctx->stream));
-    LAUNCH(os_histogram_kernel, 148 * 4, 256, ptr<uint32_t>(ctx->key_a), n, passes, ghist);
-    LAUNCH(os_scan_hist_kernel, 1, 32 * OS_MAX_PASSES, ghist, passes);
-    uint32_t *kin = ptr<uint32_t>(ctx->key_a), *kout = ptr<uint32_t>(ctx->key_b);
-    uint32_t *vin = nullptr, *vout = ptr<uint32_t>(ctx->val_a), *vother = ptr<uint32_t>(ctx->val_b);
-    for (int pass = 0; pass < passes; pass++) {
-        CK(cudaMemsetAsync(status, 0, (size_t)ntiles * OS_BINS * sizeof(uint32_t), ctx->stream));
-        LAUNCH(os_pass_kernel, ntiles, OS_THREADS, kin, vin, kout, vout, n, 8 * pass, ghist + pass * OS_BINS, status,
-               tickets + pass);
-        uint32_t *t = kin; kin = kout; kout = t;
-        vin = vout; vout = vother; vother = vin;
-    }
-    ctx->sorted_keys = kin; ctx->spare_keys = kout;
-    ctx->perm = vin; ctx->spare_vals = vout;
+    TRY(onesweep_pairs(ctx, ptr<uint32_t>(ctx->key_a), ptr<uint32_t>(ctx->key_b), nullptr, ptr<uint32_t>(ctx->val_a),
+                       ptr<uint32_t>(ctx->val_b), n, bits / 8, &ctx->sorted_keys, &ctx->perm, &ctx->spare_keys,
+                       &ctx->spare_vals));
     TRY(phase_end(ctx, CC_PH_SORT));
 
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
@@ -615,7 +628,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
                      &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->mid_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
-                     &ctx->first_read};
+                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
@@ -896,6 +909,50 @@ int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2,
     LAUNCH(kernel, blocks_for(n_pairs * g, 256), 256, ptr<uint8_t>(ctx->tmp_a),
            ptr<uint8_t>(ctx->tmp_b), n_pairs, lpad, stride, g, ptr<uint8_t>(ctx->tmp_c));
     CK(cudaMemcpyAsync(out_rows, ctx->tmp_c.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return CC_OK;
+}
+
+int cc_sort_coordinates(cc_ctx *ctx, const int32_t *tid, const int32_t *pos, const uint16_t *flag, uint64_t n,
+                        uint32_t *order)
+{
+    if (!ctx || (n && (!tid || !pos || !flag || !order))) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) return CC_OK;
+    if (n >= (1ull << 31)) return fail(ctx, CC_ERR_TOO_LARGE, "cc_sort_coordinates: at most 2^31 - 1 records");
+    int32_t max_pos = -1, max_tid = -1;
+    bool no_contig = false;
+    for (uint64_t i = 0; i < n; i++) {
+        if (pos[i] < -1 || pos[i] == INT32_MAX) return fail(ctx, CC_ERR_ARG, "cc_sort_coordinates: position outside [-1, 2^31 - 2]");
+        max_pos = pos[i] > max_pos ? pos[i] : max_pos;
+        max_tid = tid[i] > max_tid ? tid[i] : max_tid;
+        no_contig |= tid[i] < 0;
+    }
+    auto passes_for = [](uint64_t max_key) { int p = 1; while (p < 4 && (max_key >> (8 * p))) p++; return p; };
+    const int passes_lo = passes_for((((uint64_t)max_pos + 1) << 1) | 1);
+    const uint32_t tid_last = (uint32_t)(max_tid + 1);                   // key of records without a contig
+    const int passes_hi = (max_tid <= 0 && !no_contig) ? 0 : passes_for(tid_last);
+    // staged input: tid[n], pos[n] (i32) then flag[n] (u16)
+    TRY(ensure(ctx, ctx->cs_in, n * 10));
+    TRY(ensure(ctx, ctx->cs_k0, n * 4)); TRY(ensure(ctx, ctx->cs_k1, n * 4));
+    TRY(ensure(ctx, ctx->cs_v0, n * 4)); TRY(ensure(ctx, ctx->cs_v1, n * 4));
+    int32_t *d_tid = ptr<int32_t>(ctx->cs_in), *d_pos = d_tid + n;
+    uint16_t *d_flag = reinterpret_cast<uint16_t *>(d_pos + n);
+    CK(cudaMemcpyAsync(d_tid, tid, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_pos, pos, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_flag, flag, n * 2, cudaMemcpyHostToDevice, ctx->stream));
+    uint32_t *k0 = ptr<uint32_t>(ctx->cs_k0), *k1 = ptr<uint32_t>(ctx->cs_k1);
+    uint32_t *v0 = ptr<uint32_t>(ctx->cs_v0), *v1 = ptr<uint32_t>(ctx->cs_v1);
+    uint32_t *ks, *vs, *kf, *vf;
+    LAUNCH(coord_pos_key_kernel, blocks_for(n, 256), 256, d_pos, d_flag, n, k0);
+    TRY(onesweep_pairs(ctx, k0, k1, nullptr, v0, v1, n, passes_lo, &ks, &vs, &kf, &vf));
+    if (passes_hi) {
+        // LSD over the two words: the second sort is stable, so position order survives inside a contig
+        LAUNCH(coord_tid_key_kernel, blocks_for(n, 256), 256, d_tid, vs, n, tid_last, kf);
+        uint32_t *kin = kf, *kother = ks, *vin = vs, *vother = vf;
+        TRY(onesweep_pairs(ctx, kin, kother, vin, vin, vother, n, passes_hi, &ks, &vs, &kf, &vf));
+    }
+    CK(cudaMemcpyAsync(order, vs, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return CC_OK;
 }

@@ -550,6 +550,26 @@ __global__ void fill_i32_kernel(int32_t *p, uint64_t n, int32_t v)
     if (i < n) p[i] = v;
 }
 
+// ---- coordinate sort of output records (sort_index, ConsensusCruncher.py:10-29) ----------------
+// low key: position then strand, as `samtools sort` orders records of one contig
+__global__ void coord_pos_key_kernel(const int32_t *__restrict__ pos, const uint16_t *__restrict__ flag, uint64_t n,
+                                     uint32_t *__restrict__ key)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) key[i] = ((uint32_t)(pos[i] + 1) << 1) | ((flag[i] >> 4) & 1u);     // pos >= -1 (checked on the host)
+}
+
+// high key, read through the order the first sort left: contig index, records without one last
+__global__ void coord_tid_key_kernel(const int32_t *__restrict__ tid, const uint32_t *__restrict__ order, uint64_t n,
+                                     uint32_t no_contig, uint32_t *__restrict__ key)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        int32_t t = tid[order[i]];
+        key[i] = t < 0 ? no_contig : (uint32_t)t;
+    }
+}
+
 __global__ void iota_kernel(uint32_t *p, uint32_t n)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

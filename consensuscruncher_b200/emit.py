@@ -34,18 +34,18 @@ class _Out:
         self.rec, self.fam = rec, fam
 
 
-def _sorted(outs):
-    recs = sort_records([o.rec for o in outs])
+def _sorted(outs, sorter=None):
+    recs = sort_records([o.rec for o in outs], sorter)
     by_id = {id(o.rec): o for o in outs}
     return [by_id[id(r)] for r in recs]
 
 
-def _merged(*lists):
+def _merged(*lists, sorter=None):
     by_id = {}
     for l in lists:
         for o in l:
             by_id[id(o.rec)] = o
-    return [by_id[id(r)] for r in merge_records(*[[o.rec for o in l] for l in lists])]
+    return [by_id[id(r)] for r in merge_records(*[[o.rec for o in l] for l in lists], sorter=sorter)]
 
 
 def _pair_walk(outs, mate_fam):
@@ -104,7 +104,7 @@ def sscs_stage_records(reads, packed, arrays, lpad, with_family=False):
     return sscs, singleton
 
 
-def emit_all(reads, packed, res, scorrect=True):
+def emit_all(reads, packed, res, scorrect=True, sorter=None):
     """-> (files: {name: [Read]}, stats_text, read_families_text).
 
     `reads` is the record list `packed` was built from.  File names follow
@@ -152,7 +152,7 @@ def emit_all(reads, packed, res, scorrect=True):
     sscs_pairs, singleton_pairs = sscs_stage_records(reads, packed, arrays, lpad, with_family=True)
     sscs = [_Out(r, g) for r, g in sscs_pairs]
     singleton = [_Out(r, g) for r, g in singleton_pairs]
-    sscs_sorted, singleton_sorted = _sorted(sscs), _sorted(singleton)
+    sscs_sorted, singleton_sorted = _sorted(sscs, sorter), _sorted(singleton, sorter)
 
     def dcs_stage(inp, in_set, row_of, rows, mq, fl, tl, rgc):
         dcs, single = [], []
@@ -180,7 +180,7 @@ def emit_all(reads, packed, res, scorrect=True):
     dcs, sscs_single = dcs_stage(sscs_sorted, lambda p: size[p] >= 2, res.dcs_row, res.dcs_rows,
                                  res.dcs_mapq, res.dcs_flag, res.dcs_tlen, res.dcs_rg)
     files = {"sscs.sorted": sscs_sorted, "singleton.sorted": singleton_sorted,
-             "dcs.sorted": _sorted(dcs), "sscs.singleton.sorted": _sorted(sscs_single)}
+             "dcs.sorted": _sorted(dcs, sorter), "sscs.singleton.sorted": _sorted(sscs_single, sorter)}
     c = packed.counters
     stats = ("# === SSCS ===\nUncollapsed - Total reads: %d\nUncollapsed - Unmapped reads: %d\n"
              "Uncollapsed - Secondary/Supplementary reads: %d\nSSCS reads: %d\nSingletons: %d\n"
@@ -215,18 +215,19 @@ def emit_all(reads, packed, res, scorrect=True):
                          repr((len(sscs_cor) / n_single) * 100), len(sing_cor),
                          repr((len(sing_cor) / n_single) * 100), len(uncorrected)))
         # else: the reference dies on a ZeroDivisionError before writing this block (App. B Q20)
-        files["sscs.correction.sorted"] = _sorted(sscs_cor)
-        files["singleton.correction.sorted"] = _sorted(sing_cor)
-        files["uncorrected.sorted"] = _sorted(uncorrected)
-        sscs_sc = _merged(sscs_sorted, files["sscs.correction.sorted"], files["singleton.correction.sorted"])
+        files["sscs.correction.sorted"] = _sorted(sscs_cor, sorter)
+        files["singleton.correction.sorted"] = _sorted(sing_cor, sorter)
+        files["uncorrected.sorted"] = _sorted(uncorrected, sorter)
+        sscs_sc = _merged(sscs_sorted, files["sscs.correction.sorted"], files["singleton.correction.sorted"],
+                          sorter=sorter)
         files["sscs.sc.sorted"] = sscs_sc
         rec_of = {o.fam: o.rec for o in sscs_sc}
         dcs_sc, sscs_sc_single = dcs_stage(sscs_sc, lambda p: p in rec_of, res.dcssc_row, res.dcssc_rows,
                                            res.dcssc_mapq, res.dcssc_flag, res.dcssc_tlen, res.dcssc_rg)
-        files["dcs.sc.sorted"] = _sorted(dcs_sc)
-        files["sscs.sc.singleton.sorted"] = _sorted(sscs_sc_single)
+        files["dcs.sc.sorted"] = _sorted(dcs_sc, sorter)
+        files["sscs.sc.singleton.sorted"] = _sorted(sscs_sc_single, sorter)
         files["all.unique.dcs.sorted"] = _merged(files["dcs.sc.sorted"], files["sscs.sc.singleton.sorted"],
-                                                 files["uncorrected.sorted"])
+                                                 files["uncorrected.sorted"], sorter=sorter)
         stats += dcs_block % ("DCS - Singleton Correction", " SC", len(sscs_sc), " SC", 0, " SC", 0,
                               " SC", len(dcs_sc), " SC", len(sscs_sc_single))
     files["badReads"] = [_Out(reads[i], -1) for i in packed.bad]

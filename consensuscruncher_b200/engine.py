@@ -36,7 +36,7 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_load_reads_device", "cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run",
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
-           "cc_consensus_maker_static")
+           "cc_consensus_maker_static", "cc_sort_coordinates")
 
 
 class CcParams(ctypes.Structure):
@@ -88,6 +88,7 @@ def load_library(path=None):
     L.cc_device_ptr.argtypes = [vp, i32]
     L.cc_consensus_maker.argtypes = [vp, vp, u32, u32, u32, ctypes.c_double, vp]
     L.cc_duplex_consensus.argtypes = [vp, vp, vp, u64, u32, u32, i32, vp]
+    L.cc_sort_coordinates.argtypes = [vp, vp, vp, vp, u64, vp]
     L.cc_consensus_maker_static.argtypes = [vp, u32, u32, u32, ctypes.c_double, vp, vp]
     L.cc_profile.argtypes = [vp, i32]
     L.cc_phase_ms.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(u64)]
@@ -236,6 +237,27 @@ class GpuConsensus:
                                                  rows1.shape[0], int(lpad), rows1.shape[1],
                                                  1 if sc else 0, out.ctypes.data))
         return out
+
+    def sort_coordinates(self, tid, pos, flag):
+        """Stable coordinate order of records given as arrays: the permutation `sort_index` /
+        `samtools merge` would apply (ConsensusCruncher.py:10-29,248).  -> uint32[n]."""
+        tid = np.ascontiguousarray(tid, np.int32)
+        pos = np.ascontiguousarray(pos, np.int32)
+        flag = np.ascontiguousarray(flag, np.uint16)
+        order = np.empty(len(tid), np.uint32)
+        self._check(self.lib.cc_sort_coordinates(self.ctx, tid.ctypes.data, pos.ctypes.data, flag.ctypes.data,
+                                                 len(tid), order.ctypes.data))
+        return order
+
+    def sort_records(self, records):
+        """`records.sort_records` with the ordering done on the GPU."""
+        n = len(records)
+        if n < 2:
+            return list(records)
+        order = self.sort_coordinates(np.fromiter((r.tid for r in records), np.int32, n),
+                                      np.fromiter((r.pos for r in records), np.int32, n),
+                                      np.fromiter((r.flag for r in records), np.uint16, n))
+        return [records[i] for i in order]
 
     # -- timing ------------------------------------------------------------------------
     def profile(self, enable=True):

@@ -104,15 +104,20 @@ def sort_key(r: Read):
     return (tid, r.pos, 1 if (r.flag & 0x10) else 0)
 
 
-def sort_records(records):
-    """Stable coordinate sort used in place of `samtools view -bu | samtools sort -`."""
+def sort_records(records, sorter=None):
+    """Stable coordinate sort used in place of `samtools view -bu | samtools sort -`.
+
+    `sorter(records) -> list` does the ordering elsewhere (`GpuConsensus.sort_records`: the same
+    key, sorted on the GPU); the default is the host statement of the rule."""
+    if sorter is not None:
+        return sorter(records)
     return sorted(records, key=sort_key)
 
 
-def merge_records(*files):
+def merge_records(*files, sorter=None):
     """`samtools merge OUT IN1 IN2 IN3`: ties broken by input-file order
     (ConsensusCruncher.py:248,282)."""
     out = []
     for f in files:
         out.extend(f)
-    return sort_records(out)
+    return sort_records(out, sorter)

@@ -344,17 +344,19 @@ def sc_main(argv=None):
 
 
 # ---- what the driver does between the stages (ConsensusCruncher.py:10-29, :247-251) ---------------
-def sort_index(path):
-    """`samtools view -bu | samtools sort -`, remove the unsorted file, `samtools index`."""
+def sort_index(path, engine=None):
+    """`samtools view -bu | samtools sort -`, remove the unsorted file, `samtools index`.
+    With an engine the ordering runs on the GPU (`cc_sort_coordinates`)."""
     from .records import sort_records
     header, reads = bam.read_bam(path)
     out = path.split(".bam", 1)[0] + ".sorted.bam"
-    bam.write_bam(out, header, sort_records(reads), sort_order="coordinate", index=True)
+    bam.write_bam(out, header, sort_records(reads, engine.sort_records if engine else None),
+                  sort_order="coordinate", index=True)
     os.remove(path)
     return out
 
 
-def merge_bams(out, *inputs):
+def merge_bams(out, *inputs, engine=None):
     """`samtools merge OUT IN1 IN2 ...` (ties keep the order of the inputs)."""
     from .records import merge_records
     header = None
@@ -363,5 +365,5 @@ def merge_bams(out, *inputs):
         h, reads = bam.read_bam(p)
         header = header or h
         lists.append(reads)
-    bam.write_bam(out, header, merge_records(*lists))
+    bam.write_bam(out, header, merge_records(*lists, sorter=engine.sort_records if engine else None))
     return out

@@ -188,6 +188,14 @@ int cc_consensus_maker(cc_ctx *ctx, const uint8_t *rows, uint32_t n, uint32_t lp
 int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2, uint64_t n_pairs,
                         uint32_t lpad, uint32_t stride, int sc, uint8_t *out_rows);
 
+/* Coordinate sort of output records: the `samtools view -bu | samtools sort` of sort_index
+ * (ConsensusCruncher.py:10-29) and, applied to concatenated inputs, `samtools merge`
+ * (ConsensusCruncher.py:248,282).  order[k] = index of the record of rank k under the stable
+ * order (contig index, position, strand bit 0x10 of flag); records without a contig (tid < 0)
+ * go last.  Host buffers; position must lie in [-1, 2^31 - 2]. */
+int cc_sort_coordinates(cc_ctx *ctx, const int32_t *tid, const int32_t *pos, const uint16_t *flag, uint64_t n,
+                        uint32_t *order);
+
 /* Largest family cc_consensus_maker_static accepts (its scratch is sized for this). */
 #define CC_STATIC_MAX_READS 4096
 

@@ -243,3 +243,27 @@ def test_region_shards_on_the_gpu_equal_the_whole(engine):
         assert size == whole.fam_size[g] and has_partner == (whole.partner[g] >= 0)
         assert row == (bytes(whole.sscs_rows[whole.sscs_row[g]]) if whole.sscs_row[g] >= 0 else None)
         assert corr == (bytes(whole.corr_rows[whole.corr_row[g]]) if whole.corr_row[g] >= 0 else None)
+
+
+@pytest.mark.parametrize("n,n_tid,max_pos", [(1, 1, 10), (2, 1, 0), (5000, 1, 200), (100000, 3, 5000),
+                                             (300000, 700, 2 ** 31 - 2), (70000, 1, 70000)])
+def test_coordinate_sort_equals_the_host_rule(engine, n, n_tid, max_pos):
+    # sort_index / samtools merge (ConsensusCruncher.py:10-29,248): (contig, position, strand), stable,
+    # records without a contig last
+    rng = np.random.default_rng(n)
+    tid = rng.integers(-1, n_tid, n).astype(np.int32)
+    pos = rng.integers(-1, max_pos + 1, n, dtype=np.int64).astype(np.int32)
+    flag = rng.choice(np.array([99, 147, 83, 163, 77, 141, 1123], np.uint16), n)
+    got = engine.sort_coordinates(tid, pos, flag)
+    t = np.where(tid < 0, np.int64(1) << 31, tid.astype(np.int64))
+    exp = np.lexsort(((flag >> 4) & 1, pos.astype(np.int64), t))          # lexsort is stable, last key first
+    assert np.array_equal(got.astype(np.int64), exp)
+    recs = [Read("q%d" % i, int(flag[i]), int(tid[i]), int(pos[i]), 0, "", -1, -1, 0, "", []) for i in range(min(n, 3000))]
+    from consensuscruncher_b200.records import sort_records
+    assert [r.qname for r in engine.sort_records(recs)] == [r.qname for r in sort_records(recs)]
+
+
+def test_coordinate_sort_rejects_positions_it_cannot_key(engine):
+    with pytest.raises(Exception):
+        engine.sort_coordinates(np.array([0], np.int32), np.array([-2], np.int32), np.array([0], np.uint16))
+    assert len(engine.sort_coordinates(np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.uint16))) == 0

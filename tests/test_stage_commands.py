@@ -30,7 +30,7 @@ def test_stage_chain_reproduces_reference_tree(tmp_path, name, engine):
         _write_bed(bed, g["params"]["bed"])
     sscs = os.path.join(d, "s.sscs.bam")
     stages.run_sscs(inp, sscs, g["params"]["cutoff"], "|", bed, engine=engine)
-    sscs = stages.sort_index(sscs)
+    sscs = stages.sort_index(sscs, engine=engine)
     sing = stages.sort_index(os.path.join(d, "s.singleton.bam"))
     dcs = os.path.join(d, "s.dcs.bam")
     stages.run_dcs(sscs, dcs, bed, engine=engine)
@@ -40,7 +40,7 @@ def test_stage_chain_reproduces_reference_tree(tmp_path, name, engine):
     for nm in ("sscs.correction", "singleton.correction", "uncorrected"):
         out[nm + ".sorted"] = stages.sort_index(os.path.join(d, "s.%s.bam" % nm))
     sc = stages.merge_bams(os.path.join(d, "s.sscs.sc.bam"), sscs, out["sscs.correction.sorted"],
-                           out["singleton.correction.sorted"])
+                           out["singleton.correction.sorted"], engine=engine)
     out["sscs.sc.sorted"] = stages.sort_index(sc)
     dcs_sc = os.path.join(d, "s.dcs.sc.bam")
     stages.run_dcs(out["sscs.sc.sorted"], dcs_sc, bed, engine=engine)
