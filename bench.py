@@ -12,8 +12,10 @@ independent), so scaling is weak; the only collective is the all-r
 the stats counters and the family-size histogram.
 
 value   reads/s with the batch resident in HBM when the timed region starts
-e2e     reads/s through cc_run_host: pinned host buffers in, every result array read
-        back to pinned host memory, copies inside the timed region
+e2e     reads/s through cc_run_host / cc_run_host_q4: pinned host buffers in, every result array
+        read back to pinned host memory, copies inside the timed region.  The compact rows of
+        cc_run_host_q4 (4-bit quality codes) are used when the batch has at most 15 distinct
+        non-zero qualities - binned instruments; the 8-bit-row figure is reported beside it
 Inputs (4.5 GB per GPU) are far larger than L2 (126 MB), so no L2 flush is needed
 between iterations.
 """
@@ -49,6 +51,9 @@ def parse():
     ap.add_argument("--cpu-pairs", type=int, default=CPU_SAMPLE_PAIRS, help="read pairs of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4"],
+                    help="host row format of the end-to-end leg: 8-bit qualities (cc_run_host), 4-bit quality "
+                         "codes (cc_run_host_q4), or both with the compact one reported when the batch allows it")
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"],
                     help="c2 = BASELINE.json configs[1] (the bench line); c3 / c4: panel / WGS-like batches for profiling")
     return ap.parse_args()
@@ -189,6 +194,34 @@ def vote_algorithmic_bytes(res_sizes, n_sscs, stride_l):
     return n_big * (1.5 * stride_l + 4) + n_sscs * (1.5 * stride_l + 16), n_big
 
 
+def device_q4(batch):
+    """(payload4 u8[n][stride4], table u8[16]) on the device for `cc_run_host_q4`, or None when the
+    batch has more than 15 distinct non-zero quality values (pack.to_q4 is the host statement)."""
+    import torch
+    lpad, half = batch.lpad, batch.lpad // 2
+    pay = batch.payload
+    n = pay.shape[0]
+    rows = 1 << 20
+    hist = torch.zeros(256, dtype=torch.int64, device=pay.device)
+    for a in range(0, n, rows):
+        hist += torch.bincount(pay[a:a + rows, half:half + lpad].reshape(-1).to(torch.int32), minlength=256)
+    values = [0] + [int(v) for v in torch.nonzero(hist).reshape(-1).tolist() if v != 0]
+    if len(values) > 16:
+        return None
+    table = torch.zeros(16, dtype=torch.uint8, device=pay.device)
+    table[:len(values)] = torch.tensor(values, dtype=torch.uint8, device=pay.device)
+    code_of = torch.zeros(256, dtype=torch.uint8, device=pay.device)
+    code_of[torch.tensor(values, dtype=torch.int64, device=pay.device)] = torch.arange(len(values), dtype=torch.uint8,
+                                                                                      device=pay.device)
+    stride4 = (lpad + 15) // 16 * 16
+    out = torch.zeros((n, stride4), dtype=torch.uint8, device=pay.device)
+    for a in range(0, n, rows):
+        codes = code_of[pay[a:a + rows, half:half + lpad].to(torch.int64)]
+        out[a:a + rows, :half] = pay[a:a + rows, :half]
+        out[a:a + rows, half:lpad] = codes[:, 0::2] | (codes[:, 1::2] << 4)
+    return out, table
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -299,10 +332,28 @@ def main():
         turn = {"next": 0}
         turn_cv = threading.Condition()
 
+        # Compact rows (cc_run_host_q4): 4-bit quality codes when the batch has at most 15 distinct
+        # non-zero qualities, as binned instruments produce; built here, outside every timed region.
+        q4 = device_q4(batch) if args.e2e_format in ("auto", "q4") else None
+        if args.e2e_format == "q4" and q4 is None:
+            raise SystemExit("--e2e-format q4: the batch has more than 15 distinct non-zero qualities")
+        h_q4 = h_table = None
+        if q4 is not None:
+            h_q4 = torch.empty(q4[0].shape, dtype=torch.uint8, pin_memory=True)
+            h_q4.copy_(q4[0])
+            h_table = q4[1].cpu().contiguous()
+            torch.cuda.synchronize(dev)
+            q4 = None
+        fmt = {"name": "q8"}
+
         def e2e_step(which, step_no):
             e = engines[which]
-            e._check(e.lib.cc_run_host(e.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
-                                       batch.stride, h_dup.data_ptr(), batch.n_bc))
+            if fmt["name"] == "q4":
+                e._check(e.lib.cc_run_host_q4(e.ctx, h_fields.data_ptr(), h_q4.data_ptr(), n_reads, batch.lpad,
+                                              h_q4.shape[1], h_table.data_ptr(), h_dup.data_ptr(), batch.n_bc))
+            else:
+                e._check(e.lib.cc_run_host(e.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
+                                           batch.stride, h_dup.data_ptr(), batch.n_bc))
             if world > 1:                      # the collective is issued in step order on every rank
                 with turn_cv:
                     turn_cv.wait_for(lambda: turn["next"] == step_no)
@@ -338,22 +389,40 @@ def main():
                 futs = [ex.submit(worker, w, w, (count + 1 - w) // 2) for w in (0, 1)]
                 return max(f.result() for f in futs)
 
-        run_steps(4)                           # warm-up: allocations, pinning of the result buffers
-        barrier()
         e2e_steps = max(4, min(args.steps, 8))
-        t0 = time.perf_counter()
-        d2h = run_steps(e2e_steps)
-        torch.cuda.synchronize(dev)
-        wall = (time.perf_counter() - t0) * 1e3
-        barrier()
-        t = torch.tensor([wall], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": n_reads * world * e2e_steps / (float(t.item()) * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": int(batch.nbytes()), "d2h_bytes_per_step": int(d2h),
-               "steps": e2e_steps, "ms_per_step": float(t.item()) / e2e_steps,
-               "pipeline": "2 contexts alternate: read-back of batch k overlaps upload of batch k+1; host wall clock",
-               "numa": numa}
+
+        def measure(name):
+            fmt["name"] = name
+            run_steps(4)                       # warm-up: allocations, pinning of the result buffers
+            barrier()
+            t0 = time.perf_counter()
+            d2h = run_steps(e2e_steps)
+            torch.cuda.synchronize(dev)
+            wall = (time.perf_counter() - t0) * 1e3
+            barrier()
+            t = torch.tensor([wall], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            payload_bytes = h_q4.numel() if name == "q4" else h_payload.numel()
+            h2d = h_fields.numel() * h_fields.element_size() + payload_bytes + h_dup.numel() * h_dup.element_size()
+            return {"value": n_reads * world * e2e_steps / (float(t.item()) * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "steps": e2e_steps, "ms_per_step": float(t.item()) / e2e_steps}
+
+        legs = {}
+        if args.e2e_format in ("auto", "q8"):
+            legs["q8"] = measure("q8")
+        if h_q4 is not None:
+            legs["q4"] = measure("q4")
+        best = "q4" if "q4" in legs else "q8"
+        e2e = dict(legs[best])
+        e2e["input_format"] = ("cc_run_host_q4: rows with 4-bit quality codes (the batch has %d distinct qualities)"
+                               % int((h_table != 0).sum() + 1)) if best == "q4" else \
+                              "cc_run_host: rows with 8-bit qualities"
+        if best == "q4" and "q8" in legs:
+            e2e["q8_rows"] = {k: legs["q8"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
+        e2e["pipeline"] = "2 contexts alternate: read-back of batch k overlaps upload of batch k+1; host wall clock"
+        e2e["numa"] = numa
         engines[1].close()
 
     if rank != 0:

@@ -73,7 +73,7 @@ def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bd
     eng = engine or GpuConsensus(device, cutoff=cutoff, scorrect=scorrect)
     try:
         eng.set_params(cutoff=cutoff, scorrect=scorrect)
-        res = eng.consensus(packed)
+        res = eng.consensus(packed, compact="auto")
         t_gpu = time.time()
         # the sort / merge steps between the stages (ConsensusCruncher.py:10-29,248,282) order on the GPU
         files, stats, fam_txt = emit.emit_all(reads, packed, res, scorrect, sorter=eng.sort_records)

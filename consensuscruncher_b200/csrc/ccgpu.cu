@@ -47,7 +47,7 @@ struct cc_ctx {
     const uint32_t *dup_bc = nullptr;
     uint64_t n = 0;
     uint32_t lpad = 0, stride = 0, n_bc = 0;
-    DevBuf in_fields, in_payload, in_dup;
+    DevBuf in_fields, in_payload, in_dup, in_q4;
     // grouping scratch
     DevBuf key_a, key_b, val_a, val_b, head, radix_counts, scan_status, counters, hist, stats;
     uint32_t *perm = nullptr, *sorted_keys = nullptr, *spare_keys = nullptr, *spare_vals = nullptr;
@@ -620,7 +620,7 @@ void cc_destroy(cc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
+    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
                      &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->hist, &ctx->stats,
                      &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
                      &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
@@ -668,6 +668,40 @@ int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, 
     if (n) {
         CK(cudaMemcpyAsync(ctx->in_fields.p, fields, n * sizeof(cc_fields), cudaMemcpyHostToDevice, ctx->stream));
         CK(cudaMemcpyAsync(ctx->in_payload.p, payload, n * (size_t)stride, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (n_bc) CK(cudaMemcpyAsync(ctx->in_dup.p, dup_bc, (size_t)n_bc * 4, cudaMemcpyHostToDevice, ctx->stream));
+    TRY(phase_end(ctx, CC_PH_H2D));
+    ctx->fields = ptr<uint4>(ctx->in_fields);
+    ctx->payload = ptr<uint8_t>(ctx->in_payload);
+    ctx->dup_bc = ptr<uint32_t>(ctx->in_dup);
+    ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
+    ctx->have_reads = true;
+    ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
+    return CC_OK;
+}
+
+int cc_load_reads_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload4, uint64_t n, uint32_t lpad,
+                     uint32_t stride4, const uint8_t qual_table[16], const uint32_t *dup_bc, uint32_t n_bc)
+{
+    if (!ctx || !qual_table) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (lpad == 0 || lpad % 32 || stride4 % 16 || stride4 < lpad)
+        return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride4 % 16 == 0, stride4 >= lpad");
+    const uint32_t stride = (lpad / 2 + lpad + 63) / 64 * 64;           // the standard row the kernels read
+    TRY(check_geometry(ctx, fields, payload4, n, lpad, stride));
+    if (qual_table[0] != 0) return fail(ctx, CC_ERR_ARG, "qual_table[0] must be 0 (code 0 pads the rows)");
+    TRY(ensure(ctx, ctx->in_fields, n * sizeof(cc_fields)));
+    TRY(ensure(ctx, ctx->in_q4, n * (size_t)stride4));
+    TRY(ensure(ctx, ctx->in_payload, n * (size_t)stride));
+    TRY(ensure(ctx, ctx->in_dup, (size_t)n_bc * 4));
+    TRY(phase_begin(ctx, CC_PH_H2D));
+    if (n) {
+        CK(cudaMemcpyAsync(ctx->in_fields.p, fields, n * sizeof(cc_fields), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->in_q4.p, payload4, n * (size_t)stride4, cudaMemcpyHostToDevice, ctx->stream));
+        QualTable table;
+        memcpy(table.q, qual_table, 16);
+        LAUNCH(expand_q4_kernel, blocks_for(n * (lpad / 16), 256), 256, ptr<uint8_t>(ctx->in_q4), stride4,
+               ptr<uint8_t>(ctx->in_payload), stride, lpad, n, table);
     }
     if (n_bc) CK(cudaMemcpyAsync(ctx->in_dup.p, dup_bc, (size_t)n_bc * 4, cudaMemcpyHostToDevice, ctx->stream));
     TRY(phase_end(ctx, CC_PH_H2D));
@@ -761,6 +795,13 @@ int cc_run_host(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, ui
                 uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc)
 {
     TRY(cc_load_reads(ctx, fields, payload, n, lpad, stride, dup_bc, n_bc));
+    return cc_run(ctx);
+}
+
+int cc_run_host_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload4, uint64_t n, uint32_t lpad,
+                   uint32_t stride4, const uint8_t qual_table[16], const uint32_t *dup_bc, uint32_t n_bc)
+{
+    TRY(cc_load_reads_q4(ctx, fields, payload4, n, lpad, stride4, qual_table, dup_bc, n_bc));
     return cc_run(ctx);
 }
 

@@ -550,6 +550,38 @@ __global__ void fill_i32_kernel(int32_t *p, uint64_t n, int32_t v)
     if (i < n) p[i] = v;
 }
 
+// ---- compact input rows (cc_load_reads_q4): lpad/2 base bytes + lpad/2 bytes of 4-bit quality
+// codes -> the standard row (lpad/2 base bytes + lpad quality bytes, zero tail).  One thread
+// expands 16 positions; a CTA first builds byte -> two-qualities from the 16-entry table.
+struct QualTable { uint8_t q[16]; };
+
+__global__ void __launch_bounds__(256)
+expand_q4_kernel(const uint8_t *__restrict__ in, uint32_t stride_in, uint8_t *__restrict__ out, uint32_t stride_out,
+                 uint32_t lpad, uint64_t n, QualTable table)
+{
+    __shared__ uint16_t pair_of[256];
+    pair_of[threadIdx.x] = (uint16_t)(table.q[threadIdx.x & 15] | (table.q[threadIdx.x >> 4] << 8));   // low nibble = even position
+    __syncthreads();
+    const uint32_t lanes = lpad / 16, half = lpad / 2;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t row = t / lanes;
+    const uint32_t lane = (uint32_t)(t % lanes);
+    if (row >= n) return;
+    const uint8_t *src = in + row * stride_in;
+    uint8_t *dst = out + row * stride_out;
+    const uint2 bases = *reinterpret_cast<const uint2 *>(src + lane * 8);
+    const uint2 codes = *reinterpret_cast<const uint2 *>(src + half + lane * 8);
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t c = (k < 2 ? codes.x : codes.y) >> (16 * (k & 1));
+        w[k] = pair_of[c & 0xFF] | ((uint32_t)pair_of[(c >> 8) & 0xFF] << 16);
+    }
+    *reinterpret_cast<uint2 *>(dst + lane * 8) = bases;
+    *reinterpret_cast<uint4 *>(dst + half + lane * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    for (uint32_t x = half + lpad + lane * 4; x < stride_out; x += lanes * 4) *reinterpret_cast<uint32_t *>(dst + x) = 0;
+}
+
 // ---- coordinate sort of output records (sort_index, ConsensusCruncher.py:10-29) ----------------
 // low key: position then strand, as `samtools sort` orders records of one contig
 __global__ void coord_pos_key_kernel(const int32_t *__restrict__ pos, const uint16_t *__restrict__ flag, uint64_t n,

@@ -36,7 +36,7 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_load_reads_device", "cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run",
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
-           "cc_consensus_maker_static", "cc_sort_coordinates")
+           "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4")
 
 
 class CcParams(ctypes.Structure):
@@ -78,6 +78,8 @@ def load_library(path=None):
     L.cc_load_reads.argtypes = load_args
     L.cc_load_reads_device.argtypes = load_args
     L.cc_run_host.argtypes = load_args
+    L.cc_load_reads_q4.argtypes = [vp, vp, vp, u64, u32, u32, vp, vp, u32]
+    L.cc_run_host_q4.argtypes = [vp, vp, vp, u64, u32, u32, vp, vp, u32]
     for nm in ("cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run"):
         getattr(L, nm).argtypes = [vp]
     L.cc_counts.argtypes = [vp, ctypes.POINTER(u64)]
@@ -166,6 +168,21 @@ class GpuConsensus:
         """Host SoA -> device (cc_load_reads)."""
         self._check(self.lib.cc_load_reads(*self._host_args(packed)))
 
+    def load_q4(self, packed: PackedReads, q4=None):
+        """Host SoA with 4-bit quality codes -> device (cc_load_reads_q4); raises if the batch has
+        too many distinct qualities for the compact rows."""
+        from .pack import row_geometry, to_q4
+        q4 = q4 or to_q4(packed)
+        if q4 is None:
+            raise GpuError("more than 15 distinct non-zero quality values: use load()")
+        payload4, table = q4
+        fields = np.ascontiguousarray(packed.fields)
+        dup = np.ascontiguousarray(packed.dup_bc, dtype=np.uint32)
+        self._keep = (fields, payload4, dup, table)
+        self.lpad, self.stride = packed.lpad, row_geometry(packed.lpad)[1]
+        self._check(self.lib.cc_load_reads_q4(self.ctx, fields.ctypes.data, payload4.ctypes.data, packed.n, packed.lpad,
+                                              payload4.shape[1], table.ctypes.data, dup.ctypes.data, len(dup)))
+
     def load_device(self, fields_ptr, payload_ptr, n, lpad, stride, dup_ptr, n_bc):
         """Adopt buffers that already live in device memory (cc_load_reads_device)."""
         self.lpad, self.stride = int(lpad), int(stride)
@@ -216,9 +233,19 @@ class GpuConsensus:
         arrays = {k: self.fetch(k) for k in ALL_ARRAYS}
         return ConsensusResult(self.lpad, self.stride, bool(self.params.scorrect), **arrays)
 
-    def consensus(self, packed: PackedReads) -> ConsensusResult:
-        """The whole path on one batch: host SoA in, family-level results out."""
-        self.run_host(packed)
+    def consensus(self, packed: PackedReads, compact=False) -> ConsensusResult:
+        """The whole path on one batch: host SoA in, family-level results out.
+        compact=True sends the rows with 4-bit quality codes (cc_load_reads_q4)."""
+        q4 = None
+        if compact == "auto":                  # compact rows whenever the batch's qualities allow them
+            from .pack import to_q4
+            q4 = to_q4(packed)
+            compact = q4 is not None
+        if compact:
+            self.load_q4(packed, q4)
+            self.run()
+        else:
+            self.run_host(packed)
         return self.result()
 
     # -- stand-alone primitives ----------------------------------------------------

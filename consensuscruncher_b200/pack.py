@@ -221,3 +221,40 @@ def pack_reads(reads, stage="sscs", bdelim="|", regions=None, row_source=None):
     return PackedReads(fields, payload, lpad, barcodes, build_dup_table(barcodes),
                        list(cig_ids), list(rg_ids), src=src, lens=lens,
                        counters=counters, bad=bad, leftover=leftover)
+
+
+def to_q4(packed):
+    """Compact rows for `cc_load_reads_q4`: (payload4 u8[n][stride4], qual_table u8[16]), or None
+    when the batch has more than 15 distinct non-zero quality values.
+
+    A row is lpad/2 base bytes (unchanged) + lpad/2 bytes of 4-bit quality codes, even position in
+    the low nibble; code 0 is quality 0 (row padding)."""
+    lpad, half = packed.lpad, packed.lpad // 2
+    q = packed.payload[:, half:half + lpad]
+    present = np.flatnonzero(np.bincount(q.reshape(-1), minlength=256)) if q.size else np.zeros(0, np.int64)
+    values = [0] + [int(v) for v in present if v != 0]
+    if len(values) > 16:
+        return None
+    table = np.zeros(16, np.uint8)
+    table[:len(values)] = values
+    code_of = np.zeros(256, np.uint8)
+    code_of[values] = np.arange(len(values), dtype=np.uint8)
+    codes = code_of[q]
+    stride4 = (lpad + 15) // 16 * 16
+    out = np.zeros((packed.n, stride4), np.uint8)
+    out[:, :half] = packed.payload[:, :half]
+    out[:, half:lpad] = codes[:, 0::2] | (codes[:, 1::2] << 4)
+    return out, table
+
+
+def from_q4(payload4, table, lpad):
+    """Inverse of `to_q4`: the standard payload rows (what the device expands to)."""
+    half = lpad // 2
+    n = payload4.shape[0]
+    _, stride = row_geometry(lpad)
+    out = np.zeros((n, stride), np.uint8)
+    out[:, :half] = payload4[:, :half]
+    c = payload4[:, half:lpad]
+    out[:, half:half + lpad:2] = table[c & 15]
+    out[:, half + 1:half + lpad:2] = table[c >> 4]
+    return out

@@ -168,6 +168,19 @@ int cc_run(cc_ctx *ctx);
 int cc_run_host(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
                 uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
 
+/* Compact input for instruments that bin their qualities (at most 15 distinct non-zero values,
+ * e.g. the 4 of a NovaSeq): a row is lpad/2 base bytes, as in `payload`, followed by lpad/2 bytes of
+ * 4-bit quality codes (even position in the low nibble), stride4 % 16 == 0, stride4 >= lpad;
+ * qual_table[code] is the quality byte, qual_table[0] == 0 (code 0 pads the rows).  The rows are
+ * expanded on the device into the standard layout (stride = 3*lpad/2 rounded up to 64); everything
+ * after that, results included, is as with cc_load_reads / cc_run_host.  Same reference code as
+ * cc_load_reads (read_bam, consensus_helper.py:376-436); it moves 29 % fewer bytes over PCIe at
+ * lpad = 128. */
+int cc_load_reads_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload4, uint64_t n, uint32_t lpad,
+                     uint32_t stride4, const uint8_t qual_table[16], const uint32_t *dup_bc, uint32_t n_bc);
+int cc_run_host_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload4, uint64_t n, uint32_t lpad,
+                   uint32_t stride4, const uint8_t qual_table[16], const uint32_t *dup_bc, uint32_t n_bc);
+
 /* counts[CC_N_*] after the stage that produces them (synchronises). */
 int cc_counts(cc_ctx *ctx, uint64_t counts[8]);
 

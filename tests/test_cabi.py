@@ -13,7 +13,7 @@ def test_library_builds_and_exports_declared_symbols():
     path = build.build_lib()
     lib = ctypes.CDLL(path)
     header = open(os.path.join(ROOT, "include", "ccgpu.h")).read()
-    declared = set(re.findall(r"\b(cc_[a-z_]+)\s*\(", header))
+    declared = set(re.findall(r"\b(cc_[a-z_0-9]+)\s*\(", header))
     assert declared == set(engine.SYMBOLS)
     for sym in sorted(declared):
         assert hasattr(lib, sym), sym

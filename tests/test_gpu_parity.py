@@ -267,3 +267,22 @@ def test_coordinate_sort_rejects_positions_it_cannot_key(engine):
     with pytest.raises(Exception):
         engine.sort_coordinates(np.array([0], np.int32), np.array([-2], np.int32), np.array([0], np.uint16))
     assert len(engine.sort_coordinates(np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.uint16))) == 0
+
+
+@pytest.mark.parametrize("L", [32, 75, 128, 150])
+def test_compact_quality_rows_give_the_same_result(engine, L):
+    packed = synth.generate(seed=91, n_molecules=900, L=L).to_packed()
+    engine.set_params(cutoff=0.7, scorrect=True)
+    got = engine.consensus(packed, compact=True)
+    helpers.assert_same_result(got, oracle.run(packed, 0.7, True))
+    helpers.assert_same_result(got, engine.consensus(packed))
+
+
+def test_compact_rows_need_a_zero_code(engine):
+    packed = synth.generate(seed=92, n_molecules=10, L=32).to_packed()
+    payload4, table = pack.to_q4(packed)
+    table = table.copy()
+    table[0] = 7
+    rc = engine.lib.cc_load_reads_q4(engine.ctx, packed.fields.ctypes.data, payload4.ctypes.data, packed.n, packed.lpad,
+                                     payload4.shape[1], table.ctypes.data, packed.dup_bc.ctypes.data, len(packed.dup_bc))
+    assert rc == -2

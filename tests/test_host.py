@@ -127,3 +127,20 @@ def test_sort_and_merge_model():
     u = Read("u", 77, -1, -1)
     assert [r.qname for r in sort_records([u, a, c, b, d])] == ["d", "a", "b", "c", "u"]
     assert [r.qname for r in merge_records([b], [a], [d])] == ["d", "b", "a"]
+
+
+def test_q4_rows_round_trip():
+    s = synth.generate(seed=9, n_molecules=120, L=75)
+    packed = s.to_packed()
+    q4 = pack.to_q4(packed)
+    assert q4 is not None
+    payload4, table = q4
+    assert table[0] == 0 and payload4.shape[1] % 16 == 0 and payload4.shape[1] >= packed.lpad
+    assert np.array_equal(pack.from_q4(payload4, table, packed.lpad), packed.payload)
+    # 16 distinct non-zero qualities do not fit (code 0 is reserved for the padding)
+    s.qual[:, :] = (np.arange(s.qual.size).reshape(s.qual.shape) % 16 + 20).astype(np.uint8)
+    assert pack.to_q4(s.to_packed()) is None
+    s.qual[:, :] = (np.arange(s.qual.size).reshape(s.qual.shape) % 15 + 20).astype(np.uint8)
+    p2 = s.to_packed()
+    payload4, table = pack.to_q4(p2)
+    assert np.array_equal(pack.from_q4(payload4, table, p2.lpad), p2.payload)
