@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--cpu-pairs", type=int, default=CPU_SAMPLE_PAIRS, help="read pairs of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-contexts", type=int, default=2, help="contexts the end-to-end leg rotates over")
     ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4"],
                     help="host row format of the end-to-end leg: 8-bit qualities (cc_run_host), 4-bit quality "
                          "codes (cc_run_host_q4), or both with the compact one reported when the batch allows it")
@@ -326,9 +327,10 @@ def main():
         # host, the next batch is already being uploaded, so both PCIe directions stay busy.
         # Each context works on its own stream; each step is still one cc_run_host call plus
         # the read-back of every result array.
-        engines = [eng, GpuConsensus(local, cutoff=CUTOFF, scorrect=True)]
+        n_ctx = max(1, args.e2e_contexts)
+        engines = [eng] + [GpuConsensus(local, cutoff=CUTOFF, scorrect=True) for _ in range(n_ctx - 1)]
         eng.set_stream(0)
-        h_outs = [{}, {}]
+        h_outs = [{} for _ in range(n_ctx)]
         turn = {"next": 0}
         turn_cv = threading.Condition()
 
@@ -380,20 +382,20 @@ def main():
             torch.cuda.set_device(local)
             out = 0
             for k in range(count):
-                out = e2e_step(which, first + 2 * k)
+                out = e2e_step(which, first + n_ctx * k)
             return out
 
         def run_steps(count):                  # `count` steps in total, alternating between the contexts
             turn["next"] = 0
-            with ThreadPoolExecutor(max_workers=2) as ex:
-                futs = [ex.submit(worker, w, w, (count + 1 - w) // 2) for w in (0, 1)]
+            with ThreadPoolExecutor(max_workers=n_ctx) as ex:
+                futs = [ex.submit(worker, w, w, (count + n_ctx - 1 - w) // n_ctx) for w in range(n_ctx)]
                 return max(f.result() for f in futs)
 
-        e2e_steps = max(4, min(args.steps, 8))
+        e2e_steps = max(4, min(args.steps, 8)) // n_ctx * n_ctx or n_ctx
 
         def measure(name):
             fmt["name"] = name
-            run_steps(4)                       # warm-up: allocations, pinning of the result buffers
+            run_steps(2 * n_ctx)               # warm-up: allocations, pinning of the result buffers
             barrier()
             t0 = time.perf_counter()
             d2h = run_steps(e2e_steps)
@@ -421,9 +423,11 @@ def main():
                               "cc_run_host: rows with 8-bit qualities"
         if best == "q4" and "q8" in legs:
             e2e["q8_rows"] = {k: legs["q8"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
-        e2e["pipeline"] = "2 contexts alternate: read-back of batch k overlaps upload of batch k+1; host wall clock"
+        e2e["pipeline"] = ("%d contexts take turns: read-back of batch k overlaps upload of batch k+1; "
+                           "host wall clock" % n_ctx)
         e2e["numa"] = numa
-        engines[1].close()
+        for extra in engines[1:]:
+            extra.close()
 
     if rank != 0:
         if world > 1:
