@@ -45,15 +45,17 @@ def build_lib(force=False, verbose=False):
 
 
 PACK_LIB = os.path.join(HERE, "libccpack.so")
-PACK_SRC = os.path.join(CSRC, "ccpack.cpp")
+PACK_SRCS = [os.path.join(CSRC, f) for f in ("ccpack.cpp", "ccemit.cpp")]
+PACK_DEPS = PACK_SRCS + [os.path.join(CSRC, "ccpack.hpp")]
 
 
 def build_pack_lib(force=False):
-    """Compile csrc/ccpack.cpp (host-only: BGZF inflate + packing) into libccpack.so."""
-    if not force and os.path.exists(PACK_LIB) and os.path.getmtime(PACK_LIB) >= os.path.getmtime(PACK_SRC):
+    """Compile csrc/ccpack.cpp + ccemit.cpp (host-only: BGZF inflate / deflate, packing, record
+    assembly) into libccpack.so."""
+    if not force and os.path.exists(PACK_LIB) and all(os.path.getmtime(PACK_LIB) >= os.path.getmtime(f) for f in PACK_DEPS):
         return PACK_LIB
     cxx = shutil.which("g++") or "g++"
-    cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", "-o", PACK_LIB, PACK_SRC, "-lz", "-lpthread"]
+    cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", "-o", PACK_LIB] + PACK_SRCS + ["-lz", "-lpthread"]
     out = subprocess.run(cmd, capture_output=True, text=True)
     if out.returncode != 0:
         raise RuntimeError("g++ failed:\n" + out.stdout + out.stderr)

@@ -74,23 +74,25 @@ def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bd
     try:
         eng.set_params(cutoff=cutoff, scorrect=scorrect)
         res = eng.consensus(packed, compact="auto")
-        t_gpu = time.time()
-        # the sort / merge steps between the stages (ConsensusCruncher.py:10-29,248,282) order on the GPU
-        files, stats, fam_txt = emit.emit_all(reads, packed, res, scorrect, sorter=eng.sort_records)
     finally:
         if own:
             eng.close()
+    t_gpu = time.time()
+    # record assembly, the sort / merge steps between the stages and the BAM + BAI writing are native
+    # host code (csrc/ccemit.cpp); emit.emit_all + bam.write_bam are the same thing in Python
     where = {"sscs.sorted": "sscs", "singleton.sorted": "sscs", "badReads": "sscs",
              "dcs.sorted": "dcs", "sscs.singleton.sorted": "dcs",
              "sscs.correction.sorted": "sscs_sc", "singleton.correction.sorted": "sscs_sc",
              "uncorrected.sorted": "sscs_sc", "sscs.sc.sorted": "sscs_sc",
              "dcs.sc.sorted": "dcs_sc", "sscs.sc.singleton.sorted": "dcs_sc", "all.unique.dcs.sorted": "dcs_sc"}
-    for name, recs in files.items():
-        d = os.path.join(sample_dir, where[name])
-        os.makedirs(d, exist_ok=True)
-        is_sorted = name.endswith(".sorted")
-        bam.write_bam(os.path.join(d, "%s.%s.bam" % (identifier, name)), header, recs,
-                      sort_order="coordinate" if is_sorted else None, index=is_sorted)
+    sc_only = {"sscs_sc", "dcs_sc"}
+    paths = {}
+    for name, sub in where.items():
+        if sub in sc_only and not scorrect:
+            continue
+        os.makedirs(os.path.join(sample_dir, sub), exist_ok=True)
+        paths[name] = os.path.join(sample_dir, sub, "%s.%s.bam" % (identifier, name))
+    _, stats, fam_txt = fastpack.emit_files(reads, packed, res, scorrect, paths)
     with open(os.path.join(sample_dir, identifier + ".stats.txt"), "w") as fh:
         fh.write(stats)
     with open(os.path.join(sample_dir, identifier + ".read_families.txt"), "w") as fh:

@@ -104,6 +104,37 @@ def sscs_stage_records(reads, packed, arrays, lpad, with_family=False):
     return sscs, singleton
 
 
+def stats_text(c, n, scorrect=True):
+    """stats.txt from the packer's counters `c` and the record counts `n` of the
+    output lists (keys as in `emit_all`'s files)."""
+    stats = ("# === SSCS ===\nUncollapsed - Total reads: %d\nUncollapsed - Unmapped reads: %d\n"
+             "Uncollapsed - Secondary/Supplementary reads: %d\nSSCS reads: %d\nSingletons: %d\n"
+             "Bad spacers: %d\n" % (c.get("total", 0), c.get("unmapped_mate", 0),
+                                    c.get("multiple_mapping", 0), n["sscs.sorted"], n["singleton.sorted"],
+                                    c.get("bad_spacer", 0)))
+    dcs_block = ("# === %s ===\nSSCS%s - Total reads: %d\nSSCS%s - Unmapped reads: %d\n"
+                 "SSCS%s - Secondary/Supplementary reads: %d\nDCS%s reads: %d\nSSCS%s singletons: %d \n")
+    stats += dcs_block % ("DCS", "", n["sscs.sorted"], "", 0, "", 0, "", n["dcs.sorted"], "", n["sscs.singleton.sorted"])
+    if scorrect:
+        n_single = n["singleton.sorted"]
+        n_cor, n_sing, n_unc = n["sscs.correction.sorted"], n["singleton.correction.sorted"], n["uncorrected.sorted"]
+        if n_single:
+            stats += ("# === Singleton Correction ===\nTotal singletons: %d\nSingleton Correction by SSCS: %d\n"
+                      "%% Singleton Correction by SSCS: %s\nSingleton Correction by Singletons: %d\n"
+                      "%% Singleton Correction by Singletons : %s\nUncorrected Singletons: %d \n"
+                      % (n_cor + n_sing + n_unc, n_cor, repr((n_cor / n_single) * 100), n_sing,
+                         repr((n_sing / n_single) * 100), n_unc))
+        # else: the reference dies on a ZeroDivisionError before writing this block (App. B Q20)
+        stats += dcs_block % ("DCS - Singleton Correction", " SC", n["sscs.sc.sorted"], " SC", 0, " SC", 0,
+                              " SC", n["dcs.sc.sorted"], " SC", n["sscs.sc.singleton.sorted"])
+    return stats
+
+
+def families_text(res):
+    """read_families.txt (SSCS_maker.py:360-365)."""
+    return "family_size\tfrequency\n" + "\n".join("%d\t%d" % x for x in res.family_size_table())
+
+
 def emit_all(reads, packed, res, scorrect=True, sorter=None):
     """-> (files: {name: [Read]}, stats_text, read_families_text).
 
@@ -181,15 +212,6 @@ def emit_all(reads, packed, res, scorrect=True, sorter=None):
                                  res.dcs_mapq, res.dcs_flag, res.dcs_tlen, res.dcs_rg)
     files = {"sscs.sorted": sscs_sorted, "singleton.sorted": singleton_sorted,
              "dcs.sorted": _sorted(dcs, sorter), "sscs.singleton.sorted": _sorted(sscs_single, sorter)}
-    c = packed.counters
-    stats = ("# === SSCS ===\nUncollapsed - Total reads: %d\nUncollapsed - Unmapped reads: %d\n"
-             "Uncollapsed - Secondary/Supplementary reads: %d\nSSCS reads: %d\nSingletons: %d\n"
-             "Bad spacers: %d\n" % (c.get("total", 0), c.get("unmapped_mate", 0),
-                                    c.get("multiple_mapping", 0), len(sscs), len(singleton),
-                                    c.get("bad_spacer", 0)))
-    dcs_block = ("# === %s ===\nSSCS%s - Total reads: %d\nSSCS%s - Unmapped reads: %d\n"
-                 "SSCS%s - Secondary/Supplementary reads: %d\nDCS%s reads: %d\nSSCS%s singletons: %d \n")
-    stats += dcs_block % ("DCS", "", len(sscs_sorted), "", 0, "", 0, "", len(dcs), "", len(sscs_single))
 
     # ---- singleton correction + second DCS pass ---------------------------------
     if scorrect:
@@ -206,15 +228,6 @@ def emit_all(reads, packed, res, scorrect=True, sorter=None):
                 s = o.rec
                 rec = consensus_record(g, qn, res.corr_rows, res.corr_row[g], s.mapq, s.tlen, s.flag, s.rg, s)
                 (sscs_cor if size[p] >= 2 else sing_cor).append(_Out(rec, g))
-        n_single = len(singleton_sorted)
-        if n_single:
-            stats += ("# === Singleton Correction ===\nTotal singletons: %d\nSingleton Correction by SSCS: %d\n"
-                      "%% Singleton Correction by SSCS: %s\nSingleton Correction by Singletons: %d\n"
-                      "%% Singleton Correction by Singletons : %s\nUncorrected Singletons: %d \n"
-                      % (len(sscs_cor) + len(sing_cor) + len(uncorrected), len(sscs_cor),
-                         repr((len(sscs_cor) / n_single) * 100), len(sing_cor),
-                         repr((len(sing_cor) / n_single) * 100), len(uncorrected)))
-        # else: the reference dies on a ZeroDivisionError before writing this block (App. B Q20)
         files["sscs.correction.sorted"] = _sorted(sscs_cor, sorter)
         files["singleton.correction.sorted"] = _sorted(sing_cor, sorter)
         files["uncorrected.sorted"] = _sorted(uncorrected, sorter)
@@ -228,8 +241,6 @@ def emit_all(reads, packed, res, scorrect=True, sorter=None):
         files["sscs.sc.singleton.sorted"] = _sorted(sscs_sc_single, sorter)
         files["all.unique.dcs.sorted"] = _merged(files["dcs.sc.sorted"], files["sscs.sc.singleton.sorted"],
                                                  files["uncorrected.sorted"], sorter=sorter)
-        stats += dcs_block % ("DCS - Singleton Correction", " SC", len(sscs_sc), " SC", 0, " SC", 0,
-                              " SC", len(dcs_sc), " SC", len(sscs_sc_single))
     files["badReads"] = [_Out(reads[i], -1) for i in packed.bad]
-    fam_txt = "family_size\tfrequency\n" + "\n".join("%d\t%d" % x for x in res.family_size_table())
-    return {k: [o.rec for o in v] for k, v in files.items()}, stats, fam_txt
+    stats = stats_text(packed.counters, {k: len(v) for k, v in files.items()}, scorrect)
+    return {k: [o.rec for o in v] for k, v in files.items()}, stats, families_text(res)

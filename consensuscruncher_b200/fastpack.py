@@ -19,6 +19,31 @@ _lib = None
 COUNTER_NAMES = ("total", "unmapped", "unmapped_mate", "multiple_mapping", "bad_spacer")
 
 
+class EmitIn(C.Structure):
+    """struct ccp_emit_in of csrc/ccemit.cpp."""
+    _fields_ = ([("n_reads", C.c_uint64), ("n_fam", C.c_uint64), ("lpad", C.c_uint32), ("stride", C.c_uint32),
+                 ("src", C.c_void_p), ("fields", C.c_void_p),
+                 ("barcodes", C.c_char_p), ("cigar_pairs", C.c_char_p), ("rgs", C.c_char_p),
+                 ("n_bc", C.c_uint32), ("n_cig", C.c_uint32), ("n_rg", C.c_uint32),
+                 ("bad", C.c_void_p), ("n_bad", C.c_uint64)] +
+                [(k, C.c_void_p) for k in ("read_fam", "fam_size", "fam_tmpl", "fam_mapq", "fam_flag", "fam_tlen", "fam_rg",
+                                           "partner", "sscs_row", "corr_row", "dcs_row", "dcssc_row",
+                                           "sscs_rows", "corr_rows", "dcs_rows", "dcssc_rows",
+                                           "dcs_mapq", "dcs_flag", "dcs_tlen", "dcs_rg",
+                                           "dcssc_mapq", "dcssc_flag", "dcssc_tlen", "dcssc_rg")])
+
+
+# output lists in the order of csrc/ccemit.cpp's F_* enum
+FILES = ("sscs.sorted", "singleton.sorted", "dcs.sorted", "sscs.singleton.sorted", "sscs.correction.sorted",
+         "singleton.correction.sorted", "uncorrected.sorted", "sscs.sc.sorted", "dcs.sc.sorted",
+         "sscs.sc.singleton.sorted", "all.unique.dcs.sorted", "badReads")
+_RESULT_DTYPES = dict(read_fam=np.uint32, fam_size=np.uint32, fam_tmpl=np.uint32, fam_mapq=np.uint8, fam_flag=np.uint16,
+                      fam_tlen=np.int32, fam_rg=np.uint8, partner=np.int32, sscs_row=np.int32, corr_row=np.int32,
+                      dcs_row=np.int32, dcssc_row=np.int32, sscs_rows=np.uint8, corr_rows=np.uint8, dcs_rows=np.uint8,
+                      dcssc_rows=np.uint8, dcs_mapq=np.uint8, dcs_flag=np.uint16, dcs_tlen=np.int32, dcs_rg=np.uint8,
+                      dcssc_mapq=np.uint8, dcssc_flag=np.uint16, dcssc_tlen=np.int32, dcssc_rg=np.uint8)
+
+
 def load_library():
     """dlopen libccpack.so (built by `build.build_pack_lib`); raises if it is missing."""
     global _lib
@@ -53,6 +78,8 @@ def load_library():
         "ccp_pack_leftover": (P, [P, u64p]),
         "ccp_pack_dup_bc": (P, [P, u32p]),
         "ccp_pack_dict": (P, [P, C.c_int, u32p, u64p]),
+        "ccp_emit": (C.c_int, [P, C.POINTER(EmitIn), C.c_int, C.POINTER(C.c_char_p), C.c_int,
+                               C.POINTER(C.c_int64), C.c_char_p, C.c_int]),
     }
     for name, (res, args) in protos.items():
         fn = getattr(lib, name)
@@ -65,7 +92,7 @@ SYMBOLS = ("ccp_bam_open", "ccp_bam_close", "ccp_bam_n_records", "ccp_bam_data",
            "ccp_bam_header_text", "ccp_bam_n_refs", "ccp_bam_ref_name", "ccp_bam_ref_len", "ccp_pack_run",
            "ccp_pack_free", "ccp_pack_n", "ccp_pack_geometry", "ccp_pack_fields", "ccp_pack_payload",
            "ccp_pack_src", "ccp_pack_lens", "ccp_pack_counters", "ccp_pack_bad", "ccp_pack_leftover",
-           "ccp_pack_dup_bc", "ccp_pack_dict")
+           "ccp_pack_dup_bc", "ccp_pack_dict", "ccp_emit")
 
 
 def _view(ptr, nbytes, dtype):
@@ -186,3 +213,43 @@ def pack_reads(bamfile, stage="sscs", bdelim="|", regions=None):
         lib.ccp_pack_free(h)
     return PackedReads(fields, payload, lpad, dicts[0], dup_bc, dicts[1], dicts[2], src=src, lens=lens,
                        counters=counters, bad=bad, leftover=leftover)
+
+
+def emit_files(bamfile, packed, res, scorrect, paths, threads=None):
+    """`emit.emit_all` + `bam.write_bam` of every list, in C++ (csrc/ccemit.cpp): writes the BAM
+    (+ BAI for the sorted ones) of each entry of `paths` ({list name: path}, names as in `FILES`)
+    and returns ({list name: record count}, stats text, read_families text)."""
+    from . import emit
+    lib = load_library()
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dt)
+        keep.append(a)
+        return a.ctypes.data if a.size else None
+
+    def joined(names):
+        return b"".join(n.encode() + b"\0" for n in names) + b"\0"
+
+    e = EmitIn()
+    e.n_reads, e.n_fam, e.lpad, e.stride = packed.n, res.n_fam, res.lpad, res.stride
+    e.src = arr(packed.src, np.int64)
+    e.fields = arr(packed.fields, FIELDS_DT)
+    e.barcodes, e.cigar_pairs, e.rgs = joined(packed.barcodes), joined(packed.cigar_pairs), joined(packed.rgs)
+    e.n_bc, e.n_cig, e.n_rg = len(packed.barcodes), len(packed.cigar_pairs), len(packed.rgs)
+    e.bad = arr(np.asarray(packed.bad, np.int64), np.int64)
+    e.n_bad = len(packed.bad)
+    for k, dt in _RESULT_DTYPES.items():
+        setattr(e, k, arr(getattr(res, k), dt))
+    c_paths = (C.c_char_p * len(FILES))(*[os.fsencode(paths[k]) if paths.get(k) else None for k in FILES])
+    counts = (C.c_int64 * len(FILES))()
+    err = C.create_string_buffer(512)
+    rc = lib.ccp_emit(bamfile._h, C.byref(e), 1 if scorrect else 0, c_paths, int(threads or bamfile.threads), counts,
+                      err, len(err))
+    if rc != 0:
+        msg = err.value.decode()
+        if msg.startswith("domain: "):
+            raise DomainError(msg[len("domain: "):])
+        raise ValueError(msg)
+    n = {k: int(counts[i]) for i, k in enumerate(FILES)}
+    return n, emit.stats_text(packed.counters, n, scorrect), emit.families_text(res)
