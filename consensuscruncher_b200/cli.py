@@ -73,7 +73,7 @@ def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bd
     eng = engine or GpuConsensus(device, cutoff=cutoff, scorrect=scorrect)
     try:
         eng.set_params(cutoff=cutoff, scorrect=scorrect)
-        res = eng.consensus(packed, compact="auto")
+        res = eng.consensus(packed)
     finally:
         if own:
             eng.close()

@@ -9,6 +9,8 @@
 //   sort / merge        ConsensusCruncher.py:10-29, :247-251, :281-286
 #include "ccpack.hpp"
 
+#include <chrono>
+#include <cstdlib>
 #include <deque>
 #include <map>
 #include <tuple>
@@ -214,39 +216,26 @@ bool deflate_block(const uint8_t *src, size_t len, int level, std::vector<uint8_
     return true;
 }
 
-// Writes `stream` as BGZF; block_coff[i] = compressed offset of block i (for virtual offsets).
-bool write_bgzf(const std::string &path, const std::vector<uint8_t> &stream, int threads, int level,
-                std::vector<uint64_t> &block_coff, std::string &err)
+// One output file on its way to disk: records -> uncompressed stream -> BGZF blocks -> file (+ index).
+struct FileJob {
+    std::string path;
+    std::vector<const OutRec *> recs;
+    bool coordinate = false, index = false;
+    std::vector<uint8_t> stream;
+    std::vector<uint64_t> rec_off;
+    std::vector<std::vector<uint8_t>> comp;
+    std::string err;
+};
+
+template <typename Fn>
+void parallel_for(size_t n, int threads, Fn fn)
 {
-    const size_t n_blocks = (stream.size() + BGZF_BLOCK - 1) / BGZF_BLOCK;
-    std::vector<std::vector<uint8_t>> comp(n_blocks);
     std::atomic<size_t> next{0};
-    std::atomic<bool> ok{true};
-    auto work = [&]() {
-        for (size_t i; (i = next.fetch_add(1)) < n_blocks;) {
-            size_t a = i * BGZF_BLOCK, len = std::min(BGZF_BLOCK, stream.size() - a);
-            if (!deflate_block(stream.data() + a, len, level, comp[i])) ok = false;
-        }
-    };
-    int nt = std::max(1, std::min(threads, 64));
+    auto work = [&]() { for (size_t i; (i = next.fetch_add(1)) < n;) fn(i); };
+    int nt = (int)std::max<size_t>(1, std::min<size_t>({(size_t)std::max(threads, 1), n, 64}));
     std::vector<std::thread> pool;
     for (int t = 0; t < nt; t++) pool.emplace_back(work);
     for (auto &t : pool) t.join();
-    if (!ok) { err = "deflate failed"; return false; }
-    FILE *fh = fopen(path.c_str(), "wb");
-    if (!fh) { err = "cannot create " + path; return false; }
-    block_coff.assign(n_blocks + 1, 0);
-    uint64_t off = 0;
-    for (size_t i = 0; i < n_blocks; i++) {
-        block_coff[i] = off;
-        if (fwrite(comp[i].data(), 1, comp[i].size(), fh) != comp[i].size()) { fclose(fh); err = "short write to " + path; return false; }
-        off += comp[i].size();
-    }
-    block_coff[n_blocks] = off;
-    static const uint8_t eof[28] = {0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 0xff, 6, 0, 0x42, 0x43, 2, 0, 0x1b, 0, 3, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    fwrite(eof, 1, 28, fh);
-    fclose(fh);
-    return true;
 }
 
 // bam.py:_header_bytes
@@ -278,35 +267,66 @@ std::vector<uint8_t> header_bytes(const ccp_bam *b, bool coordinate)
     return out;
 }
 
-// bam.py:write_bam
-bool write_bam(const std::string &path, const ccp_bam *b, const std::vector<const OutRec *> &recs, bool coordinate,
-               bool index, int threads, std::string &err)
+// bam.py:write_bam for a set of files at once: every file's records are encoded (one task per file),
+// then the 0xFF00-byte blocks of all files are deflated by one pool, then files and indexes are written.
+bool write_bams(const ccp_bam *b, std::vector<FileJob> &jobs, int threads, std::string &err)
 {
-    std::vector<uint8_t> stream = header_bytes(b, coordinate);
-    std::vector<uint64_t> rec_off(recs.size() + 1);
-    for (size_t i = 0; i < recs.size(); i++) {
-        rec_off[i] = stream.size();
-        if (!encode_record(*recs[i], stream, err)) return false;
+    parallel_for(jobs.size(), threads, [&](size_t j) {
+        FileJob &f = jobs[j];
+        f.stream = header_bytes(b, f.coordinate);
+        f.rec_off.resize(f.recs.size() + 1);
+        for (size_t i = 0; i < f.recs.size() && f.err.empty(); i++) {
+            f.rec_off[i] = f.stream.size();
+            encode_record(*f.recs[i], f.stream, f.err);
+        }
+        f.rec_off[f.recs.size()] = f.stream.size();
+        f.comp.resize((f.stream.size() + BGZF_BLOCK - 1) / BGZF_BLOCK);
+    });
+    std::vector<std::pair<uint32_t, uint32_t>> blocks;       // (file, block) over all files
+    for (size_t j = 0; j < jobs.size(); j++) {
+        if (!jobs[j].err.empty()) { err = jobs[j].err; return false; }
+        for (size_t k = 0; k < jobs[j].comp.size(); k++) blocks.emplace_back((uint32_t)j, (uint32_t)k);
     }
-    rec_off[recs.size()] = stream.size();
-    std::vector<uint64_t> coff;
-    if (!write_bgzf(path, stream, threads, 6, coff, err)) return false;
-    if (!index) return true;
-    // virtual offset of an uncompressed position; a position on a block boundary belongs to the block
-    // that ends there while that block is the last one written so far (BgzfWriter.tell before a flush)
-    const size_t n_blocks = coff.size() - 1;
-    auto voff_end = [&](uint64_t u) {                        // tell() right after the bytes up to u were written
-        uint64_t blk = u / BGZF_BLOCK, within = u % BGZF_BLOCK;
-        if (blk >= n_blocks) return (coff[n_blocks] << 16);
-        return (coff[blk] << 16) | within;
-    };
-    BaiBuilder bai(b->ref_names.size());
-    for (size_t i = 0; i < recs.size(); i++) bai.add(*recs[i], voff_end(rec_off[i]), voff_end(rec_off[i + 1]));
-    std::vector<uint8_t> dump = bai.dump();
-    FILE *fh = fopen((path + ".bai").c_str(), "wb");
-    if (!fh) { err = "cannot create " + path + ".bai"; return false; }
-    fwrite(dump.data(), 1, dump.size(), fh);
-    fclose(fh);
+    std::atomic<bool> ok{true};
+    parallel_for(blocks.size(), threads, [&](size_t x) {
+        FileJob &f = jobs[blocks[x].first];
+        size_t a = (size_t)blocks[x].second * BGZF_BLOCK, len = std::min(BGZF_BLOCK, f.stream.size() - a);
+        if (!deflate_block(f.stream.data() + a, len, 6, f.comp[blocks[x].second])) ok = false;
+    });
+    if (!ok) { err = "deflate failed"; return false; }
+    parallel_for(jobs.size(), threads, [&](size_t j) {
+        FileJob &f = jobs[j];
+        FILE *fh = fopen(f.path.c_str(), "wb");
+        if (!fh) { f.err = "cannot create " + f.path; return; }
+        const size_t n_blocks = f.comp.size();
+        std::vector<uint64_t> coff(n_blocks + 1, 0);
+        uint64_t off = 0;
+        for (size_t i = 0; i < n_blocks; i++) {
+            coff[i] = off;
+            if (fwrite(f.comp[i].data(), 1, f.comp[i].size(), fh) != f.comp[i].size()) f.err = "short write to " + f.path;
+            off += f.comp[i].size();
+        }
+        coff[n_blocks] = off;
+        static const uint8_t eof[28] = {0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 0xff, 6, 0, 0x42, 0x43, 2, 0, 0x1b, 0, 3, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        fwrite(eof, 1, 28, fh);
+        fclose(fh);
+        if (!f.index || !f.err.empty()) return;
+        // BgzfWriter.tell() once the bytes before u are written: inside the block still being filled,
+        // or - exactly on a block boundary - at the start of the next block (the EOF block at the end)
+        auto voff = [&](uint64_t u) {
+            uint64_t blk = u / BGZF_BLOCK, within = u % BGZF_BLOCK;
+            return blk >= n_blocks ? (coff[n_blocks] << 16) : ((coff[blk] << 16) | within);
+        };
+        BaiBuilder bai(b->ref_names.size());
+        for (size_t i = 0; i < f.recs.size(); i++) bai.add(*f.recs[i], voff(f.rec_off[i]), voff(f.rec_off[i + 1]));
+        std::vector<uint8_t> dump = bai.dump();
+        FILE *bh = fopen((f.path + ".bai").c_str(), "wb");
+        if (!bh) { f.err = "cannot create " + f.path + ".bai"; return; }
+        fwrite(dump.data(), 1, dump.size(), bh);
+        fclose(bh);
+    });
+    for (auto &f : jobs)
+        if (!f.err.empty()) { err = f.err; return false; }
     return true;
 }
 
@@ -493,6 +513,14 @@ int ccp_emit(ccp_bam *b, const ccp_emit_in *in_p, int scorrect, const char *cons
     Emitter E(b, in);
     const int64_t nf = (int64_t)in.n_fam;
     std::string msg;
+    const bool timing = getenv("CCP_TIMING") != nullptr;
+    auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "ccp_emit %-28s %.3f s\n", what, std::chrono::duration<double>(now - t_start).count());
+        t_start = now;
+    };
     try {
         // the two families a consensus pair name owns (SSCS_maker.py:275 needs exactly two)
         E.mate_fam.resize(nf);
@@ -524,8 +552,10 @@ int ccp_emit(ccp_bam *b, const ccp_emit_in *in_p, int scorrect, const char *cons
                                                 in.fam_tlen[g], in.fam_flag[g], has, rg, t));
             }
         }
+        lap("sscs stage");
         Emitter::sort_records(L[F_SSCS]);
         Emitter::sort_records(L[F_SINGLETON]);
+        lap("sort sscs, singleton");
 
         // ---- DCS stage (DCS_maker.py:226-259), replayed over a sorted record list ---------------------
         auto dcs_stage = [&](const std::vector<OutRec *> &inp, const std::unordered_map<int64_t, OutRec *> &rec_of,
@@ -562,6 +592,7 @@ int ccp_emit(ccp_bam *b, const ccp_emit_in *in_p, int scorrect, const char *cons
         dcs_stage(L[F_SSCS], rec_of, false, L[F_DCS], L[F_SSCS_SINGLETON]);
         Emitter::sort_records(L[F_DCS]);
         Emitter::sort_records(L[F_SSCS_SINGLETON]);
+        lap("dcs stage + sorts");
 
         // ---- singleton correction (singleton_correction.py:249-285) + second DCS pass --------------------
         if (scorrect) {
@@ -594,14 +625,19 @@ int ccp_emit(ccp_bam *b, const ccp_emit_in *in_p, int scorrect, const char *cons
             L[F_ALL_UNIQUE] = Emitter::merged({&L[F_DCS_SC], &L[F_SSCS_SC_SINGLETON], &L[F_UNCORRECTED]});
         }
         for (uint64_t i = 0; i < in.n_bad; i++) L[F_BAD].push_back(E.passthrough(in.bad[i], -1));
+        lap("rescue + second dcs + merges");
 
+        std::vector<FileJob> jobs;
         for (int f = 0; f < F_COUNT; f++) {
             counts[f] = (int64_t)L[f].size();
             if (!paths[f]) continue;
-            std::vector<const OutRec *> recs(L[f].begin(), L[f].end());
-            const bool sorted_file = f != F_BAD;
-            if (!write_bam(paths[f], b, recs, sorted_file, sorted_file, threads, msg)) { set_err(err, errlen, msg); return -1; }
+            FileJob &job = jobs.emplace_back();
+            job.path = paths[f];
+            job.recs.assign(L[f].begin(), L[f].end());
+            job.coordinate = job.index = f != F_BAD;         // every list but badReads is sorted and indexed
         }
+        if (!write_bams(b, jobs, threads, msg)) { set_err(err, errlen, msg); return -1; }
+        lap("encode + deflate + write");
     } catch (const DomainFault &d) {
         set_err(err, errlen, "domain: " + d.msg);
         return -1;
