@@ -32,7 +32,7 @@ struct PhaseTimer {
 };
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
-           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_COUNT = 32 };
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_COUNT = 40 };
 
 }  // namespace
 
@@ -360,15 +360,18 @@ int do_join_index(cc_ctx *ctx)
     while (slots < 2ull * nf) slots <<= 1;
     TRY(ensure(ctx, ctx->table, slots * 8));
     CK(cudaMemsetAsync(ctx->table.p, 0, slots * 8, ctx->stream));
+    CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
+    if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
+    LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(ctx->partner), (uint64_t)nf, -1);
     LAUNCH(join_build_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf,
-           ptr<unsigned long long>(ctx->table), slots - 1);
+           ptr<unsigned long long>(ctx->table), slots - 1, ctr + CT_ASYM);
     LAUNCH(join_probe_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc,
-           ctx->n_bc, ptr<unsigned long long>(ctx->table), slots - 1, ptr<int32_t>(ctx->partner));
+           ctx->n_bc, ptr<unsigned long long>(ctx->table), slots - 1, ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
     TRY(phase_end(ctx, CC_PH_JOIN));
     TRY(phase_begin(ctx, CC_PH_CLASSIFY));
     LAUNCH(classify_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
            (int)ctx->params.scorrect, ptr<uint8_t>(ctx->f_dcs), ptr<uint8_t>(ctx->f_corr),
-           ptr<uint8_t>(ctx->f_dcssc), ptr<unsigned long long>(ctx->stats));
+           ptr<uint8_t>(ctx->f_dcssc), ptr<unsigned long long>(ctx->stats), ctr + CT_ONESIDED);
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcs), nf, ptr<uint32_t>(ctx->dcs_list), ctr + CT_NDCS));
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_corr), nf, ptr<uint32_t>(ctx->corr_list), ctr + CT_NCORR));
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcssc), nf, ptr<uint32_t>(ctx->dcssc_list), ctr + CT_NDCSSC));
@@ -394,6 +397,10 @@ int do_lists(cc_ctx *ctx, bool with_join)
     if (ctx->host_ctr[CT_FAULTS])
         return fail(ctx, CC_ERR_DOMAIN, "a read pair does not found/join its two families together "
                                         "(SSCS_maker.py:275 would not emit this pair name): outside the GPU path's domain");
+    if (ctx->host_ctr[CT_ONESIDED])
+        return fail(ctx, CC_ERR_DOMAIN, "a duplex partnership is not mutual (undotted barcodes of odd length: duplex_tag "
+                                        "applied twice gives another barcode, consensus_helper.py:629-639); what the "
+                                        "reference writes then depends on file order: outside the GPU path's domain");
     ctx->n_sscs = ctx->host_ctr[CT_NSSCS];
     TRY(row_map(ctx, ctx->sscs_row, ctx->sscs_list, ctx->n_sscs));
     if (with_join) {

@@ -249,14 +249,28 @@ read_fam_kernel(const uint32_t *__restrict__ fam_start, const uint32_t *__restri
 }
 
 // ---- K6: complementary-key hash join (duplex_tag, consensus_helper.py:605-648) -------------
+// duplex_tag swaps the barcode halves and R1 <-> R2.  When swapping twice gives the barcode back
+// (every dotted barcode, every undotted one of even length) the relation is symmetric: a partner
+// of an R1 family is an R2 family and finds it back.  Then only the R2 families go into the table,
+// only the R1 families probe, and a hit fills both `partner` entries.  *asym != 0 (some barcode's
+// double swap is another barcode: undotted, odd length) keeps the full build and probe.
+__global__ void dup_symmetry_kernel(const uint32_t *__restrict__ dup_bc, uint32_t n_bc, uint32_t *__restrict__ asym)
+{
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_bc) return;
+    uint32_t d = dup_bc[b];
+    if (d != NO_ID && (d >= n_bc || dup_bc[d] != b)) *asym = 1u;
+}
+
 // table entry: high word = join tag of the family's key hash, low word = family id + 1
 __global__ void __launch_bounds__(256)
 join_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, uint32_t n_fam,
-                  unsigned long long *__restrict__ table, uint64_t mask)
+                  unsigned long long *__restrict__ table, uint64_t mask, const uint32_t *__restrict__ asym)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_fam) return;
     Rec r = load_rec(fields, tmpl[c]);
+    if (!*asym && (r.b.w & 0x40u)) return;          // symmetric join: R1 families only probe
     uint64_t h = rec_hash(r);
     unsigned long long entry = ((h >> 32) << 32) | (unsigned long long)(c + 1);
     uint64_t slot = (h * 0xD6E8FEB86659FD93ull >> 20) & mask;
@@ -266,11 +280,14 @@ join_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__
 __global__ void __launch_bounds__(256)
 join_probe_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, uint32_t n_fam,
                   const uint32_t *__restrict__ dup_bc, uint32_t n_bc,
-                  const unsigned long long *__restrict__ table, uint64_t mask, int32_t *__restrict__ partner)
+                  const unsigned long long *__restrict__ table, uint64_t mask, int32_t *__restrict__ partner,
+                  const uint32_t *__restrict__ asym)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_fam) return;
     Rec r = load_rec(fields, tmpl[c]);
+    const bool symmetric = !*asym;
+    if (symmetric && !(r.b.w & 0x40u)) return;      // an R2 family hears from its R1 partner (partner[] starts at -1)
     int32_t found = -1;
     uint32_t d = r.a.x < n_bc ? __ldg(&dup_bc[r.a.x]) : NO_ID;
     if (d != NO_ID) {
@@ -291,6 +308,7 @@ join_probe_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__
         }
     }
     partner[c] = found;
+    if (symmetric && found >= 0) partner[found] = (int32_t)c;
 }
 
 // ---- classification of families into output classes ----------------------------------------
@@ -306,7 +324,7 @@ __device__ __forceinline__ bool leads_after_sc(uint32_t c, uint32_t p, bool c_bi
 __global__ void __launch_bounds__(256)
 classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict__ partner, uint32_t n_fam,
                 int scorrect, uint8_t *__restrict__ f_dcs, uint8_t *__restrict__ f_corr,
-                uint8_t *__restrict__ f_dcssc, unsigned long long *__restrict__ stats)
+                uint8_t *__restrict__ f_dcssc, unsigned long long *__restrict__ stats, uint32_t *__restrict__ one_sided)
 {
     __shared__ unsigned int s_st[16];
     if (threadIdx.x < 16) s_st[threadIdx.x] = 0;
@@ -315,6 +333,9 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
     if (c < n_fam) {
         bool big = fam_size[c] >= 2;
         int32_t p = partner[c];
+        // a partner that has another partner (undotted barcode of odd length): which strand leads, and
+        // whether the reference survives, depends on file order (DCS_maker.py:231-247) - outside the domain
+        if (p >= 0 && partner[p] != (int32_t)c) atomicAdd(one_sided, 1u);
         bool p_big = p >= 0 && fam_size[p] >= 2;
         bool dcs = big && p_big && c < (uint32_t)p;
         bool corr = scorrect && !big && p >= 0;

@@ -429,6 +429,14 @@ uint64_t cco_domain_faults(void *ctx)
         uint32_t h = c->read_fam[m];
         if (c->fam_tmpl[h] != m || c->fam_size[h] != c->fam_size[g]) bad++;
     }
+    /* a duplex partner that has another partner (duplex_tag is not its own inverse for undotted
+     * barcodes of odd length): the reference's DCS loop then depends on file order and can die on
+     * read_dict[ds] (DCS_maker.py:231-247) */
+    if (c->partner)
+        for (uint64_t g = 0; g < c->n_fam; g++) {
+            int32_t p = c->partner[g];
+            if (p >= 0 && c->partner[p] != (int32_t)g) bad++;
+        }
     return bad;
 }
 

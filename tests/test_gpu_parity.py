@@ -286,3 +286,33 @@ def test_compact_rows_need_a_zero_code(engine):
     rc = engine.lib.cc_load_reads_q4(engine.ctx, packed.fields.ctypes.data, payload4.ctypes.data, packed.n, packed.lpad,
                                      payload4.shape[1], table.ctypes.data, packed.dup_bc.ctypes.data, len(packed.dup_bc))
     assert rc == -2
+
+
+def test_one_sided_duplex_partnerships_are_outside_the_domain(engine):
+    # duplex_tag swaps an undotted barcode at len // 2: for an odd length the swap is not its own inverse,
+    # a family can then have a partner that has another partner (or none).  What the reference writes
+    # in that case depends on file order and it can die on read_dict[ds] (DCS_maker.py:231-247), so both
+    # the GPU path and the oracle report the input instead of inventing an answer.
+    s = synth.generate(seed=93, n_molecules=6000, L=32, umi_len=2, umi_dot=False, region=(0, 1500), insert_sd=3.0,
+                       fam_mean=2.0)
+    reads = s.to_reads()
+    for r in reads:
+        head, bc = r.qname.rsplit("|", 1)
+        r.qname = head + "|" + bc[:3]
+    packed = pack.pack_reads(reads)
+    d = packed.dup_bc
+    has = d != 0xFFFFFFFF
+    assert np.any(d[d[has]] != np.flatnonzero(has))          # the swap really is not an involution here
+    engine.set_params(cutoff=0.7, scorrect=True)
+    with pytest.raises(pack.DomainError):
+        engine.consensus(packed)
+    exp, faults = oracle.run(packed, 0.7, True, return_faults=True)
+    p = exp.partner
+    linked = np.flatnonzero(p >= 0)
+    assert faults == int(np.sum(p[p[linked]] != linked)) > 0
+    # even-length undotted barcodes stay in the domain: the join takes its R1 / R2 shortcut
+    even = synth.generate(seed=94, n_molecules=3000, L=32, umi_len=2, umi_dot=False, region=(0, 1500)).to_packed()
+    got = _both(engine, even)
+    q = got.partner
+    linked = np.flatnonzero(q >= 0)
+    assert len(linked) and np.array_equal(q[q[linked]], linked)
