@@ -85,7 +85,8 @@ __device__ __forceinline__ uint32_t ge7(uint32_t a, uint32_t b) { return ((a | 0
 __device__ __forceinline__ uint32_t nz7(uint32_t x) { return (x + 0x7F7F7F7Fu) & 0x80808080u; }
 
 // the same tests with garbage in bits 0-6: enough when the result only feeds bytes_of()
-__device__ __forceinline__ uint32_t ge7u(uint32_t a, uint32_t b) { return (a | 0x80808080u) - b; }
+// (a + 0x80 == a | 0x80 for bytes < 128; written as a sum so that it is one three-input add)
+__device__ __forceinline__ uint32_t ge7u(uint32_t a, uint32_t b) { return a + 0x80808080u - b; }
 __device__ __forceinline__ uint32_t nz7u(uint32_t x) { return x + 0x7F7F7F7Fu; }
 
 __device__ __forceinline__ uint32_t sel(uint32_t a, uint32_t b, uint32_t mask) { return (a & mask) | (b & ~mask); }
@@ -162,6 +163,12 @@ __device__ __forceinline__ uint32_t cap60(uint32_t q)
     return sel(0x3C3C3C3Cu, lo, big);
 }
 
+// min(60, q) for qualities below 128 (vote_small_kernel: families with larger bytes are voted again, exactly)
+__device__ __forceinline__ uint32_t cap60_lo(uint32_t q)
+{
+    return sel(0x3C3C3C3Cu, q, bytes_of(ge7u(q, 0x3C3C3C3Cu)));
+}
+
 struct QuadOut {
     uint32_t code;       // winner or N per byte
     uint32_t qual;       // consensus quality per byte (valid unless `single` is set there)
@@ -217,7 +224,7 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
     uint32_t lone = bytes_of(nz7u(best)) & ~two;            // winner has exactly one supporter
     uint32_t one_pass = lone & ~bytes_of(ge7u(pass, 0x02020202u));   // ... and it is the only passing read
     o.single = lone & ~one_pass;                           // several passing reads, all different: needs a re-walk
-    o.qual = (two & 0x3C3C3C3Cu) | (cap60(a.qany) & one_pass);     // 60 where two or more passing reads agree
+    o.qual = (two & 0x3C3C3C3Cu) | (cap60_lo(a.qany) & one_pass);     // 60 where two or more passing reads agree
     return o;
 }
 
@@ -304,7 +311,7 @@ __device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t n
     uint32_t ok = (agree | (m1 ^ m2)) & (unanimous_ok ? 0xFFFFFFFFu : 0u);
     if (tie_ok) ok |= clash;
     code = sel(win, 0x0F0F0F0Fu, ok);
-    qual = sel(0x3C3C3C3Cu, cap60(wq), agree) & (m1 | m2);
+    qual = sel(0x3C3C3C3Cu, cap60_lo(wq), agree) & (m1 | m2);
 }
 
 // vsize[row] = family size | flags
@@ -558,7 +565,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                                 for (int g = 0; g < 4; g++) pick[g] |= quad_pick(expand_sel(sel4[g]), q[g], o[g].win, o[g].single);
                             }
 #pragma unroll
-                            for (int g = 0; g < 4; g++) o[g].qual |= cap60(pick[g]) & o[g].single;
+                            for (int g = 0; g < 4; g++) o[g].qual |= cap60_lo(pick[g]) & o[g].single;
                         }
                         uint32_t code[4], qual[4];
 #pragma unroll
