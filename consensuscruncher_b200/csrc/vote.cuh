@@ -22,9 +22,6 @@
 #ifndef VOTE_DEPTH_CFG
 #define VOTE_DEPTH_CFG 2
 #endif
-#ifndef VOTE_FASTMASK
-#define VOTE_FASTMASK 3
-#endif
 #ifndef VOTE_BLOCKS_CFG
 #define VOTE_BLOCKS_CFG 3
 #endif
@@ -37,18 +34,6 @@ constexpr uint32_t VOTE_SMALL_MAX = 127;     // byte-lane compares below need co
 #endif
 constexpr int VOTE_ROWS_PER_BATCH = VOTE_RB_CFG;   // rows per staged batch
 static_assert(12 % VOTE_ROWS_PER_BATCH == 0, "nibble counters are flushed every 12 reads");
-
-__device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem)
-                 : "memory");
-}
-
-__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
-{
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem)
-                 : "memory");
-}
 
 __device__ __forceinline__ void cp_async_16_sh(uint32_t smem, const void *gmem)
 {
@@ -78,14 +63,12 @@ __device__ __forceinline__ uint32_t bytes_of(uint32_t bit7)
     return r;
 }
 
-// bit 7 of each byte: a >= b, for bytes < 128
-__device__ __forceinline__ uint32_t ge7(uint32_t a, uint32_t b) { return ((a | 0x80808080u) - b) & 0x80808080u; }
-
 // bit 7 of each byte: byte != 0, for bytes < 128
 __device__ __forceinline__ uint32_t nz7(uint32_t x) { return (x + 0x7F7F7F7Fu) & 0x80808080u; }
 
-// the same tests with garbage in bits 0-6: enough when the result only feeds bytes_of()
-// (a + 0x80 == a | 0x80 for bytes < 128; written as a sum so that it is one three-input add)
+// bit 7 of each byte: a >= b, resp. byte != 0, for bytes < 128; bits 0-6 are garbage, which is enough
+// when the result only feeds bytes_of().  (a + 0x80 == a | 0x80 for such bytes; written as a sum so
+// that the compare is one three-input add.)
 __device__ __forceinline__ uint32_t ge7u(uint32_t a, uint32_t b) { return a + 0x80808080u - b; }
 __device__ __forceinline__ uint32_t nz7u(uint32_t x) { return x + 0x7F7F7F7Fu; }
 
@@ -124,18 +107,10 @@ struct Quad {
 // again, exactly, by vote_big_kernel (see `hi` in vote_small_kernel).
 __device__ __forceinline__ void quad_add(Quad &a, uint32_t sel16, uint32_t q, uint32_t one)
 {
-#if VOTE_FASTMASK & 1
     uint32_t m = bytes_of(fadd(q, 0x62626262u, one));                       // 0xFF where q >= 30
-#else
-    uint32_t m = bytes_of(fadd(q & 0x7F7F7F7Fu, 0x62626262u, one) | q);
-#endif
     a.ac = fadd(prmt(0x00100100u, 0u, sel16) & m, a.ac, one);
     a.gt = fadd(prmt(0x00000080u, 0x00000001u, sel16) & m & 0x11111111u, a.gt, one);
-#if VOTE_FASTMASK & 2
     a.pc = m * 0xFEFEFEFFu + a.pc;         // 0xFF bytes -> 0x01 bytes: 0xFEFEFEFF is the inverse of 255 mod 2^32
-#else
-    a.pc = fadd(m & 0x01010101u, a.pc, one);
-#endif
     a.qany |= q & m;
 }
 
