@@ -727,7 +727,8 @@ int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *pa
     if (!ctx) return CC_ERR_ARG;
     CK(cudaSetDevice(ctx->device));
     TRY(check_geometry(ctx, fields, payload, n, lpad, stride));
-    if (((uintptr_t)fields & 15) || ((uintptr_t)payload & 15)) return fail(ctx, CC_ERR_ARG, "device buffers must be 16-byte aligned");
+    if (((uintptr_t)fields & 31) || ((uintptr_t)payload & 15))
+        return fail(ctx, CC_ERR_ARG, "device buffers: fields must be 32-byte aligned, payload 16-byte aligned");
     ctx->fields = reinterpret_cast<const uint4 *>(fields);
     ctx->payload = payload;
     ctx->dup_bc = dup_bc;

@@ -18,9 +18,11 @@ struct Rec { uint4 a, b; };
 
 __device__ __forceinline__ Rec load_rec(const uint4 *__restrict__ fields, uint32_t i)
 {
+    // one 256-bit load (sm_100: LDG.E.256): a gathered record is one sector and one LSU request
     Rec r;
-    r.a = __ldg(&fields[2 * (uint64_t)i]);
-    r.b = __ldg(&fields[2 * (uint64_t)i + 1]);
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(r.a.x), "=r"(r.a.y), "=r"(r.a.z), "=r"(r.a.w), "=r"(r.b.x), "=r"(r.b.y), "=r"(r.b.z), "=r"(r.b.w)
+        : "l"(fields + 2 * (uint64_t)i));
     return r;
 }
 

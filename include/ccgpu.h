@@ -134,7 +134,8 @@ int cc_set_stream(cc_ctx *ctx, void *stream);
 int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
                   uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
 
-/* Same, for buffers that already live in DEVICE memory (not copied, must stay valid). */
+/* Same, for buffers that already live in DEVICE memory (not copied, must stay valid);
+ * fields 32-byte aligned, payload 16-byte aligned (any cudaMalloc'd buffer is). */
 int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
                          uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
 
