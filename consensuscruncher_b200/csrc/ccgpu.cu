@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
 #include "../../include/ccgpu.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -12,6 +13,7 @@
 #include "radix_onesweep.cuh"
 #include "scan.cuh"
 #include "vote.cuh"
+#include "group_hash.cuh"
 
 using namespace ccgpu;
 
@@ -67,6 +69,8 @@ struct cc_ctx {
     bool thr_valid = false;
     DevBuf tmp_a, tmp_b, tmp_c;   // stand-alone primitives
     DevBuf cs_in, cs_k0, cs_k1, cs_v0, cs_v1;   // cc_sort_coordinates
+    DevBuf gtable;                              // hash grouping (group_hash.cuh)
+    bool group_by_hash = true;
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
     uint32_t host_ctr[CT_COUNT];
@@ -212,14 +216,14 @@ int compact_flags(cc_ctx *ctx, const uint8_t *flags, uint64_t n, uint32_t *list,
 }
 
 // out[w] = number of set bits in words[0 .. w)
-int scan_popcounts(cc_ctx *ctx, const uint32_t *words, uint32_t *out, uint64_t n)
+int scan_popcounts(cc_ctx *ctx, const uint32_t *words, uint32_t *out, uint64_t n, uint32_t *total = nullptr)
 {
     if (n == 0) return CC_OK;
     uint32_t *ticket;
     TRY(scan_prepare(ctx, n, &ticket));
     auto kernel = scan_kernel<SCAN_MODE_POPC, uint32_t>;
     LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, words, out, (uint32_t *)nullptr, n,
-           ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr);
+           ptr<unsigned long long>(ctx->scan_status), ticket, total);
     return CC_OK;
 }
 
@@ -271,6 +275,60 @@ int onesweep_pairs(cc_ctx *ctx, uint32_t *k0, uint32_t *k1, const uint32_t *vals
     return CC_OK;
 }
 
+// Grouping through the hash table of group_hash.cuh; leaves exactly what the sort path leaves
+// (families in creation order, segments of `perm`, templates, singleton fields, class bytes,
+// size histogram, SSCS list) plus read -> family, which the sort path only builds on demand.
+int do_group_hash(cc_ctx *ctx)
+{
+    const uint64_t n = ctx->n;
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
+    TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
+    TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
+    uint32_t *read_slot = ptr<uint32_t>(ctx->key_a), *ticket = ptr<uint32_t>(ctx->key_b);
+    uint64_t slots = 1024;
+    while (slots < n + n / 4) slots <<= 1;                  // load factor <= 0.8 even if every read is a family
+    TRY(ensure(ctx, ctx->gtable, slots * sizeof(GroupSlot)));
+    GroupSlot *table = ptr<GroupSlot>(ctx->gtable);
+    const uint64_t words = (n + 31) / 32;
+    TRY(ensure(ctx, ctx->bitmap, words * 4)); TRY(ensure(ctx, ctx->word_rank, words * 4));
+
+    TRY(phase_begin(ctx, CC_PH_HASH));
+    CK(cudaMemsetAsync(table, 0xFF, slots * sizeof(GroupSlot), ctx->stream));
+    LAUNCH(group_insert_kernel, blocks_for(n, 256), 256, ctx->fields, n, table, slots - 1, read_slot, ticket);
+    TRY(phase_end(ctx, CC_PH_HASH));
+
+    TRY(phase_begin(ctx, CC_PH_SEGMENT));
+    LAUNCH(group_mark_kernel, blocks_for(n, 256), 256, table, read_slot, n, ptr<uint32_t>(ctx->bitmap));
+    TRY(scan_popcounts(ctx, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), words, ctr + CT_NFAM));
+    TRY(read_counters(ctx));
+    const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
+
+    TRY(ensure(ctx, ctx->tmpl, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->fam_start, (size_t)nf * 4)); TRY(ensure(ctx, ctx->fam_size, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->is_sscs, (size_t)nf + 4)); TRY(ensure(ctx, ctx->fam_mapq, nf)); TRY(ensure(ctx, ctx->fam_rg, nf));
+    TRY(ensure(ctx, ctx->fam_flag, (size_t)nf * 2)); TRY(ensure(ctx, ctx->fam_tlen, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4));
+    LAUNCH(group_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, table, read_slot, n,
+           ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->val_b), ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size),
+           ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
+           ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
+           (uint32_t)CC_HIST_BINS, ctr + CT_NMID);
+    TRY(scan_exclusive(ctx, ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), nf));
+    ctx->perm = ptr<uint32_t>(ctx->val_a);
+    ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family
+    ctx->sorted_keys = ctx->spare_keys = nullptr;
+    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ctx->fields, table, read_slot, ticket, n,
+           ptr<uint32_t>(ctx->fam_start), ctx->perm, ctx->spare_vals, ptr<uint32_t>(ctx->is_sscs));
+    ctx->read_fam_ready = true;
+    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
+           ctr + CT_FAULTS);
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS));
+    TRY(phase_end(ctx, CC_PH_SEGMENT));
+    ctx->grouped = true;
+    return CC_OK;
+}
+
 int do_group(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
@@ -285,6 +343,7 @@ int do_group(cc_ctx *ctx)
     CK(cudaMemsetAsync(ctx->hist.p, 0, CC_HIST_BINS * sizeof(unsigned long long), ctx->stream));
     memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
     if (n == 0) { ctx->grouped = true; return CC_OK; }
+    if (ctx->group_by_hash) return do_group_hash(ctx);
 
     TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
     TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
@@ -611,6 +670,7 @@ cc_ctx *cc_create(int device, const cc_params *params)
         return nullptr;
     }
     cc_ctx *ctx = new cc_ctx();
+    if (const char *g = getenv("CCGPU_GROUP")) ctx->group_by_hash = strcmp(g, "sort") != 0;   // "sort": the radix-sort grouping
     ctx->device = device;
     if (params) ctx->params = *params;
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -635,7 +695,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
                      &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->mid_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
-                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1};
+                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);

@@ -1,0 +1,132 @@
+// Grouping reads into tag families with a hash table instead of a sort (sm_100a).
+//
+// read_bam's dictionaries (consensus_helper.py:447-475: `tag in read_dict`, append, size + 1) map
+// directly onto an open-addressing table keyed by the exact family tuple.  A slot holds the
+// smallest read index seen so far of its family (any member identifies the tuple, the smallest is
+// the family's first read = template) and a member counter.  Reads of a family sit next to each
+// other in a coordinate-sorted input, so after the first member the slot, the template's record and
+// the counter are cache hits; what reaches DRAM is about one probe per family, not per read.
+//
+//   insert   every read finds / claims its slot, keeps the slot's read index minimal, takes a ticket
+//   mark     a read that is still its slot's index is the family's first read: one bit per read
+//   (popcount scan of the bitmap: family number = rank of the first read = creation order)
+//   family   first reads write the family records and their own read -> family entry
+//   (exclusive scan of the sizes: segment starts)
+//   place    every read copies its first read's family number and goes to segment start + ticket;
+//            differing mode fields flag the family
+//
+// Tickets come from an atomic counter, so the order of a family's members in `perm` is arbitrary;
+// everything downstream is independent of it (votes count, lone supporters are unique, mode ties
+// are decided by read index - see group_mode / warp_mode).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "kernels.cuh"
+
+namespace ccgpu {
+
+struct GroupSlot {
+    uint32_t rep;       // smallest member index so far (0xFFFFFFFF = empty); in the end the family's first read
+    uint32_t cnt;       // members - 1 (the table is cleared to 0xFF bytes)
+};
+
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(256)
+group_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__restrict__ table, uint64_t mask,
+                    uint32_t *__restrict__ read_slot, uint32_t *__restrict__ ticket)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Rec r = load_rec(fields, (uint32_t)i);
+    uint64_t slot = (rec_hash(r) * 0xD6E8FEB86659FD93ull >> 20) & mask;
+    for (;;) {
+        uint32_t rep = ld_relaxed_u32(&table[slot].rep);
+        if (rep == 0xFFFFFFFFu) {
+            rep = atomicCAS(&table[slot].rep, 0xFFFFFFFFu, (uint32_t)i);
+            if (rep == 0xFFFFFFFFu) break;                      // claimed: this read founds the family
+        }
+        if (same_tag(r, load_rec(fields, rep))) {                // any member carries the family's tuple
+            if ((uint32_t)i < rep) atomicMin(&table[slot].rep, (uint32_t)i);
+            break;
+        }
+        slot = (slot + 1) & mask;
+    }
+    read_slot[i] = (uint32_t)slot;
+    ticket[i] = atomicAdd(&table[slot].cnt, 1u) + 1u;           // cnt starts at 0xFFFFFFFF: first ticket is 0
+}
+
+__global__ void __launch_bounds__(256)
+group_mark_kernel(const GroupSlot *__restrict__ table, const uint32_t *__restrict__ read_slot, uint64_t n,
+                  uint32_t *__restrict__ bitmap)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool first = i < n && table[read_slot[i]].rep == (uint32_t)i;
+    const uint32_t word = __ballot_sync(0xffffffffu, first);    // 32 consecutive reads = one bitmap word
+    if ((threadIdx.x & 31) == 0 && i < n) bitmap[i >> 5] = word;
+}
+
+// family records in creation order (what family_build_kernel writes on the sort path)
+__global__ void __launch_bounds__(256)
+group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restrict__ table,
+                    const uint32_t *__restrict__ read_slot, uint64_t n, const uint32_t *__restrict__ bitmap,
+                    const uint32_t *__restrict__ word_rank, uint32_t *__restrict__ read_fam, uint32_t *__restrict__ tmpl,
+                    uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs, uint8_t *__restrict__ fam_mapq,
+                    uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
+                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid)
+{
+    __shared__ uint32_t small_hist[256];           // sizes < 256 are counted per block first
+    small_hist[threadIdx.x] = 0;
+    __syncthreads();
+    // grid-stride: a few CTAs per SM, so the shared histogram is flushed a few thousand times in all
+    // (the global bins are a handful of addresses; one flush per 256 reads would serialise on them)
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t w = bitmap[i >> 5], bit = 1u << (i & 31);
+        if (!(w & bit)) continue;
+        const uint32_t c = word_rank[i >> 5] + __popc(w & (bit - 1u));
+        const uint32_t size = table[read_slot[i]].cnt + 1u;
+        read_fam[i] = c;                                     // the other members copy it from here (group_place_kernel)
+        tmpl[c] = (uint32_t)i;
+        fam_size[c] = size;
+        is_sscs[c] = size >= 2 ? 1 : 0;                      // bit 1 (mode fields differ) is set by group_place_kernel
+        const uint4 b = __ldg(&fields[2 * i + 1]);
+        fam_tlen[c] = (int32_t)b.z;
+        fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
+        fam_mapq[c] = (uint8_t)((b.w >> 16) & 0xFF);
+        fam_rg[c] = (uint8_t)(b.w >> 24);
+        const uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
+        if (bin < 256) atomicAdd(&small_hist[bin], 1u);
+        else atomicAdd(&hist[bin], 1ull);
+    }
+    __syncthreads();
+    const uint32_t v = small_hist[threadIdx.x];
+    if (v) atomicAdd(&hist[threadIdx.x], (unsigned long long)v);
+    if (v && threadIdx.x >= 16 && threadIdx.x < 128) atomicAdd(n_mid, v);   // families of 16..127 reads
+}
+
+__global__ void __launch_bounds__(256)
+group_place_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restrict__ table,
+                   const uint32_t *__restrict__ read_slot, const uint32_t *__restrict__ ticket, uint64_t n,
+                   const uint32_t *__restrict__ fam_start, uint32_t *__restrict__ perm, uint32_t *read_fam,
+                   uint32_t *__restrict__ class_words)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t t = table[read_slot[i]].rep;                 // the family's first read
+    const uint32_t c = read_fam[t];                              // written by group_family_kernel; t == i reads its own entry
+    perm[fam_start[c] + ticket[i]] = (uint32_t)i;
+    if (t != (uint32_t)i) {
+        read_fam[i] = c;
+        // tlen / flag / mapq / RG differ from the first read's: the family needs real modes (bit 1 of its class byte)
+        const uint4 mine = __ldg(&fields[2 * i + 1]), first = __ldg(&fields[2 * (uint64_t)t + 1]);
+        if (mine.z != first.z || mine.w != first.w) atomicOr(&class_words[c >> 2], 2u << (8 * (c & 3)));
+    }
+}
+
+}  // namespace ccgpu

@@ -407,15 +407,17 @@ __device__ __forceinline__ void vote_row(VoteAcc &a, uint32_t q, uint32_t s16, u
 // read_mode, consensus_helper.py:491-495); flags prefer 99 > 83 > 147 > 163 on a tie (:521-531)
 __device__ __forceinline__ int flag_rank(uint32_t v) { return v == 99 ? 0 : v == 83 ? 1 : v == 147 ? 2 : v == 163 ? 3 : 4; }
 
-template <typename Get>
-__device__ uint32_t warp_mode(Get get, uint32_t n, bool is_flag, int lane)
+// get(j) = value of member j, idx(j) = its read index.  "First appearing" is decided by read index, not
+// by position in the member list, so the list may be in any order.
+template <typename Get, typename Idx>
+__device__ uint32_t warp_mode(Get get, Idx idx, uint32_t n, bool is_flag, int lane)
 {
-    uint32_t best = 0, best_cnt = 0;
+    uint32_t best = 0, best_cnt = 0, best_first = 0xFFFFFFFFu;
     int best_rank = 9;
     uint32_t counted = 0;
     for (uint32_t i = 0; counted < n && i < n; i++) {
         uint32_t vi = get(i);
-        uint32_t cnt = 0;
+        uint32_t cnt = 0, first = 0xFFFFFFFFu;
         bool seen_before = false;
         for (uint32_t j0 = 0; j0 < n; j0 += 32) {
             uint32_t j = j0 + lane;
@@ -423,11 +425,15 @@ __device__ uint32_t warp_mode(Get get, uint32_t n, bool is_flag, int lane)
             uint32_t b = __ballot_sync(0xffffffffu, m);
             if (cnt == 0 && b && j0 + (uint32_t)__ffs(b) - 1u < i) { seen_before = true; break; }
             cnt += __popc(b);
+            if (m) first = min(first, idx(j));
         }
         if (seen_before) continue;
+        first = __reduce_min_sync(0xffffffffu, first);
         counted += cnt;
         int rank = is_flag ? flag_rank(vi) : 4;
-        if (cnt > best_cnt || (cnt == best_cnt && rank < best_rank)) { best = vi; best_cnt = cnt; best_rank = rank; }
+        if (cnt > best_cnt || (cnt == best_cnt && (rank < best_rank || (rank == best_rank && first < best_first)))) {
+            best = vi; best_cnt = cnt; best_rank = rank; best_first = first;
+        }
     }
     return best;
 }
@@ -521,10 +527,11 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
     }
     uint32_t tlen = m0.z, flag = m0.w & 0xFFFF, mapq = (m0.w >> 16) & 0xFF, rg = m0.w >> 24;
     if (!uniform) {
-        tlen = warp_mode([&](uint32_t j) { return meta_of(j).z; }, n, false, lane);
-        flag = warp_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, n, true, lane);
-        mapq = warp_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, n, false, lane);
-        rg = has_rg ? warp_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, n, false, lane) : 0xFFu;
+        auto idx_of = [&](uint32_t j) { return perm[start + j]; };
+        tlen = warp_mode([&](uint32_t j) { return meta_of(j).z; }, idx_of, n, false, lane);
+        flag = warp_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, idx_of, n, true, lane);
+        mapq = warp_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, idx_of, n, false, lane);
+        rg = has_rg ? warp_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, idx_of, n, false, lane) : 0xFFu;
     }
     if (lane == 0) {
         fam_tlen[c] = (int32_t)tlen; fam_flag[c] = (uint16_t)flag;

@@ -244,13 +244,15 @@ __device__ __forceinline__ void join_row(const uint32_t code[4], const uint32_t 
 }
 
 // mode of one field over a family held by a lane group (slow path: fields differ inside the family)
-template <typename Get>
-__device__ uint32_t group_mode(Get get, uint32_t n, bool is_flag, int gl, int G, uint32_t gmask)
+// (a tie goes to the value whose first occurrence has the smallest read index - idx(j) - so the member
+// list may be in any order)
+template <typename Get, typename Idx>
+__device__ uint32_t group_mode(Get get, Idx idx, uint32_t n, bool is_flag, int gl, int G, uint32_t gmask)
 {
-    uint32_t best = 0, best_cnt = 0, counted = 0;
+    uint32_t best = 0, best_cnt = 0, counted = 0, best_first = 0xFFFFFFFFu;
     int best_rank = 9;
     for (uint32_t i = 0; counted < n && i < n; i++) {
-        uint32_t vi = get(i), cnt = 0;
+        uint32_t vi = get(i), cnt = 0, first = 0xFFFFFFFFu;
         bool seen_before = false;
         for (uint32_t j0 = 0; j0 < n; j0 += G) {
             uint32_t j = j0 + gl;
@@ -258,11 +260,15 @@ __device__ uint32_t group_mode(Get get, uint32_t n, bool is_flag, int gl, int G,
             uint32_t b = __ballot_sync(gmask, m) & gmask;
             if (cnt == 0 && b && j0 + (uint32_t)(__ffs(b) - 1 - (__ffs(gmask) - 1)) < i) { seen_before = true; break; }
             cnt += __popc(b);
+            if (m) first = min(first, idx(j));
         }
         if (seen_before) continue;
+        for (int d = G >> 1; d >= 1; d >>= 1) first = min(first, __shfl_xor_sync(gmask, first, d));
         counted += cnt;
         int rank = is_flag ? flag_rank(vi) : 4;
-        if (cnt > best_cnt || (cnt == best_cnt && rank < best_rank)) { best = vi; best_cnt = cnt; best_rank = rank; }
+        if (cnt > best_cnt || (cnt == best_cnt && (rank < best_rank || (rank == best_rank && first < best_first)))) {
+            best = vi; best_cnt = cnt; best_rank = rank; best_first = first;
+        }
     }
     return best;
 }
@@ -576,10 +582,11 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                 uint32_t rg_ok = __ballot_sync(gmask, j >= n || (meta_of(j).w >> 24) != 0xFFu) & gmask;
                 has_rg = has_rg && rg_ok == gmask;
             }
-            uint32_t tlen = group_mode([&](uint32_t j) { return meta_of(j).z; }, n, false, gl, G, gmask);
-            uint32_t flag = group_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, n, true, gl, G, gmask);
-            uint32_t mapq = group_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, n, false, gl, G, gmask);
-            uint32_t rg = has_rg ? group_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, n, false, gl, G, gmask) : 0xFFu;
+            auto idx_of = [&](uint32_t j) { return __ldg(&perm[start + j]); };
+            uint32_t tlen = group_mode([&](uint32_t j) { return meta_of(j).z; }, idx_of, n, false, gl, G, gmask);
+            uint32_t flag = group_mode([&](uint32_t j) { return meta_of(j).w & 0xFFFFu; }, idx_of, n, true, gl, G, gmask);
+            uint32_t mapq = group_mode([&](uint32_t j) { return (meta_of(j).w >> 16) & 0xFFu; }, idx_of, n, false, gl, G, gmask);
+            uint32_t rg = has_rg ? group_mode([&](uint32_t j) { return meta_of(j).w >> 24; }, idx_of, n, false, gl, G, gmask) : 0xFFu;
             if (gl == 0) {
                 const uint32_t c = __ldg(&sscs_list[row]);
                 fam_tlen[c] = (int32_t)tlen; fam_flag[c] = (uint16_t)flag;
