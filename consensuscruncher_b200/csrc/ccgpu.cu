@@ -318,8 +318,8 @@ int do_group_hash(cc_ctx *ctx)
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family
     ctx->sorted_keys = ctx->spare_keys = nullptr;
-    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ctx->fields, table, read_slot, ticket, n,
-           ptr<uint32_t>(ctx->fam_start), ctx->perm, ctx->spare_vals, ptr<uint32_t>(ctx->is_sscs));
+    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, table, read_slot, ticket, n, ptr<uint32_t>(ctx->fam_start),
+           ctx->perm, ctx->spare_vals);
     ctx->read_fam_ready = true;
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);

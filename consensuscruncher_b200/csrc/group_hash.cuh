@@ -12,8 +12,7 @@
 //   (popcount scan of the bitmap: family number = rank of the first read = creation order)
 //   family   first reads write the family records and their own read -> family entry
 //   (exclusive scan of the sizes: segment starts)
-//   place    every read copies its first read's family number and goes to segment start + ticket;
-//            differing mode fields flag the family
+//   place    every read copies its first read's family number and goes to segment start + ticket
 //
 // Tickets come from an atomic counter, so the order of a family's members in `perm` is arbitrary;
 // everything downstream is independent of it (votes count, lone supporters are unique, mode ties
@@ -28,7 +27,10 @@ namespace ccgpu {
 
 struct GroupSlot {
     uint32_t rep;       // smallest member index so far (0xFFFFFFFF = empty); in the end the family's first read
-    uint32_t cnt;       // members - 1 (the table is cleared to 0xFF bytes)
+    uint32_t cnt;       // starts at 0xFFFFFFFF (the table is cleared to 0xFF bytes); every member subtracts 2,
+                        // so a ticket is (~old) >> 1 and the size (~cnt) >> 1; bit 0 is cleared once two
+                        // members are seen to differ in tlen / flag / mapq / RG (the family needs real
+                        // modes) - clearing it never borrows, so tickets are the same either way
 };
 
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p)
@@ -52,14 +54,18 @@ group_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__r
             rep = atomicCAS(&table[slot].rep, 0xFFFFFFFFu, (uint32_t)i);
             if (rep == 0xFFFFFFFFu) break;                      // claimed: this read founds the family
         }
-        if (same_tag(r, load_rec(fields, rep))) {                // any member carries the family's tuple
+        const Rec q = load_rec(fields, rep);
+        if (same_tag(r, q)) {                                    // any member carries the family's tuple
             if ((uint32_t)i < rep) atomicMin(&table[slot].rep, (uint32_t)i);
+            // every member but the founder is compared with an earlier one: the comparisons span the
+            // family, so no difference on any of them means the mode fields are uniform
+            if (r.b.z != q.b.z || r.b.w != q.b.w) atomicAnd(&table[slot].cnt, ~1u);
             break;
         }
         slot = (slot + 1) & mask;
     }
     read_slot[i] = (uint32_t)slot;
-    ticket[i] = atomicAdd(&table[slot].cnt, 1u) + 1u;           // cnt starts at 0xFFFFFFFF: first ticket is 0
+    ticket[i] = (~atomicSub(&table[slot].cnt, 2u)) >> 1;
 }
 
 __global__ void __launch_bounds__(256)
@@ -90,11 +96,12 @@ group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restric
         const uint32_t w = bitmap[i >> 5], bit = 1u << (i & 31);
         if (!(w & bit)) continue;
         const uint32_t c = word_rank[i >> 5] + __popc(w & (bit - 1u));
-        const uint32_t size = table[read_slot[i]].cnt + 1u;
+        const uint32_t cnt = table[read_slot[i]].cnt;
+        const uint32_t size = (~cnt) >> 1;
         read_fam[i] = c;                                     // the other members copy it from here (group_place_kernel)
         tmpl[c] = (uint32_t)i;
         fam_size[c] = size;
-        is_sscs[c] = size >= 2 ? 1 : 0;                      // bit 1 (mode fields differ) is set by group_place_kernel
+        is_sscs[c] = size >= 2 ? ((cnt & 1u) ? 1 : 3) : 0;   // bit 0: has a consensus row, bit 1: mode fields differ
         const uint4 b = __ldg(&fields[2 * i + 1]);
         fam_tlen[c] = (int32_t)b.z;
         fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
@@ -111,22 +118,16 @@ group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restric
 }
 
 __global__ void __launch_bounds__(256)
-group_place_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restrict__ table,
-                   const uint32_t *__restrict__ read_slot, const uint32_t *__restrict__ ticket, uint64_t n,
-                   const uint32_t *__restrict__ fam_start, uint32_t *__restrict__ perm, uint32_t *read_fam,
-                   uint32_t *__restrict__ class_words)
+group_place_kernel(const GroupSlot *__restrict__ table, const uint32_t *__restrict__ read_slot,
+                   const uint32_t *__restrict__ ticket, uint64_t n, const uint32_t *__restrict__ fam_start,
+                   uint32_t *__restrict__ perm, uint32_t *read_fam)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t t = table[read_slot[i]].rep;                 // the family's first read
     const uint32_t c = read_fam[t];                              // written by group_family_kernel; t == i reads its own entry
     perm[fam_start[c] + ticket[i]] = (uint32_t)i;
-    if (t != (uint32_t)i) {
-        read_fam[i] = c;
-        // tlen / flag / mapq / RG differ from the first read's: the family needs real modes (bit 1 of its class byte)
-        const uint4 mine = __ldg(&fields[2 * i + 1]), first = __ldg(&fields[2 * (uint64_t)t + 1]);
-        if (mine.z != first.z || mine.w != first.w) atomicOr(&class_words[c >> 2], 2u << (8 * (c & 3)));
-    }
+    if (t != (uint32_t)i) read_fam[i] = c;
 }
 
 }  // namespace ccgpu

@@ -316,3 +316,16 @@ def test_one_sided_duplex_partnerships_are_outside_the_domain(engine):
     q = got.partner
     linked = np.flatnonzero(q >= 0)
     assert len(linked) and np.array_equal(q[q[linked]], linked)
+
+
+def test_sort_grouping_path_gives_the_same_result(monkeypatch):
+    # CCGPU_GROUP=sort selects the radix-sort grouping (hash keys, stable onesweep sort, exact boundaries);
+    # the default is the hash table of group_hash.cuh.  Same families, same numbering, same everything.
+    monkeypatch.setenv("CCGPU_GROUP", "sort")
+    cases = [synth.generate(seed=41, n_molecules=2500, L=128).to_packed(),
+             synth.generate(seed=42, n_molecules=800, L=64, mapq_mixed=True, max_family=40, dist="const", fam_mean=20).to_packed(),
+             synth.generate(seed=61, n_molecules=30000, L=32, umi_len=2, region=(0, 1200), fam_mean=1.5, insert_sd=8.0).to_packed(),
+             helpers.load_case("mode_ties")[2]]
+    with GpuConsensus(0, cutoff=0.7, scorrect=True) as by_sort:
+        for packed in cases:
+            helpers.assert_same_result(by_sort.consensus(packed), oracle.run(packed, 0.7, True))
