@@ -199,19 +199,22 @@ int scan_exclusive(cc_ctx *ctx, const uint32_t *in, uint32_t *out, uint64_t n)
     TRY(scan_prepare(ctx, n, &ticket));
     auto kernel = scan_kernel<SCAN_MODE_EXCL, uint32_t>;
     LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, in, out, (uint32_t *)nullptr, n,
-           ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr);
+           ptr<unsigned long long>(ctx->scan_status), ticket, (uint32_t *)nullptr, (int32_t *)nullptr,
+           (const int32_t *)nullptr, (const uint32_t *)nullptr);
     return CC_OK;
 }
 
 // list[rank] = index of every non-zero flag; *total (device) = how many
-int compact_flags(cc_ctx *ctx, const uint8_t *flags, uint64_t n, uint32_t *list, uint32_t *total)
+// optionally also the inverse map: row_out[i] = *row_base + rank if flagged, else row_alt[i] (-1 without row_alt)
+int compact_flags(cc_ctx *ctx, const uint8_t *flags, uint64_t n, uint32_t *list, uint32_t *total,
+                  int32_t *row_out = nullptr, const int32_t *row_alt = nullptr, const uint32_t *row_base = nullptr)
 {
     if (n == 0) return CC_OK;   // *total was zeroed with the counter block
     uint32_t *ticket;
     TRY(scan_prepare(ctx, n, &ticket));
     auto kernel = scan_kernel<SCAN_MODE_COMPACT, uint8_t>;
     LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, flags, list, (uint32_t *)nullptr,
-           n, ptr<unsigned long long>(ctx->scan_status), ticket, total);
+           n, ptr<unsigned long long>(ctx->scan_status), ticket, total, row_out, row_alt, row_base);
     return CC_OK;
 }
 
@@ -223,7 +226,8 @@ int scan_popcounts(cc_ctx *ctx, const uint32_t *words, uint32_t *out, uint64_t n
     TRY(scan_prepare(ctx, n, &ticket));
     auto kernel = scan_kernel<SCAN_MODE_POPC, uint32_t>;
     LAUNCH(kernel, (unsigned)scan_tiles(n), SCAN_THREADS, words, out, (uint32_t *)nullptr, n,
-           ptr<unsigned long long>(ctx->scan_status), ticket, total);
+           ptr<unsigned long long>(ctx->scan_status), ticket, total, (int32_t *)nullptr, (const int32_t *)nullptr,
+           (const uint32_t *)nullptr);
     return CC_OK;
 }
 
@@ -323,7 +327,9 @@ int do_group_hash(cc_ctx *ctx)
     ctx->read_fam_ready = true;
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS));
+    TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS,
+                      ptr<int32_t>(ctx->sscs_row)));
     TRY(phase_end(ctx, CC_PH_SEGMENT));
     ctx->grouped = true;
     return CC_OK;
@@ -398,7 +404,9 @@ int do_group(cc_ctx *ctx)
            (uint32_t)CC_HIST_BINS, ctr + CT_NMID);
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS));
+    TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS,
+                      ptr<int32_t>(ctx->sscs_row)));
     TRY(phase_end(ctx, CC_PH_SEGMENT));
     ctx->grouped = true;
     return CC_OK;
@@ -431,25 +439,21 @@ int do_join_index(cc_ctx *ctx)
     LAUNCH(classify_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
            (int)ctx->params.scorrect, ptr<uint8_t>(ctx->f_dcs), ptr<uint8_t>(ctx->f_corr),
            ptr<uint8_t>(ctx->f_dcssc), ptr<unsigned long long>(ctx->stats), ctr + CT_ONESIDED);
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcs), nf, ptr<uint32_t>(ctx->dcs_list), ctr + CT_NDCS));
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_corr), nf, ptr<uint32_t>(ctx->corr_list), ctr + CT_NCORR));
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcssc), nf, ptr<uint32_t>(ctx->dcssc_list), ctr + CT_NDCSSC));
+    // the compactions also leave family -> output row; in the second DCS pass the SSCS-SSCS pairs keep
+    // their DCS row and the pairs with a corrected singleton follow in the same pool
+    TRY(ensure(ctx, ctx->dcs_row, (size_t)nf * 4)); TRY(ensure(ctx, ctx->corr_row, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->dcssc_row, (size_t)nf * 4));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcs), nf, ptr<uint32_t>(ctx->dcs_list), ctr + CT_NDCS,
+                      ptr<int32_t>(ctx->dcs_row)));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_corr), nf, ptr<uint32_t>(ctx->corr_list), ctr + CT_NCORR,
+                      ptr<int32_t>(ctx->corr_row)));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcssc), nf, ptr<uint32_t>(ctx->dcssc_list), ctr + CT_NDCSSC,
+                      ptr<int32_t>(ctx->dcssc_row), ctx->params.scorrect ? ptr<int32_t>(ctx->dcs_row) : nullptr,
+                      ctr + CT_NDCS));
     TRY(phase_end(ctx, CC_PH_CLASSIFY));
     return CC_OK;
 }
 
-int row_map(cc_ctx *ctx, DevBuf &row, DevBuf &list, uint32_t n_rows, uint32_t first_row = 0, bool clear = true)
-{
-    const uint32_t nf = ctx->n_fam;
-    TRY(ensure(ctx, row, (size_t)nf * 4));
-    if (nf == 0) return CC_OK;
-    if (clear) LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(row), (uint64_t)nf, -1);
-    if (n_rows)
-        LAUNCH(rows_from_list_kernel, blocks_for(n_rows, 256), 256, ptr<uint32_t>(list), n_rows, ptr<int32_t>(row), first_row);
-    return CC_OK;
-}
-
-// counts known on the host -> row maps
 int do_lists(cc_ctx *ctx, bool with_join)
 {
     TRY(read_counters(ctx));
@@ -460,18 +464,12 @@ int do_lists(cc_ctx *ctx, bool with_join)
         return fail(ctx, CC_ERR_DOMAIN, "a duplex partnership is not mutual (undotted barcodes of odd length: duplex_tag "
                                         "applied twice gives another barcode, consensus_helper.py:629-639); what the "
                                         "reference writes then depends on file order: outside the GPU path's domain");
-    ctx->n_sscs = ctx->host_ctr[CT_NSSCS];
-    TRY(row_map(ctx, ctx->sscs_row, ctx->sscs_list, ctx->n_sscs));
+    ctx->n_sscs = ctx->host_ctr[CT_NSSCS];               // family -> row maps were written by the compactions
     if (with_join) {
         ctx->n_dcs = ctx->host_ctr[CT_NDCS];
         ctx->n_corr = ctx->host_ctr[CT_NCORR];
         ctx->n_extra = ctx->host_ctr[CT_NDCSSC];
         ctx->n_dcssc = ctx->params.scorrect ? ctx->n_dcs + ctx->n_extra : 0;
-        TRY(row_map(ctx, ctx->dcs_row, ctx->dcs_list, ctx->n_dcs));
-        TRY(row_map(ctx, ctx->corr_row, ctx->corr_list, ctx->n_corr));
-        // second pass: SSCS-SSCS pairs keep their DCS row, the others follow in the same pool
-        TRY(row_map(ctx, ctx->dcssc_row, ctx->dcs_list, ctx->params.scorrect ? ctx->n_dcs : 0));
-        TRY(row_map(ctx, ctx->dcssc_row, ctx->dcssc_list, ctx->n_extra, ctx->n_dcs, false));
     }
     ctx->listed = true;
     return CC_OK;

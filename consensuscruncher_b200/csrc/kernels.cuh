@@ -360,14 +360,6 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
     if (threadIdx.x < 16 && s_st[threadIdx.x]) atomicAdd(&stats[threadIdx.x], (unsigned long long)s_st[threadIdx.x]);
 }
 
-// row[list[r]] = first_row + r for the families that own a row; everything else stays -1
-__global__ void __launch_bounds__(256)
-rows_from_list_kernel(const uint32_t *__restrict__ list, uint32_t n_rows, int32_t *__restrict__ row, uint32_t first_row)
-{
-    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r < n_rows) row[list[r]] = (int32_t)(first_row + r);
-}
-
 // ---- K4 + K5: SSCS vote and family mode fields ------------------------------------------------
 // consensus_maker (SSCS_maker.py:103-155): per position, among bases with Q >= 30, the
 // first maximum of A,C,G,T wins; quality = min(60, sum of the winner's qualities); the

@@ -40,10 +40,13 @@ __device__ __forceinline__ void st_status(unsigned long long *p, unsigned long l
 enum { SCAN_MODE_EXCL = 0, SCAN_MODE_COMPACT = 1, SCAN_MODE_POPC = 2 };   // POPC: exclusive scan of popcounts
 
 // In: u32 values (MODE_EXCL), u8 flags (MODE_COMPACT) or u32 bitmap words (MODE_POPC).
+// MODE_COMPACT can also write the inverse map: row_out[i] = *row_base + rank of i if flagged, else
+// row_alt[i] (or -1 without row_alt) - the "which output row is family i" arrays, for free.
 template <int MODE, typename InT>
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
-            uint64_t n, unsigned long long *status, uint32_t *ticket, uint32_t *total)
+            uint64_t n, unsigned long long *status, uint32_t *ticket, uint32_t *total,
+            int32_t *row_out = nullptr, const int32_t *row_alt = nullptr, const uint32_t *row_base = nullptr)
 {
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_warp[SCAN_THREADS / 32];
@@ -107,6 +110,7 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
     }
     __syncthreads();
     uint32_t run = s_prefix + warp_off + (incl - sum);
+    const uint32_t first_row = (MODE == SCAN_MODE_COMPACT && row_out != nullptr && row_base != nullptr) ? *row_base : 0u;
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
         if (base + i < n) {
@@ -116,7 +120,27 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
                 out[run] = (uint32_t)(base + i);
             }
         }
-        run += w[i];
+        if (MODE == SCAN_MODE_COMPACT) w[i] = w[i] ? first_row + run + 1u : 0u;     // row + 1, 0 = none (for row_out below)
+        run += (MODE == SCAN_MODE_COMPACT) ? (w[i] != 0u) : w[i];
+    }
+    if (MODE == SCAN_MODE_COMPACT && row_out != nullptr) {
+        // a thread owns 32 consecutive entries = one 128-byte line: written as eight 16-byte stores
+        static_assert(SCAN_ITEMS % 4 == 0, "row_out is written four entries at a time");
+        if (base + SCAN_ITEMS <= n) {
+#pragma unroll
+            for (int i = 0; i < SCAN_ITEMS; i += 4) {
+                int4 a = row_alt != nullptr ? *reinterpret_cast<const int4 *>(row_alt + base + i) : make_int4(-1, -1, -1, -1);
+                int4 v;
+                v.x = w[i] ? (int32_t)(w[i] - 1u) : a.x;
+                v.y = w[i + 1] ? (int32_t)(w[i + 1] - 1u) : a.y;
+                v.z = w[i + 2] ? (int32_t)(w[i + 2] - 1u) : a.z;
+                v.w = w[i + 3] ? (int32_t)(w[i + 3] - 1u) : a.w;
+                *reinterpret_cast<int4 *>(row_out + base + i) = v;
+            }
+        } else {
+            for (int i = 0; i < SCAN_ITEMS && base + i < n; i++)
+                row_out[base + i] = w[i] ? (int32_t)(w[i] - 1u) : (row_alt != nullptr ? row_alt[base + i] : -1);
+        }
     }
 }
 
