@@ -302,7 +302,8 @@ int do_group_hash(cc_ctx *ctx)
     TRY(phase_end(ctx, CC_PH_HASH));
 
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
-    LAUNCH(group_mark_kernel, blocks_for(n, 256), 256, table, read_slot, n, ptr<uint32_t>(ctx->bitmap));
+    LAUNCH(group_mark_kernel, blocks_for(n, 256), 256, table, read_slot, n, ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->val_b));
     TRY(scan_popcounts(ctx, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), words, ctr + CT_NFAM));
     TRY(read_counters(ctx));
     const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
@@ -322,8 +323,8 @@ int do_group_hash(cc_ctx *ctx)
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family
     ctx->sorted_keys = ctx->spare_keys = nullptr;
-    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, table, read_slot, ticket, n, ptr<uint32_t>(ctx->fam_start),
-           ctx->perm, ctx->spare_vals);
+    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->bitmap), ticket, n,
+           ptr<uint32_t>(ctx->fam_start), ctx->perm, ctx->spare_vals);
     ctx->read_fam_ready = true;
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);

@@ -8,7 +8,8 @@
 // the counter are cache hits; what reaches DRAM is about one probe per family, not per read.
 //
 //   insert   every read finds / claims its slot, keeps the slot's read index minimal, takes a ticket
-//   mark     a read that is still its slot's index is the family's first read: one bit per read
+//   mark     a read that is still its slot's index is the family's first read: one bit per read; every
+//            read notes its first read
 //   (popcount scan of the bitmap: family number = rank of the first read = creation order)
 //   family   first reads write the family records and their own read -> family entry
 //   (exclusive scan of the sizes: segment starts)
@@ -73,11 +74,12 @@ group_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__r
 
 __global__ void __launch_bounds__(256)
 group_mark_kernel(const GroupSlot *__restrict__ table, const uint32_t *__restrict__ read_slot, uint64_t n,
-                  uint32_t *__restrict__ bitmap)
+                  uint32_t *__restrict__ bitmap, uint32_t *__restrict__ first_of)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool first = i < n && table[read_slot[i]].rep == (uint32_t)i;
-    const uint32_t word = __ballot_sync(0xffffffffu, first);    // 32 consecutive reads = one bitmap word
+    uint32_t rep = 0xFFFFFFFFu;
+    if (i < n) first_of[i] = rep = table[read_slot[i]].rep;     // kept per read: the later kernels need not probe again
+    const uint32_t word = __ballot_sync(0xffffffffu, i < n && rep == (uint32_t)i);   // 32 consecutive reads = one bitmap word
     if ((threadIdx.x & 31) == 0 && i < n) bitmap[i >> 5] = word;
 }
 
@@ -101,7 +103,7 @@ group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restric
         const uint32_t c = word_rank[i >> 5] + __popc(w & (bit - 1u));
         const uint32_t cnt = table[read_slot[i]].cnt;
         const uint32_t size = (~cnt) >> 1;
-        read_fam[i] = c;                                     // the other members copy it from here (group_place_kernel)
+        read_fam[i] = c;                                     // replaces first_of[i] == i; the other members copy it (group_place_kernel)
         tmpl[c] = (uint32_t)i;
         fam_size[c] = size;
         is_sscs[c] = size >= 2 ? ((cnt & 1u) ? 1 : 3) : 0;   // bit 0: has a consensus row, bit 1: mode fields differ
@@ -121,16 +123,19 @@ group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restric
 }
 
 __global__ void __launch_bounds__(256)
-group_place_kernel(const GroupSlot *__restrict__ table, const uint32_t *__restrict__ read_slot,
-                   const uint32_t *__restrict__ ticket, uint64_t n, const uint32_t *__restrict__ fam_start,
-                   uint32_t *__restrict__ perm, uint32_t *read_fam)
+group_place_kernel(const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ ticket, uint64_t n,
+                   const uint32_t *__restrict__ fam_start, uint32_t *__restrict__ perm, uint32_t *read_fam)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t t = table[read_slot[i]].rep;                 // the family's first read
-    const uint32_t c = read_fam[t];                              // written by group_family_kernel; t == i reads its own entry
+    // read_fam[] holds the family number at first reads (group_family_kernel) and still the first read's
+    // index everywhere else (group_mark_kernel); only the latter entries are rewritten here
+    uint32_t c = read_fam[i];
+    if (!((bitmap[i >> 5] >> (i & 31)) & 1u)) {
+        c = read_fam[c];
+        read_fam[i] = c;
+    }
     perm[fam_start[c] + ticket[i]] = (uint32_t)i;
-    if (t != (uint32_t)i) read_fam[i] = c;
 }
 
 }  // namespace ccgpu
