@@ -313,7 +313,7 @@ int do_group_hash(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->is_sscs, (size_t)nf + 4)); TRY(ensure(ctx, ctx->fam_mapq, nf)); TRY(ensure(ctx, ctx->fam_rg, nf));
     TRY(ensure(ctx, ctx->fam_flag, (size_t)nf * 2)); TRY(ensure(ctx, ctx->fam_tlen, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4));
-    LAUNCH(group_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, table, read_slot, n,
+    LAUNCH(group_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, read_slot, n,
            ptr<uint32_t>(ctx->bitmap),
            ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->val_b), ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),

@@ -73,20 +73,26 @@ group_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__r
 }
 
 __global__ void __launch_bounds__(256)
-group_mark_kernel(const GroupSlot *__restrict__ table, const uint32_t *__restrict__ read_slot, uint64_t n,
+group_mark_kernel(const GroupSlot *__restrict__ table, uint32_t *__restrict__ read_slot, uint64_t n,
                   uint32_t *__restrict__ bitmap, uint32_t *__restrict__ first_of)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t rep = 0xFFFFFFFFu;
-    if (i < n) first_of[i] = rep = table[read_slot[i]].rep;     // kept per read: the later kernels need not probe again
+    if (i < n) {
+        // one 8-byte load of the slot; kept per read so that the later kernels need not probe again:
+        // first_of[i] = the family's first read, read_slot[i] := the slot's final counter
+        const uint2 s = *reinterpret_cast<const uint2 *>(&table[read_slot[i]]);
+        first_of[i] = rep = s.x;
+        read_slot[i] = s.y;
+    }
     const uint32_t word = __ballot_sync(0xffffffffu, i < n && rep == (uint32_t)i);   // 32 consecutive reads = one bitmap word
     if ((threadIdx.x & 31) == 0 && i < n) bitmap[i >> 5] = word;
 }
 
 // family records in creation order (what family_build_kernel writes on the sort path)
 __global__ void __launch_bounds__(256)
-group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restrict__ table,
-                    const uint32_t *__restrict__ read_slot, uint64_t n, const uint32_t *__restrict__ bitmap,
+group_family_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ slot_cnt, uint64_t n,
+                    const uint32_t *__restrict__ bitmap,
                     const uint32_t *__restrict__ word_rank, uint32_t *__restrict__ read_fam, uint32_t *__restrict__ tmpl,
                     uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs, uint8_t *__restrict__ fam_mapq,
                     uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
@@ -101,7 +107,7 @@ group_family_kernel(const uint4 *__restrict__ fields, const GroupSlot *__restric
         const uint32_t w = bitmap[i >> 5], bit = 1u << (i & 31);
         if (!(w & bit)) continue;
         const uint32_t c = word_rank[i >> 5] + __popc(w & (bit - 1u));
-        const uint32_t cnt = table[read_slot[i]].cnt;
+        const uint32_t cnt = slot_cnt[i];                    // left by group_mark_kernel
         const uint32_t size = (~cnt) >> 1;
         read_fam[i] = c;                                     // replaces first_of[i] == i; the other members copy it (group_place_kernel)
         tmpl[c] = (uint32_t)i;
