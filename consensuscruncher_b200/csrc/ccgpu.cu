@@ -288,7 +288,7 @@ int do_group_hash(cc_ctx *ctx)
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
     TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
-    uint32_t *read_slot = ptr<uint32_t>(ctx->key_a), *ticket = ptr<uint32_t>(ctx->key_b);
+    uint32_t *read_slot = ptr<uint32_t>(ctx->key_a), *cursor = ptr<uint32_t>(ctx->key_b);   // cursor: one per family
     uint64_t slots = 1024;
     while (slots < n + n / 4) slots <<= 1;                  // load factor <= 0.8 even if every read is a family
     TRY(ensure(ctx, ctx->gtable, slots * sizeof(GroupSlot)));
@@ -298,7 +298,7 @@ int do_group_hash(cc_ctx *ctx)
 
     TRY(phase_begin(ctx, CC_PH_HASH));
     CK(cudaMemsetAsync(table, 0xFF, slots * sizeof(GroupSlot), ctx->stream));
-    LAUNCH(group_insert_kernel, blocks_for(n, 256), 256, ctx->fields, n, table, slots - 1, read_slot, ticket);
+    LAUNCH(group_insert_kernel, blocks_for(n, 256), 256, ctx->fields, n, table, slots - 1, read_slot);
     TRY(phase_end(ctx, CC_PH_HASH));
 
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
@@ -323,8 +323,8 @@ int do_group_hash(cc_ctx *ctx)
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family
     ctx->sorted_keys = ctx->spare_keys = nullptr;
-    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->bitmap), ticket, n,
-           ptr<uint32_t>(ctx->fam_start), ctx->perm, ctx->spare_vals);
+    CK(cudaMemcpyAsync(cursor, ctx->fam_start.p, (size_t)nf * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->bitmap), n, cursor, ctx->perm, ctx->spare_vals);
     ctx->read_fam_ready = true;
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);

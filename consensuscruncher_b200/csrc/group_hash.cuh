@@ -7,15 +7,16 @@
 // other in a coordinate-sorted input, so after the first member the slot, the template's record and
 // the counter are cache hits; what reaches DRAM is about one probe per family, not per read.
 //
-//   insert   every read finds / claims its slot, keeps the slot's read index minimal, takes a ticket
+//   insert   every read finds / claims its slot, keeps the slot's read index minimal, counts itself
 //   mark     a read that is still its slot's index is the family's first read: one bit per read; every
 //            read notes its first read
 //   (popcount scan of the bitmap: family number = rank of the first read = creation order)
 //   family   first reads write the family records and their own read -> family entry
 //   (exclusive scan of the sizes: segment starts)
-//   place    every read copies its first read's family number and goes to segment start + ticket
+//   place    every read copies its first read's family number and takes the next free place of the
+//            family's segment (atomic cursor per family)
 //
-// Tickets come from an atomic counter, so the order of a family's members in `perm` is arbitrary;
+// Places come from an atomic cursor, so the order of a family's members in `perm` is arbitrary;
 // everything downstream is independent of it (votes count, lone supporters are unique, mode ties
 // are decided by read index - see group_mode / warp_mode).
 #pragma once
@@ -29,9 +30,8 @@ namespace ccgpu {
 struct GroupSlot {
     uint32_t rep;       // smallest member index so far (0xFFFFFFFF = empty); in the end the family's first read
     uint32_t cnt;       // starts at 0xFFFFFFFF (the table is cleared to 0xFF bytes); every member subtracts 2,
-                        // so a ticket is (~old) >> 1 and the size (~cnt) >> 1; bit 0 is cleared once two
-                        // members are seen to differ in tlen / flag / mapq / RG (the family needs real
-                        // modes) - clearing it never borrows, so tickets are the same either way
+                        // so the size is (~cnt) >> 1; bit 0 is cleared once two members are seen to differ
+                        // in tlen / flag / mapq / RG (the family needs real modes) - that never borrows
 };
 
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p)
@@ -46,7 +46,7 @@ __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p)
 // 52 resident warps per SM already saturate.)
 __global__ void __launch_bounds__(256)
 group_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__restrict__ table, uint64_t mask,
-                    uint32_t *__restrict__ read_slot, uint32_t *__restrict__ ticket)
+                    uint32_t *__restrict__ read_slot)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -69,7 +69,7 @@ group_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__r
         slot = (slot + 1) & mask;
     }
     read_slot[i] = (uint32_t)slot;
-    ticket[i] = (~atomicSub(&table[slot].cnt, 2u)) >> 1;
+    atomicSub(&table[slot].cnt, 2u);                             // result unused: a reduction, nothing to wait for
 }
 
 __global__ void __launch_bounds__(256)
@@ -129,8 +129,8 @@ group_family_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
 }
 
 __global__ void __launch_bounds__(256)
-group_place_kernel(const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ ticket, uint64_t n,
-                   const uint32_t *__restrict__ fam_start, uint32_t *__restrict__ perm, uint32_t *read_fam)
+group_place_kernel(const uint32_t *__restrict__ bitmap, uint64_t n, uint32_t *__restrict__ cursor,
+                   uint32_t *__restrict__ perm, uint32_t *read_fam)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -141,7 +141,7 @@ group_place_kernel(const uint32_t *__restrict__ bitmap, const uint32_t *__restri
         c = read_fam[c];
         read_fam[i] = c;
     }
-    perm[fam_start[c] + ticket[i]] = (uint32_t)i;
+    perm[atomicAdd(&cursor[c], 1u)] = (uint32_t)i;             // cursor[] starts as a copy of fam_start[] (a few MB: L2)
 }
 
 }  // namespace ccgpu
