@@ -71,6 +71,7 @@ struct cc_ctx {
     DevBuf cs_in, cs_k0, cs_k1, cs_v0, cs_v1;   // cc_sort_coordinates
     DevBuf gtable;                              // hash grouping (group_hash.cuh)
     bool group_by_hash = true;
+    uint64_t gtable_mask = 0;                   // non-zero while gtable describes the loaded batch
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
     uint32_t host_ctr[CT_COUNT];
@@ -326,6 +327,7 @@ int do_group_hash(cc_ctx *ctx)
     CK(cudaMemcpyAsync(cursor, ctx->fam_start.p, (size_t)nf * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->bitmap), n, cursor, ctx->perm, ctx->spare_vals);
     ctx->read_fam_ready = true;
+    ctx->gtable_mask = slots - 1;
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);
     TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
@@ -342,6 +344,7 @@ int do_group(cc_ctx *ctx)
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = ctx->read_fam_ready = false;
     ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = ctx->n_extra = 0;
     ctx->next_ticket = 0;
+    ctx->gtable_mask = 0;
     TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
     TRY(ensure(ctx, ctx->stats, 16 * sizeof(unsigned long long)));
     TRY(ensure(ctx, ctx->hist, CC_HIST_BINS * sizeof(unsigned long long)));
@@ -414,6 +417,8 @@ int do_group(cc_ctx *ctx)
 }
 
 // ---- stage 2: join + classification (index work only) -----------------------------------------
+int do_classify(cc_ctx *ctx);
+
 int do_join_index(cc_ctx *ctx)
 {
     const uint32_t nf = ctx->n_fam;
@@ -424,18 +429,32 @@ int do_join_index(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->dcssc_list, (size_t)nf * 4));
     if (nf == 0) return CC_OK;
     TRY(phase_begin(ctx, CC_PH_JOIN));
+    CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
+    if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
+    LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(ctx->partner), (uint64_t)nf, -1);
+    if (ctx->gtable_mask) {
+        // the grouping table already maps every family tuple to its first read
+        LAUNCH(group_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,
+               ptr<GroupSlot>(ctx->gtable), ctx->gtable_mask, ctx->spare_vals, ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
+        TRY(phase_end(ctx, CC_PH_JOIN));
+        return do_classify(ctx);
+    }
     uint64_t slots = 64;
     while (slots < 2ull * nf) slots <<= 1;
     TRY(ensure(ctx, ctx->table, slots * 8));
     CK(cudaMemsetAsync(ctx->table.p, 0, slots * 8, ctx->stream));
-    CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
-    if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
-    LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(ctx->partner), (uint64_t)nf, -1);
     LAUNCH(join_build_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf,
            ptr<unsigned long long>(ctx->table), slots - 1, ctr + CT_ASYM);
     LAUNCH(join_probe_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc,
            ctx->n_bc, ptr<unsigned long long>(ctx->table), slots - 1, ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
     TRY(phase_end(ctx, CC_PH_JOIN));
+    return do_classify(ctx);
+}
+
+int do_classify(cc_ctx *ctx)
+{
+    const uint32_t nf = ctx->n_fam;
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     TRY(phase_begin(ctx, CC_PH_CLASSIFY));
     LAUNCH(classify_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
            (int)ctx->params.scorrect, ptr<uint8_t>(ctx->f_dcs), ptr<uint8_t>(ctx->f_corr),

@@ -144,4 +144,35 @@ group_place_kernel(const uint32_t *__restrict__ bitmap, uint64_t n, uint32_t *__
     perm[atomicAdd(&cursor[c], 1u)] = (uint32_t)i;             // cursor[] starts as a copy of fam_start[] (a few MB: L2)
 }
 
+// The duplex join on the grouping table: a family's partner is the family of the complementary tuple
+// (duplex_tag, consensus_helper.py:605-648), and that tuple - like every family's - has a slot here that
+// names its first read.  No second table is built.  Symmetric / asymmetric as join_probe_kernel.
+__global__ void __launch_bounds__(256)
+group_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, uint32_t n_fam,
+                  const uint32_t *__restrict__ dup_bc, uint32_t n_bc, const GroupSlot *__restrict__ table, uint64_t mask,
+                  const uint32_t *__restrict__ read_fam, int32_t *__restrict__ partner, const uint32_t *__restrict__ asym)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_fam) return;
+    Rec r = load_rec(fields, tmpl[c]);
+    const bool symmetric = !*asym;
+    if (symmetric && !(r.b.w & 0x40u)) return;      // an R2 family hears from its R1 partner (partner[] starts at -1)
+    int32_t found = -1;
+    uint32_t d = r.a.x < n_bc ? __ldg(&dup_bc[r.a.x]) : NO_ID;
+    if (d != NO_ID) {
+        Rec q = r;
+        q.a.x = d;                 // barcode halves swapped
+        q.b.w ^= 0x40u;            // R1 <-> R2 (only the key bits of meta are compared)
+        uint64_t slot = (rec_hash(q) * 0xD6E8FEB86659FD93ull >> 20) & mask;
+        for (;;) {
+            const uint32_t rep = table[slot].rep;
+            if (rep == 0xFFFFFFFFu) break;
+            if (same_tag(load_rec(fields, rep), q)) { found = (int32_t)read_fam[rep]; break; }
+            slot = (slot + 1) & mask;
+        }
+    }
+    partner[c] = found;
+    if (symmetric && found >= 0) partner[found] = (int32_t)c;
+}
+
 }  // namespace ccgpu
