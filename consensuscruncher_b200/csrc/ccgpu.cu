@@ -313,13 +313,13 @@ int do_group_hash(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->fam_start, (size_t)nf * 4)); TRY(ensure(ctx, ctx->fam_size, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->is_sscs, (size_t)nf + 4)); TRY(ensure(ctx, ctx->fam_mapq, nf)); TRY(ensure(ctx, ctx->fam_rg, nf));
     TRY(ensure(ctx, ctx->fam_flag, (size_t)nf * 2)); TRY(ensure(ctx, ctx->fam_tlen, (size_t)nf * 4));
-    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->partner, (size_t)nf * 4));
     LAUNCH(group_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, read_slot, n,
            ptr<uint32_t>(ctx->bitmap),
            ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->val_b), ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
            ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
-           (uint32_t)CC_HIST_BINS, ctr + CT_NMID);
+           (uint32_t)CC_HIST_BINS, ctr + CT_NMID, ptr<int32_t>(ctx->partner));
     TRY(scan_exclusive(ctx, ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), nf));
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family
@@ -387,7 +387,7 @@ int do_group(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->fam_start, (size_t)nf * 4)); TRY(ensure(ctx, ctx->fam_size, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->is_sscs, nf)); TRY(ensure(ctx, ctx->fam_mapq, nf)); TRY(ensure(ctx, ctx->fam_rg, nf));
     TRY(ensure(ctx, ctx->fam_flag, (size_t)nf * 2)); TRY(ensure(ctx, ctx->fam_tlen, (size_t)nf * 4));
-    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4));
+    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->partner, (size_t)nf * 4));
 
     // creation order: bitmap of first members + rank queries (see family_build_kernel)
     const uint64_t words = (n + 31) / 32;
@@ -405,7 +405,7 @@ int do_group(cc_ctx *ctx)
            ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
            ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
-           (uint32_t)CC_HIST_BINS, ctr + CT_NMID);
+           (uint32_t)CC_HIST_BINS, ctr + CT_NMID, ptr<int32_t>(ctx->partner));
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);
     TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
@@ -431,7 +431,6 @@ int do_join_index(cc_ctx *ctx)
     TRY(phase_begin(ctx, CC_PH_JOIN));
     CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
     if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
-    LAUNCH(fill_i32_kernel, blocks_for(nf, 256), 256, ptr<int32_t>(ctx->partner), (uint64_t)nf, -1);
     if (ctx->gtable_mask) {
         // the grouping table already maps every family tuple to its first read
         LAUNCH(group_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,

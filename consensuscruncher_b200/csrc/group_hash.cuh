@@ -96,7 +96,8 @@ group_family_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
                     const uint32_t *__restrict__ word_rank, uint32_t *__restrict__ read_fam, uint32_t *__restrict__ tmpl,
                     uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs, uint8_t *__restrict__ fam_mapq,
                     uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid)
+                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid,
+                    int32_t *__restrict__ partner)
 {
     __shared__ uint32_t small_hist[256];           // sizes < 256 are counted per block first
     small_hist[threadIdx.x] = 0;
@@ -118,6 +119,7 @@ group_family_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
         fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
         fam_mapq[c] = (uint8_t)((b.w >> 16) & 0xFF);
         fam_rg[c] = (uint8_t)(b.w >> 24);
+        partner[c] = -1;                                     // until the join says otherwise
         const uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
         if (bin < 256) atomicAdd(&small_hist[bin], 1u);
         else atomicAdd(&hist[bin], 1ull);

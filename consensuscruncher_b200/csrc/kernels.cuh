@@ -190,7 +190,8 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
                     uint32_t *__restrict__ fam_size, uint8_t *__restrict__ is_sscs,
                     uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag,
                     int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid)
+                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid,
+                    int32_t *__restrict__ partner)
 {
     __shared__ uint32_t small_hist[256];           // sizes < 256 are counted per block first
     small_hist[threadIdx.x] = 0;
@@ -215,6 +216,7 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
         fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
         fam_mapq[c] = (uint8_t)((b.w >> 16) & 0xFF);
         fam_rg[c] = (uint8_t)(b.w >> 24);
+        partner[c] = -1;                              // until the join says otherwise
         uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
         if (bin < 256) atomicAdd(&small_hist[bin], 1u);
         else atomicAdd(&hist[bin], 1ull);
@@ -565,12 +567,6 @@ struct RowSources {
     const int32_t *corr_row;
     uint32_t stride;
 };
-
-__global__ void fill_i32_kernel(int32_t *p, uint64_t n, int32_t v)
-{
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) p[i] = v;
-}
 
 // ---- compact input rows (cc_load_reads_q4): lpad/2 base bytes + lpad/2 bytes of 4-bit quality
 // codes -> the standard row (lpad/2 base bytes + lpad quality bytes, zero tail).  One thread

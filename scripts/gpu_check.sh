@@ -4,7 +4,7 @@
 TAG=${1:-r1}
 OUT=gpurun_out
 mkdir -p $OUT
-KREGEX='regex:^(group_|dup_|expand_|coord_|hash|os_|scan|boundary|fix_mixed_runs|mark_first|creation_rank|family_build|domain_check|join_build|join_probe|classify|fill_i32|vote|rescue|duplex|agree|read_fam)'
+KREGEX='regex:^(group_|dup_|expand_|coord_|hash|os_|scan|boundary|fix_mixed_runs|mark_first|creation_rank|family_build|domain_check|join_build|join_probe|classify|vote|rescue|duplex|agree|read_fam)'
 python -m pytest tests -m gpu -x -q 2>&1 | tail -5 | tee $OUT/pytest_$TAG.log
 python bench.py 2> $OUT/bench_$TAG.err | tee $OUT/bench_$TAG.json
 python bench.py --impl reference --steps 2 --warmup 1 2> $OUT/bench_ref_$TAG.err | tee $OUT/bench_ref_$TAG.json
