@@ -329,3 +329,12 @@ def test_sort_grouping_path_gives_the_same_result(monkeypatch):
     with GpuConsensus(0, cutoff=0.7, scorrect=True) as by_sort:
         for packed in cases:
             helpers.assert_same_result(by_sort.consensus(packed), oracle.run(packed, 0.7, True))
+
+
+def test_one_huge_family_and_all_singletons(engine):
+    # the two extremes of the family table: every read of a strand hammers one slot / every read founds its own
+    huge = synth.generate(seed=95, n_molecules=2, L=64, dist="const", fam_mean=20000, p_duplex=1.0)
+    _both(engine, huge.to_packed())
+    lone = synth.generate(seed=96, n_molecules=40000, L=32, dist="const", fam_mean=1, p_duplex=0.3, umi_len=4)
+    got = _both(engine, lone.to_packed())
+    assert got.n_fam == got.fam_size.sum()
