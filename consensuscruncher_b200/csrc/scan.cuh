@@ -60,9 +60,21 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
     InT v[SCAN_ITEMS];
     uint32_t w[SCAN_ITEMS];
     uint32_t sum = 0;
+    // a thread's 32 consecutive items are one 32-byte (flags) or 128-byte (words) piece: 16-byte loads
+    constexpr int PER_VEC = 16 / (int)sizeof(InT);
+    static_assert(SCAN_ITEMS % PER_VEC == 0, "items per thread must fill whole 16-byte loads");
+    if (base + SCAN_ITEMS <= n) {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS / PER_VEC; k++) {
+            const uint4 q = *reinterpret_cast<const uint4 *>(in + base + k * PER_VEC);
+            memcpy(&v[k * PER_VEC], &q, 16);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < n) ? in[base + i] : (InT)0;
+    }
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
-        v[i] = (base + i < n) ? in[base + i] : (InT)0;
         w[i] = (MODE == SCAN_MODE_EXCL) ? (uint32_t)v[i] : (MODE == SCAN_MODE_COMPACT ? ((uint32_t)v[i] & 1u) : (uint32_t)__popc((uint32_t)v[i]));
         sum += w[i];
     }
@@ -115,13 +127,20 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
     for (int i = 0; i < SCAN_ITEMS; i++) {
         if (base + i < n) {
             if (MODE != SCAN_MODE_COMPACT) {
-                out[base + i] = run;
+                if (base + SCAN_ITEMS > n) out[base + i] = run;       // whole pieces are stored below, 16 bytes at a time
             } else if (w[i]) {
                 out[run] = (uint32_t)(base + i);
             }
         }
+        const uint32_t step = w[i];
         if (MODE == SCAN_MODE_COMPACT) w[i] = w[i] ? first_row + run + 1u : 0u;     // row + 1, 0 = none (for row_out below)
-        run += (MODE == SCAN_MODE_COMPACT) ? (w[i] != 0u) : w[i];
+        else w[i] = run;                                                            // the exclusive prefix itself
+        run += step;
+    }
+    if (MODE != SCAN_MODE_COMPACT && base + SCAN_ITEMS <= n) {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i += 4)
+            *reinterpret_cast<uint4 *>(out + base + i) = make_uint4(w[i], w[i + 1], w[i + 2], w[i + 3]);
     }
     if (MODE == SCAN_MODE_COMPACT && row_out != nullptr) {
         // a thread owns 32 consecutive entries = one 128-byte line: written as eight 16-byte stores
