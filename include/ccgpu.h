@@ -139,8 +139,9 @@ int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, 
 int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
                          uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
 
-/* Family grouping: key hash, stable radix sort, exact family boundaries, families in
- * creation order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
+/* Family grouping: an open-addressing table keyed by the exact family tuple (or, with
+ * CCGPU_GROUP=sort in the environment at cc_create, key hash + stable radix sort + exact
+ * boundaries); families in creation order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
  * construction (consensus_helper.py:438-475) and Counter(tag_dict.values())
  * (SSCS_maker.py:361). */
 int cc_group(cc_ctx *ctx);
@@ -161,7 +162,7 @@ int cc_dcs_join(cc_ctx *ctx);
 int cc_sc_rescue(cc_ctx *ctx);
 
 /* cc_group, cc_sscs_vote, cc_dcs_join and (if params.scorrect) cc_sc_rescue in one call
- * with a single host synchronisation for the row counts. */
+ * with one host synchronisation for the family count, one for the row counts and one at the end. */
 int cc_run(cc_ctx *ctx);
 
 /* Whole path from host buffers to host results: cc_load_reads + cc_run; afterwards
