@@ -338,3 +338,46 @@ def test_one_huge_family_and_all_singletons(engine):
     lone = synth.generate(seed=96, n_molecules=40000, L=32, dist="const", fam_mean=1, p_duplex=0.3, umi_len=4)
     got = _both(engine, lone.to_packed())
     assert got.n_fam == got.fam_size.sum()
+
+
+def _fuzz_case(seed):
+    """A small random batch: random geometry and family structure, then tlen / mapq / RG / flag bit 0x20
+    scrambled per read - none of them is part of the family key, all of them feed the mode fields,
+    so most families get ties that only the first-appearance rule decides."""
+    rng = np.random.default_rng(1000 + seed)
+    L = int(rng.integers(20, 200))
+    kw = dict(seed=seed, n_molecules=int(rng.integers(1, 400)), L=L,
+              dist=str(rng.choice(["ztpoisson", "const", "lognormal", "wgs"])), fam_mean=float(rng.choice([1, 2, 3, 6, 20])),
+              p_duplex=float(rng.choice([0.0, 0.5, 1.0])), umi_len=int(rng.integers(1, 4)), umi_dot=bool(rng.integers(0, 2)),
+              n_tid=int(rng.integers(1, 4)), region=(0, int(rng.choice([600 + 2 * L, 5000, 200000]))),
+              insert_sd=float(rng.choice([2.0, 20.0])), p_n=float(rng.choice([0.0, 0.01])), max_family=300)
+    packed = synth.generate(**kw).to_packed()
+    f = packed.fields
+    n = packed.n
+    if n:
+        f["tlen"] = rng.integers(-3, 4, n).astype(np.int32)
+        f["mapq"] = rng.choice(np.array([0, 20, 60], np.uint8), n)
+        f["rg"] = rng.choice(np.array([0, 1, 2, 0xFF], np.uint8), n, p=[0.4, 0.3, 0.25, 0.05])
+        f["flag"] = f["flag"] ^ (rng.integers(0, 2, n).astype(np.uint16) << 5)
+    packed.rgs = ["rgA", "rgB", "rgC"]
+    return packed, float(rng.choice([0.5, 0.6, 0.7, 0.9, 1.0])), bool(rng.integers(0, 2))
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_fuzz_small_batches(engine, block):
+    for seed in range(block * 15, block * 15 + 15):
+        packed, cutoff, scorrect = _fuzz_case(seed)
+        engine.set_params(cutoff=cutoff, scorrect=scorrect)
+        try:
+            exp, faults = oracle.run(packed, cutoff, scorrect, return_faults=True)
+        except oracle.OracleError:
+            with pytest.raises(GpuError):
+                engine.consensus(packed)
+            continue
+        if faults:
+            with pytest.raises(pack.DomainError):
+                engine.consensus(packed)
+            continue
+        got = engine.consensus(packed)
+        bad = got.diff(exp)
+        assert not bad, "seed %d: %s" % (seed, bad)
