@@ -38,7 +38,8 @@ UNIT = "reads/s"
 PAIRS_PER_GPU = 10_000_000
 L = 128
 CUTOFF = 0.7
-CPU_SAMPLE_PAIRS = 2_000_000
+CPU_SAMPLE_PAIRS = 8_000_000       # cpu_baseline leg: head of the GPU batch, ~10 s of one host thread
+REF_SAMPLE_PAIRS = 2_000_000       # --impl reference: generated on the host, split over all host threads
 
 
 def parse():
@@ -167,7 +168,7 @@ def reference_arm(args):
     from oracle import oracle
     oracle.build()
     cores = os.cpu_count() or 1
-    per = max(1000, args.cpu_pairs // cores)
+    per = max(1000, min(args.cpu_pairs, REF_SAMPLE_PAIRS) // cores)
     shards = [cpu_sample(per, 9000 + i) for i in range(cores)]
     reads = sum(p.n for p in shards)
     for _ in range(max(1, min(args.warmup, 1))):
@@ -461,12 +462,17 @@ def main():
     if not args.no_cpu_baseline:
         from oracle import oracle
         oracle.build()
-        sample = cpu_sample(args.cpu_pairs, 777)
+        # the sample is the head of the batch the GPU just processed (whole pairs, so every kept pair still
+        # founds / joins its two families together), downloaded - not generated again on the host
+        from consensuscruncher_b200.synth_device import DeviceBatch
+        n_cpu = min(batch.n, 2 * args.cpu_pairs)
+        sample = DeviceBatch(batch.fields[:n_cpu], batch.payload[:n_cpu], batch.dup_bc, batch.lpad, batch.stride,
+                             batch.L, batch.umi_len).to_packed()
         t0 = time.perf_counter()
         oracle.run(sample, CUTOFF, True)
         dt = time.perf_counter() - t0
         cpu = {"value": sample.n / dt, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": "%d reads (%d pairs) of the same distribution, oracle/cc_oracle.c single thread, %.1f s"
+               "sample": "the first %d reads (%d pairs) of the GPU's batch, oracle/cc_oracle.c single thread, %.1f s"
                          % (sample.n, sample.n // 2, dt),
                "host_cores_available": os.cpu_count()}
 
