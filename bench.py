@@ -168,8 +168,25 @@ def reference_arm(args):
     from oracle import oracle
     oracle.build()
     cores = os.cpu_count() or 1
-    per = max(1000, min(args.cpu_pairs, REF_SAMPLE_PAIRS) // cores)
-    shards = [cpu_sample(per, 9000 + i) for i in range(cores)]
+    shards = None
+    try:
+        # the sample is a batch of the bench's own generator (made on the GPU when there is one: that is
+        # input preparation, not the timed path), cut into one range of whole pairs per host thread
+        import torch
+        if torch.cuda.is_available():
+            from consensuscruncher_b200.pack import PackedReads
+            from consensuscruncher_b200.synth_device import generate_device
+            whole = generate_device(seed=1234, n_pairs=min(args.pairs, args.cpu_pairs), L=L, device="cuda:0").to_packed()
+            per = whole.n // 2 // cores
+            shards = [PackedReads(whole.fields[2 * per * i:2 * per * (i + 1)], whole.payload[2 * per * i:2 * per * (i + 1)],
+                                  whole.lpad, whole.barcodes, whole.dup_bc, whole.cigar_pairs, whole.rgs)
+                      for i in range(cores)]
+            torch.cuda.empty_cache()
+    except Exception:
+        shards = None
+    if shards is None:
+        per = max(1000, min(args.cpu_pairs, REF_SAMPLE_PAIRS) // cores)
+        shards = [cpu_sample(per, 9000 + i) for i in range(cores)]
     reads = sum(p.n for p in shards)
     for _ in range(max(1, min(args.warmup, 1))):
         run_oracle_threads(shards[:cores], cores)
