@@ -584,7 +584,7 @@ int do_vote(cc_ctx *ctx)
     TRY(phase_end(ctx, CC_PH_VOTE));
     if (rows) {
         TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
-        LAUNCH(vote_big_kernel, 296, 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
+        LAUNCH(vote_big_kernel, 148 * 8, 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
                ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list),
                ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG, ctx->params.cutoff, ptr<uint8_t>(ctx->sscs_rows),
                ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),

@@ -432,17 +432,23 @@ __device__ uint32_t warp_mode(Get get, Idx idx, uint32_t n, bool is_flag, int la
     return best;
 }
 
-// One warp votes one family of any size: members perm[start .. start+n), consensus row -> out,
-// mode fields -> fam_*[c].  Used for families too large for vote_small_kernel (vote.cuh) and by
-// the single-family entry points.
+// WARPS warps vote one family of any size: members perm[start .. start+n), consensus row -> out,
+// mode fields -> fam_*[c].  Used for families too large for vote_small_kernel (vote.cuh; WARPS = 8:
+// the warps of a CTA share the members - counts add, the per-base quality ORs combine - and warp 0
+// finishes) and by the single-family entry points (WARPS = 1).  `scratch`: WARPS * 32 * 21 words of
+// shared memory when WARPS > 1; every thread of the CTA must make the call.
+constexpr int VOTE_PART_WORDS = 21;      // 16 wide counts + 4 quality ORs + error bits per lane
+
+template <int WARPS>
 __device__ __forceinline__ void
 vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride,
                  uint32_t lpad, const uint32_t *__restrict__ perm, uint32_t start, uint32_t n, double cutoff,
                  uint8_t *__restrict__ out, uint32_t c, uint8_t *__restrict__ fam_mapq,
                  uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-                 uint32_t *__restrict__ err_flag)
+                 uint32_t *__restrict__ err_flag, uint32_t *scratch = nullptr)
 {
     const int lane = threadIdx.x & 31;
+    const int warp = WARPS > 1 ? (int)(threadIdx.x >> 5) : 0;
     const uint32_t half = lpad >> 1;
     uint32_t err = 0;
 
@@ -458,7 +464,7 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
 #pragma unroll
         for (int bi = 0; bi < 4; bi++) { acc.cnt[bi] = 0; acc.qor[bi] = 0; }
         uint32_t since_flush = 0;
-        for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+        for (uint32_t j0 = 32 * warp; j0 < n; j0 += 32 * WARPS) {
             // lanes fetch 32 member indices at once, then the warp walks the rows together
             uint32_t mine = (j0 + lane < n) ? perm[start + j0 + lane] : 0;
             uint32_t lim = min(32u, n - j0);
@@ -481,14 +487,46 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
                 }
             }
         }
-        if (active) {
+#pragma unroll
+        for (int bi = 0; bi < 4; bi++) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) wide[bi][k] += (acc.cnt[bi] >> (8 * k)) & 0xFF;
+        }
+        if (WARPS > 1) {
+            // the warps' partial tallies meet in shared memory; warp 0 adds them up and finishes
+            uint32_t *mine = scratch + ((size_t)warp * 32 + lane) * VOTE_PART_WORDS;
+            __syncthreads();                                   // scratch is free (previous chunk / family done)
+            if (warp != 0) {
+#pragma unroll
+                for (int bi = 0; bi < 4; bi++) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) mine[4 * bi + k] = wide[bi][k];
+                    mine[16 + bi] = acc.qor[bi];
+                }
+                mine[20] = err;
+            }
+            __syncthreads();
+            if (warp == 0) {
+                for (int w2 = 1; w2 < WARPS; w2++) {
+                    const uint32_t *o = scratch + ((size_t)w2 * 32 + lane) * VOTE_PART_WORDS;
+#pragma unroll
+                    for (int bi = 0; bi < 4; bi++) {
+#pragma unroll
+                        for (int k = 0; k < 4; k++) wide[bi][k] += o[4 * bi + k];
+                        acc.qor[bi] |= o[16 + bi];
+                    }
+                    err |= o[20];
+                }
+            }
+        }
+        if (active && warp == 0) {
             uint32_t seq_out = 0, q_out = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                uint32_t cA = wide[0][k] + ((acc.cnt[0] >> (8 * k)) & 0xFF);
-                uint32_t cC = wide[1][k] + ((acc.cnt[1] >> (8 * k)) & 0xFF);
-                uint32_t cG = wide[2][k] + ((acc.cnt[2] >> (8 * k)) & 0xFF);
-                uint32_t cT = wide[3][k] + ((acc.cnt[3] >> (8 * k)) & 0xFF);
+                uint32_t cA = wide[0][k];
+                uint32_t cC = wide[1][k];
+                uint32_t cG = wide[2][k];
+                uint32_t cT = wide[3][k];
                 uint32_t best = cA; int w = 0;                  // first maximum in A,C,G,T order
                 if (cC > best) { best = cC; w = 1; }
                 if (cG > best) { best = cG; w = 2; }
@@ -506,6 +544,7 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
             *reinterpret_cast<uint32_t *>(out + half + p0) = q_out;
         }
     }
+    if (warp != 0) return;                                     // (after the last barrier)
     for (uint32_t x = half + lpad + lane * 4; x < stride; x += 128) *reinterpret_cast<uint32_t *>(out + x) = 0;
     if (err) atomicOr(err_flag, 1u);
 
@@ -544,7 +583,7 @@ vote_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payloa
     const uint32_t row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (row >= n_rows) return;
     const uint32_t c = sscs_list[row];
-    vote_family_warp(fields, payload, stride, lpad, perm, fam_start[c], fam_size[c], cutoff,
+    vote_family_warp<1>(fields, payload, stride, lpad, perm, fam_start[c], fam_size[c], cutoff,
                      out_rows + (uint64_t)row * stride, c, fam_mapq, fam_flag, fam_tlen, fam_rg, err_flag);
 }
 

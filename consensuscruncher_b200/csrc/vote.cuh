@@ -616,7 +616,8 @@ vote_segments_kernel(const uint32_t *__restrict__ sscs_list, const uint32_t *__r
     else if (n > 15) mid_list[atomicAdd(n_mid, 1u)] = r;             // 16..127 reads: the launch with counter flushes
 }
 
-// one warp per large family, looping over however many the device-side counter says
+// one CTA per large family (its 8 warps share the members), looping over however many the
+// device-side counter says
 __global__ void __launch_bounds__(256)
 vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ payload, uint32_t stride, uint32_t lpad,
                 const uint32_t *__restrict__ perm, const uint32_t *__restrict__ vstart,
@@ -625,13 +626,13 @@ vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ pa
                 uint8_t *__restrict__ out_rows, uint8_t *__restrict__ fam_mapq, uint16_t *__restrict__ fam_flag,
                 int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg, uint32_t *__restrict__ err_flag)
 {
-    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    __shared__ uint32_t scratch[8 * 32 * VOTE_PART_WORDS];
     const uint32_t total = *n_big;
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
+    for (uint32_t i = blockIdx.x; i < total; i += gridDim.x) {
         const uint32_t row = big_list[i];
-        vote_family_warp(fields, payload, stride, lpad, perm, vstart[row], vsize[row] & VSIZE_COUNT, cutoff,
-                         out_rows + (uint64_t)row * stride, sscs_list[row], fam_mapq, fam_flag, fam_tlen, fam_rg,
-                         err_flag);
+        vote_family_warp<8>(fields, payload, stride, lpad, perm, vstart[row], vsize[row] & VSIZE_COUNT, cutoff,
+                            out_rows + (uint64_t)row * stride, sscs_list[row], fam_mapq, fam_flag, fam_tlen, fam_rg,
+                            err_flag, scratch);
     }
 }
 
