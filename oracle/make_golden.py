@@ -44,15 +44,77 @@ CASES = {
     "big_families": (dict(seed=18, n_molecules=6, L=32, fam_mean=45.0, p_duplex=1.0, region=(0, 1500),
                           err=0.03),
                      dict(cutoff=0.7, scorrect=True)),
+    "c1prime_real_fastq": (None, dict(cutoff=0.7, scorrect=True)),
     "no_rg_aux": (dict(seed=19, n_molecules=40, L=40, fam_mean=2.0, p_duplex=0.7, region=(0, 2500),
                        rg_name=None),
                   dict(cutoff=0.7, scorrect=True, aux=True)),
 }
 
 
+def c1prime_reads(seed=56, pairs=1500, molecules=140, fam_mean=2.5, p_duplex=0.75, err=0.01):
+    """Config 1 of BASELINE.json cannot be produced here (no bwa / hg19 / picard), so this is its
+    stand-in (SURVEY.md 8d "c1'"): the reference's own test FASTQ pairs, barcodes extracted with pattern
+    NNT (extract.py, pinned against the reference's extract_barcodes.py), real 123-base sequences as
+    molecule templates, real quality strings (the full HiSeq alphabet, Q2 'N' calls included) on every
+    copy, synthetic positions and cigar 123M.  -> (reads in coordinate order, header)"""
+    import numpy as np
+    from consensuscruncher_b200 import extract
+    from consensuscruncher_b200.records import Read
+    rng = np.random.default_rng(seed)
+    d = tempfile.mkdtemp()
+    for r in ("R1", "R2"):
+        with open(os.path.join(run_reference.REF_ROOT, "test", "fastq", "LargeMid_56_L005_%s.fastq" % r)) as fh, \
+                open(os.path.join(d, r + ".fastq"), "w") as out:
+            out.write("".join(fh.readline() for _ in range(4 * pairs)))
+    extract.extract_pattern(os.path.join(d, "R1.fastq"), os.path.join(d, "R2.fastq"), os.path.join(d, "x"), "NNT")
+    mates = [list(extract.read_fastq(os.path.join(d, "x_barcode_%s.fastq" % r))) for r in ("R1", "R2")]
+    L = 123
+    real = [(t1.split("|")[0], t1.split("|")[1].split("/")[0], s1, q1, s2, q2)
+            for (t1, s1, q1), (_, s2, q2) in zip(*mates) if len(s1) == L and len(s2) == L]
+    assert len(real) > 2 * molecules
+    reads, donor = [], molecules                 # records [0, molecules) are templates, the rest lend names + qualities
+    for m in range(molecules):
+        _, umi, s1, _, s2, _ = real[m]
+        a, b = umi.split(".")
+        start = int(rng.integers(100, 60000))
+        insert = int(max(L, rng.normal(170, 20)))
+        for strand in (0, 1):
+            if strand == 1 and rng.random() >= p_duplex:
+                continue
+            for _ in range(max(1, int(rng.poisson(fam_mean)))):
+                name, _, _, q1, _, q2 = real[donor % len(real)]
+                donor += 1
+                seqs = []
+                for s in (s1, s2):
+                    s = list(s)
+                    for i in np.flatnonzero(rng.random(L) < err):
+                        if s[i] != "N":
+                            s[i] = "ACGT"[("ACGT".index(s[i]) + int(rng.integers(1, 4))) % 4]
+                    seqs.append("".join(s))
+                quals = [np.frombuffer(q.encode(), np.uint8) - 33 for q in (q1, q2)]
+                for i in (0, 1):                 # an N call carries Q2 in real data; a confident N kills the reference (App. B)
+                    quals[i] = quals[i].copy()
+                    quals[i][np.frombuffer(seqs[i].encode(), np.uint8) == ord("N")] = 2
+                qname = "%s|%s.%s" % (name, a, b) if strand == 0 else "%s|%s.%s" % (name, b, a)
+                lo, hi = start, start + insert - L
+                # + strand: lo = R1 fwd (99), hi = R2 rev (147); - strand: lo = R2 fwd (163), hi = R1 rev (83)
+                first, second = (0, 1) if strand == 0 else (1, 0)
+                flags = (99, 147) if strand == 0 else (163, 83)
+                reads.append(Read(qname, flags[0], 0, lo, 60, "%dM" % L, 0, hi, insert, seqs[first], quals[first], rg="1"))
+                reads.append(Read(qname, flags[1], 0, hi, 60, "%dM" % L, 0, lo, -insert, seqs[second], quals[second], rg="1"))
+    order = sorted(range(len(reads)), key=lambda i: reads[i].pos)
+    return [reads[i] for i in order], {"references": ["chr1"], "lengths": [100000]}
+
+
 def build_case(name):
     gen_kw, run_kw = CASES[name]
     run_kw = dict(run_kw)
+    if gen_kw is None:                           # the stand-in for config 1
+        reads, header = c1prime_reads()
+        tuples = [golden.read_to_tuple(r) for r in reads]
+        out = run_reference.run_reference(tuples, header, bedfile=None, **run_kw)
+        return golden.save(name, dict(gen="c1prime_reads()", cutoff=run_kw["cutoff"], scorrect=run_kw["scorrect"], bed=None),
+                           header, tuples, out)
     s = synth.generate(**gen_kw)
     reads = s.to_reads()
     if run_kw.pop("aux", False):

@@ -80,7 +80,7 @@ def _compare(tmp_path, header, reads, regions, cutoff, scorrect):
     return n
 
 
-@pytest.mark.parametrize("name", ["duplex_small", "mode_ties", "undotted_umi", "no_scorrect", "crowded", "bed_three_chr",
+@pytest.mark.parametrize("name", ["c1prime_real_fastq", "duplex_small", "mode_ties", "undotted_umi", "no_scorrect", "crowded", "bed_three_chr",
                                   "big_families", "no_rg_aux"])
 def test_native_emit_equals_python_emit_on_golden_inputs(tmp_path, name):
     g = golden.load(name)
