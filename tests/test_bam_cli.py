@@ -93,7 +93,7 @@ def test_cli_argument_handling(tmp_path, capsys):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["duplex_small", "bed_three_chr", "no_scorrect", "no_rg_aux"])
+@pytest.mark.parametrize("name", ["c1prime_real_fastq", "duplex_small", "bed_three_chr", "no_scorrect", "no_rg_aux"])
 def test_consensus_command_reproduces_reference_tree(tmp_path, name, engine):
     g = golden.load(name)
     reads = [golden.tuple_to_read(t) for t in g["input"]]

@@ -16,7 +16,7 @@ def _write_bed(path, bed):
             fh.write("%s\t%d\t%d\t%s\tgneg\n" % (c, a, b, nm))
 
 
-@pytest.mark.parametrize("name", ["duplex_small", "mode_ties", "bed_three_chr", "crowded", "undotted_umi"])
+@pytest.mark.parametrize("name", ["c1prime_real_fastq", "duplex_small", "mode_ties", "bed_three_chr", "crowded", "undotted_umi"])
 def test_stage_chain_reproduces_reference_tree(tmp_path, name, engine):
     g = golden.load(name)
     reads = [golden.tuple_to_read(t) for t in g["input"]]
