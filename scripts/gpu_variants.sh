@@ -8,7 +8,7 @@ import json, sys
 try:
     d = json.load(open("gpurun_out/var.json"))
     ph = d["roofline"]["phase_ms_per_step"]
-    print("%-40s ms/step %.3f  vote %.3f  sort %.3f segment %.3f join %.3f dcs %.3f" % (sys.argv[1], d["ms_per_step"], ph["vote"], ph["sort"], ph["segment"], ph["join"], ph["dcs"]))
+    print("%-40s ms/step %.3f  %s" % (sys.argv[1], d["ms_per_step"], {k: round(v, 3) for k, v in ph.items()}))
 except Exception as e:
     print(sys.argv[1], "FAILED", e, open("gpurun_out/var.err").read()[-300:])
 PY
