@@ -6,6 +6,9 @@
 // Build: g++ -O2 -std=c++17 -shared -fPIC ccpack.cpp -lz -lpthread
 #include "ccpack.hpp"
 
+#include <chrono>
+#include <cstdlib>
+
 namespace {
 
 struct Block { uint64_t coff, clen, uoff, ulen; };
@@ -30,6 +33,14 @@ extern "C" {
 
 ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
 {
+    const bool timing = getenv("CCP_TIMING") != nullptr;
+    auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "ccp_bam_open %-22s %.3f s\n", what, std::chrono::duration<double>(now - t_start).count());
+        t_start = now;
+    };
     FILE *fh = fopen(path, "rb");
     if (!fh) { set_err(err, errlen, std::string("cannot open ") + path); return nullptr; }
     fseek(fh, 0, SEEK_END);
@@ -62,8 +73,10 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
         total += isize;
         off += blen;
     }
+    lap("read + block table");
     ccp_bam *b = new ccp_bam();
     b->data.resize(total);
+    lap("allocate");
     std::atomic<size_t> next{0};
     std::atomic<bool> ok{true};
     int nt = std::max(1, std::min(threads, 64));
@@ -76,6 +89,7 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
             }
         });
     for (auto &t : pool) t.join();
+    lap("inflate");
     if (!ok) { delete b; set_err(err, errlen, "inflate failed"); return nullptr; }
     const uint8_t *d = b->data.data();
     const uint64_t n = b->data.size();
@@ -95,6 +109,7 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
         b->offsets.push_back(p);
         p += 4 + (uint64_t)rd32(d + p);
     }
+    lap("record index");
     return b;
 }
 
@@ -150,14 +165,14 @@ std::vector<int64_t> visit_order(const ccp_bam *b, const int32_t *regions, int n
 }
 
 // qname.split(delim)[1] (sscs stage) / qname.split('_')[0] (dcs stage), consensus_helper.py:423-431
-std::string barcode_of(std::string_view q, bool sscs, std::string_view delim)
+std::string_view barcode_view(std::string_view q, bool sscs, std::string_view delim)
 {
-    if (!sscs) return std::string(q.substr(0, q.find('_')));
+    if (!sscs) return q.substr(0, q.find('_'));
     size_t a = q.find(delim);
-    if (a == std::string_view::npos) return std::string();
+    if (a == std::string_view::npos) return std::string_view();
     a += delim.size();
     size_t e = q.find(delim, a);
-    return std::string(q.substr(a, e == std::string_view::npos ? e : e - a));
+    return q.substr(a, e == std::string_view::npos ? e : e - a);
 }
 
 }  // namespace
@@ -175,7 +190,16 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
     const uint8_t *d = b->data.data();
     ccp_pack *out = new ccp_pack();
     int64_t *ct = out->counters;
+    const bool timing = getenv("CCP_TIMING") != nullptr;
+    auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "ccp_pack_run %-22s %.3f s\n", what, std::chrono::duration<double>(now - t_start).count());
+        t_start = now;
+    };
     std::vector<int64_t> order = visit_order(b, regions, n_regions);
+    lap("visit order");
     struct Waiting { int64_t idx, step; };
     std::unordered_map<std::string_view, Waiting> waiting;
     waiting.reserve(order.size() / 2 + 16);
@@ -207,12 +231,20 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
         std::sort(left.begin(), left.end(), [](const Waiting &x, const Waiting &y) { return x.step < y.step; });
         for (auto &w : left) out->leftover.push_back(w.idx);
     }
+    lap("filter + pairing");
     const int64_t n = (int64_t)src.size();
     out->fields.resize(n);
     out->lens.resize(n);
     Dict bcs, cigs, rgs;
     uint32_t max_len = 0;
-    std::string ckey;
+    std::string ckey, raw, last_raw;
+    // The dictionaries are keyed by strings, but almost every pair repeats what an earlier one had: look
+    // the raw bytes up first (views into the BAM / binary cigars) and build a string only for a new value.
+    std::unordered_map<std::string_view, uint32_t> bc_seen, rg_seen;
+    std::unordered_map<std::string, uint32_t> cig_seen;
+    uint32_t last_cg = 0;
+    std::string_view last_rg;
+    uint32_t last_rg_id = 0;
     for (int64_t k = 0; k < n; k += 2) {
         Rec read{d + b->offsets[src[k]]}, mate{d + b->offsets[src[k + 1]]};
         for (const Rec *r : {&read, &mate})
@@ -223,11 +255,26 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
                 delete out;
                 return nullptr;
             }
-        const uint32_t bc = bcs.get(barcode_of(read.qname(), sscs, delim));
+        const std::string_view bview = barcode_view(read.qname(), sscs, delim);
+        uint32_t bc;
+        if (auto it = bc_seen.find(bview); it != bc_seen.end()) bc = it->second;
+        else bc_seen.emplace(bview, bc = bcs.get(std::string(bview)));
         // cigar_order (consensus_helper.py:158-172): the read's cigar leads iff (pos and R1) or (neg and R2)
         const bool lead = (strand_of(read) == 1) == (read_number(read.flag()) == 1);
-        ckey = lead ? cigar_string(read) + "_" + cigar_string(mate) : cigar_string(mate) + "_" + cigar_string(read);
-        const uint32_t cg = cigs.get(ckey);
+        const Rec &c1 = lead ? read : mate, &c2 = lead ? mate : read;
+        raw.assign(reinterpret_cast<const char *>(c1.cigar()), 4 * c1.n_cigar());
+        raw.push_back('_');
+        raw.append(reinterpret_cast<const char *>(c2.cigar()), 4 * c2.n_cigar());
+        raw.push_back((char)(c1.n_cigar() & 0xFF));          // the split point (n_cigar is 16 bits), so that two
+        raw.push_back((char)(c1.n_cigar() >> 8));            // different pairs never give the same raw key
+        uint32_t cg;
+        if (k && raw == last_raw) cg = last_cg;
+        else if (auto it = cig_seen.find(raw); it != cig_seen.end()) cg = it->second;
+        else {
+            ckey = cigar_string(c1) + "_" + cigar_string(c2);
+            cig_seen.emplace(raw, cg = cigs.get(ckey));
+        }
+        last_raw = raw; last_cg = cg;
         for (int j = 0; j < 2; j++) {
             const Rec &r = j ? mate : read;
             Fields &f = out->fields[k + j];
@@ -237,7 +284,11 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
             std::string_view g = find_rg(r);
             if (g.data() == nullptr) f.rg = 0xff;
             else {
-                uint32_t id = rgs.get(std::string(g));
+                uint32_t id;
+                if (last_rg.data() != nullptr && g == last_rg) id = last_rg_id;
+                else if (auto it = rg_seen.find(g); it != rg_seen.end()) id = it->second;
+                else rg_seen.emplace(g, id = rgs.get(std::string(g)));
+                last_rg = g; last_rg_id = id;
                 if (id >= 0xff) { set_err(err, errlen, "domain: more than 255 distinct read groups"); delete out; return nullptr; }
                 f.rg = (uint8_t)id;
             }
@@ -245,6 +296,7 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
             max_len = std::max(max_len, r.l_seq());
         }
     }
+    lap("keys + fields");
     out->lpad = std::max(32u, (max_len + 31) / 32 * 32);
     out->stride = (out->lpad / 2 + out->lpad + 63) / 64 * 64;
     out->payload.assign((size_t)n * out->stride, 0);
@@ -270,6 +322,7 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
         for (int t = 0; t < nt; t++) pool.emplace_back(work);
         for (auto &t : pool) t.join();
     }
+    lap("payload");
     out->n_bc = (uint32_t)bcs.names.size();
     out->n_cig = (uint32_t)cigs.names.size();
     out->n_rg = (uint32_t)rgs.names.size();
