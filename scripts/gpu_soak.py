@@ -1,0 +1,38 @@
+#!/usr/bin/env python
+"""One-off soak: many random small and medium batches through the GPU path against the oracle, each batch
+several times (the hash grouping places members in arrival order, so repeats exercise different orders).
+python scripts/gpu_soak.py [first_seed] [count]"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+from consensuscruncher_b200 import pack, synth
+from consensuscruncher_b200.engine import GpuConsensus, GpuError
+from oracle import oracle
+import test_gpu_parity as T
+
+first = int(sys.argv[1]) if len(sys.argv) > 1 else 100
+count = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+bad = 0
+with GpuConsensus(0) as eng:
+    for seed in range(first, first + count):
+        packed, cutoff, scorrect = T._fuzz_case(seed)
+        if seed % 10 == 0:                      # now and then something bigger
+            packed = synth.generate(seed=seed, n_molecules=20000 + 1000 * (seed % 7), L=100 + seed % 60, mapq_mixed=True,
+                                    region=(0, 50000)).to_packed()
+        eng.set_params(cutoff=cutoff, scorrect=scorrect)
+        try:
+            exp, faults = oracle.run(packed, cutoff, scorrect, return_faults=True)
+        except oracle.OracleError:
+            continue
+        if faults:
+            continue
+        for rep in range(3):
+            got = eng.consensus(packed)
+            d = got.diff(exp)
+            if d:
+                bad += 1
+                print("seed", seed, "rep", rep, "differs in", d)
+                break
+print("soak done:", count, "cases,", bad, "bad")
+sys.exit(1 if bad else 0)
