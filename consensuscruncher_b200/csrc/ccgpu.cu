@@ -526,10 +526,10 @@ int launch_vote_small(cc_ctx *ctx, uint32_t rows, uint32_t n_lo, uint32_t n_hi, 
 {
     auto kernel = vote_small_kernel<G, CH, DEPTH, FLUSH>;
     constexpr int ring = vote_ring_bytes(CH, DEPTH);
-    static bool configured = false;      // per template instance
-    if (!configured) {
+    static bool configured[64] = {};     // per template instance and per device (the attribute is per device)
+    if (ctx->device < 0 || ctx->device >= 64 || !configured[ctx->device]) {
         CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
-        configured = true;
+        if (ctx->device >= 0 && ctx->device < 64) configured[ctx->device] = true;
     }
     kernel<<<blocks_for(rows, VOTE_CHUNK), 256, ring, ctx->stream>>>(
         ctx->payload, ctx->stride, ctx->lpad, ctx->perm, ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize),
