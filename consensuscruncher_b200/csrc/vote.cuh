@@ -1,10 +1,11 @@
-// SSCS vote for families of 2..127 reads: sub-warp groups, rows staged through registers.
+// SSCS vote for families of 2..127 reads: sub-warp lane groups, rows staged through a lane-private
+// cp.async ring in shared memory.
 //
 // consensus_maker (SSCS_maker.py:103-155) + read_mode / consensus_flag
 // (consensus_helper.py:483-535) for the bulk of the families.  A group of G lanes owns one
 // family; a lane owns 16 consecutive positions of it (8 sequence bytes + 16 quality bytes
-// per read, one 8-byte and one 16-byte load), so a warp votes 32/G families at once and
-// keeps 32/G times more independent loads in flight than one family per warp.
+// per read, one 8-byte and one 16-byte asynchronous copy), so a warp votes 32/G families at once
+// and keeps 32/G times more independent copies in flight than one family per warp.
 //
 // Per read and 4 positions the work is byte-lane SIMD in 32-bit registers:
 //   pass mask (Q >= 30), base & mask, one-hot counts per base, count of passing reads,
