@@ -382,7 +382,6 @@ struct Emitter {
     std::vector<std::string_view> barcodes, cigar_pairs, rgs;
     std::deque<OutRec> arena;
     std::vector<int64_t> mate_fam;
-    std::unordered_map<int64_t, std::string> ctag;
 
     Emitter(const ccp_bam *bam, const ccp_emit_in &i)
         : b(bam), in(i), fields(reinterpret_cast<const Fields *>(i.fields)),
@@ -407,21 +406,16 @@ struct Emitter {
         return s;
     }
 
-    const std::string &family_ctag(int64_t g)
-    {
-        const int64_t k = in.fam_tmpl[g] >> 1;
-        auto it = ctag.find(k);
-        if (it != ctag.end()) return it->second;
-        Rec read = raw(2 * k), mate = raw(2 * k + 1);
-        const Fields &f = fields[2 * k];
-        return ctag.emplace(k, sscs_qname(read.tid(), read.pos(), mate.tid(), mate.pos(), strand_of(read) == 1,
-                                          read.tlen(), barcodes[f.bc], cigar_pairs[f.cig])).first->second;
-    }
-
     OutRec *passthrough(int64_t record, int64_t fam)
     {
-        Rec t = raw_record(record);
         OutRec &o = arena.emplace_back();
+        fill_passthrough(o, record, fam);
+        return &o;
+    }
+
+    void fill_passthrough(OutRec &o, int64_t record, int64_t fam) const
+    {
+        Rec t = raw_record(record);
         o.fam = fam;
         o.qname = std::string(t.qname());
         o.tid = t.tid(); o.pos = t.pos(); o.mtid = t.mtid(); o.mpos = t.mpos(); o.tlen = t.tlen();
@@ -430,7 +424,16 @@ struct Emitter {
         std::string_view g = find_rg(t);
         o.has_rg = g.data() != nullptr;
         o.rg = g;
-        return &o;
+    }
+
+    // consensus pair name of family g, computed from scratch (the SSCS stage runs on all host threads)
+    std::string pair_name(int64_t g) const
+    {
+        const int64_t k = in.fam_tmpl[g] >> 1;
+        Rec read = raw(2 * k), mate = raw(2 * k + 1);
+        const Fields &f = fields[2 * k];
+        return sscs_qname(read.tid(), read.pos(), mate.tid(), mate.pos(), strand_of(read) == 1, read.tlen(),
+                          barcodes[f.bc], cigar_pairs[f.cig]);
     }
 
     // emit.py:consensus_record - coordinates and cigar of `tpl`, bases and qualities of a consensus row
@@ -536,22 +539,23 @@ int ccp_emit(ccp_bam *b, const ccp_emit_in *in_p, int scorrect, const char *cons
 
         // ---- SSCS stage (SSCS_maker.py:274-298) ---------------------------------------------------
         std::vector<OutRec *> L[F_COUNT];
-        for (int64_t g = 0; g < nf; g++) {
-            const int64_t record = in.src[in.fam_tmpl[g]];
-            std::string qn = E.family_ctag(g) + ":" + std::to_string(in.fam_size[g]);
-            if (in.fam_size[g] == 1) {
-                OutRec *o = E.passthrough(record, g);
-                o->qname = std::move(qn);
-                L[F_SINGLETON].push_back(o);
-            } else {
-                OutRec t = *E.passthrough(record, g);          // coordinates / cigar of the first member
-                E.arena.pop_back();
-                bool has;
-                std::string_view rg = rg_of(in.fam_rg[g], has);
-                L[F_SSCS].push_back(E.consensus(g, std::move(qn), in.sscs_rows, in.sscs_row[g], in.fam_mapq[g],
-                                                in.fam_tlen[g], in.fam_flag[g], has, rg, t));
+        std::vector<OutRec> stage((size_t)nf);               // one record per family, built on all host threads
+        const int64_t chunk = 2048;
+        parallel_for((size_t)((nf + chunk - 1) / chunk), threads, [&](size_t c) {
+            for (int64_t g = (int64_t)c * chunk; g < std::min(nf, (int64_t)(c + 1) * chunk); g++) {
+                OutRec &o = stage[g];
+                E.fill_passthrough(o, in.src[in.fam_tmpl[g]], g);      // coordinates / cigar of the first member
+                o.qname = E.pair_name(g) + ":" + std::to_string(in.fam_size[g]);
+                if (in.fam_size[g] != 1) {                             // consensus: row, mode fields, RG only
+                    bool has;
+                    o.rg = rg_of(in.fam_rg[g], has);
+                    o.has_rg = has;
+                    o.row = in.sscs_rows + (size_t)in.sscs_row[g] * in.stride;
+                    o.mapq = in.fam_mapq[g]; o.tlen = in.fam_tlen[g]; o.flag = in.fam_flag[g];
+                }
             }
-        }
+        });
+        for (int64_t g = 0; g < nf; g++) L[in.fam_size[g] == 1 ? F_SINGLETON : F_SSCS].push_back(&stage[g]);
         lap("sscs stage");
         Emitter::sort_records(L[F_SSCS]);
         Emitter::sort_records(L[F_SINGLETON]);
