@@ -75,7 +75,7 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
     }
     lap("read + block table");
     ccp_bam *b = new ccp_bam();
-    b->data.resize(total);
+    if (!b->data.resize(total)) { delete b; set_err(err, errlen, "out of memory"); return nullptr; }
     lap("allocate");
     std::atomic<size_t> next{0};
     std::atomic<bool> ok{true};

@@ -9,6 +9,7 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <string_view>
@@ -38,8 +39,22 @@ inline void set_err(char *err, int len, const std::string &msg)
 }  // namespace ccp
 using namespace ccp;
 
+// byte buffer that is not zero-filled on allocation (the inflate threads write every byte of it)
+struct RawBytes {
+    uint8_t *p = nullptr;
+    size_t n = 0;
+    RawBytes() = default;
+    RawBytes(const RawBytes &) = delete;
+    RawBytes &operator=(const RawBytes &) = delete;
+    ~RawBytes() { free(p); }
+    bool resize(size_t bytes) { free(p); p = static_cast<uint8_t *>(malloc(bytes ? bytes : 1)); n = p ? bytes : 0; return p != nullptr; }
+    uint8_t *data() { return p; }
+    const uint8_t *data() const { return p; }
+    size_t size() const { return n; }
+};
+
 struct ccp_bam {
-    std::vector<uint8_t> data;            // the whole uncompressed BAM stream
+    RawBytes data;                        // the whole uncompressed BAM stream
     std::string text;
     std::vector<std::string> ref_names;
     std::vector<int32_t> ref_lens;
