@@ -200,9 +200,13 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
     };
     std::vector<int64_t> order = visit_order(b, regions, n_regions);
     lap("visit order");
-    struct Waiting { int64_t idx, step; };
-    std::unordered_map<std::string_view, Waiting> waiting;
-    waiting.reserve(order.size() / 2 + 16);
+    // Mates meet through an open-addressing table keyed by the query name (a slot: hash, record, visit
+    // step; a record leaves the table when its mate arrives, the slot stays as a tombstone so that probe
+    // chains of other names are not cut).
+    struct Waiting { uint64_t hash; int64_t idx, step; };     // idx: -1 empty, -2 tombstone
+    size_t cap = 64;
+    while (cap < order.size() + order.size() / 2 + 16) cap <<= 1;
+    std::vector<Waiting> table(cap, Waiting{0, -1, 0});
     std::vector<int64_t> &src = out->src;
     src.reserve(order.size());
     int64_t step = 0;
@@ -219,15 +223,28 @@ ccp_pack *ccp_pack_run(ccp_bam *b, int stage, const char *delim_c, const int32_t
         else is_bad = false;
         step++;
         if (is_bad && sscs) { out->bad.push_back(i); continue; }
-        auto it = waiting.find(q);
-        if (it == waiting.end()) { waiting.emplace(q, Waiting{i, step}); continue; }
-        src.push_back(it->second.idx);
-        src.push_back(i);
-        waiting.erase(it);
+        const uint64_t h = std::hash<std::string_view>{}(q) | 1;
+        size_t s = (size_t)(h * 0x9E3779B97F4A7C15ull >> 17) & (cap - 1), grave = cap;
+        for (;; s = (s + 1) & (cap - 1)) {
+            Waiting &w = table[s];
+            if (w.idx == -1) {                               // not waiting: this record waits (in the first free slot seen)
+                Waiting &dst = grave != cap ? table[grave] : w;
+                dst = Waiting{h, i, step};
+                break;
+            }
+            if (w.idx == -2) { if (grave == cap) grave = s; continue; }
+            if (w.hash == h && Rec{d + b->offsets[w.idx]}.qname() == q) {
+                src.push_back(w.idx);                        // the pair is complete: first-seen mate, then this one
+                src.push_back(i);
+                w.idx = -2;
+                break;
+            }
+        }
     }
     {
         std::vector<Waiting> left;
-        for (auto &kv : waiting) left.push_back(kv.second);
+        for (auto &w : table)
+            if (w.idx >= 0) left.push_back(w);
         std::sort(left.begin(), left.end(), [](const Waiting &x, const Waiting &y) { return x.step < y.step; });
         for (auto &w : left) out->leftover.push_back(w.idx);
     }
