@@ -101,3 +101,25 @@ def test_native_emit_equals_python_emit_on_synthetic(tmp_path, kw):
     header = bam.BamHeader("", ["chr%d" % (i + 1) for i in range(3)], [10 ** 7] * 3)
     n = _compare(tmp_path, header, reads, None, 0.7, True)
     assert n["dcs.sorted"] and n["sscs.correction.sorted"] and n["all.unique.dcs.sorted"]
+
+
+def test_bad_reads_and_aux_tags_pass_through(tmp_path):
+    """Diverted records (badReads.bam) and singletons keep every field and tag; RG moves to the front."""
+    from consensuscruncher_b200.records import Read
+    s = synth.generate(seed=6, n_molecules=300, L=50, fam_mean=1.6)
+    reads = s.to_reads()
+    for i, r in enumerate(reads):
+        r.aux = {"NM": i % 4, "XA": "alt%d" % (i % 3)} if i % 2 else b""
+        if i % 7 == 0:
+            r.rg = None
+    q = np.full(50, 30, np.uint8)
+    extra = [Read("nodelim", 99, 0, 500, 60, "50M", 0, 700, 250, "A" * 50, q, rg="1"),
+             Read("nodelim", 147, 0, 700, 60, "50M", 0, 500, -250, "C" * 50, q, rg="1"),
+             Read("u|AA.CC", 77, -1, -1, 0, "", -1, -1, 0, "G" * 50, q, aux={"XS": "unmapped"}),
+             Read("u|AA.CC", 141, -1, -1, 0, "", -1, -1, 0, "T" * 50, q),
+             Read("m|AC.GT", 73, 0, 900, 60, "50M", 0, 900, 0, "A" * 50, q, rg="1"),
+             Read("s|AC.GT", 99 | 0x100, 0, 950, 3, "20S30M", 0, 990, 90, "A" * 50, q, rg="1")]
+    reads = sorted(reads + extra, key=lambda r: (r.tid if r.tid >= 0 else 1 << 30, r.pos))
+    header = bam.BamHeader("@HD\tVN:1.6\tSO:coordinate\n", ["chr1"], [10 ** 7])
+    n = _compare(tmp_path, header, reads, None, 0.7, True)
+    assert n["badReads"] == 6 and n["singleton.sorted"]
