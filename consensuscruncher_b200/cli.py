@@ -33,10 +33,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 def default_bedfile(genome):
-    """The reference ships UCSC cytoband tables next to its scripts (`ConsensusCruncher.py:384`).
-    They are third-party data and are not copied into this repository: put
-    `hg19_cytoBand.txt` / `hg38_cytoBand.txt` into consensuscruncher_b200/data/ or name a
-    directory in CC_CYTOBAND_DIR."""
+    """The cytoband table the reference defaults `-b` to (`ConsensusCruncher.py:382-384`, hg38 forced
+    by `-g hg38`, `:143-145`): UCSC's public cytoBand tables, 863 contiguous bands each, shipped as
+    data in consensuscruncher_b200/data/.  CC_CYTOBAND_DIR names another directory."""
     name = "%s_cytoBand.txt" % genome
     for d in (os.environ.get("CC_CYTOBAND_DIR"), os.path.join(HERE, "data")):
         if d and os.path.exists(os.path.join(d, name)):
@@ -167,6 +166,8 @@ def main(argv=None):
     if args.bam is None or args.c_output is None:          # ConsensusCruncher.py:481 (samtools no longer required)
         cons_p.print_help()
         return 0
+    if not os.path.isfile(args.bam):
+        cons_p.error("input BAM %r does not exist" % args.bam)
     bedfile = args.bedfile
     if args.genome == "hg38":                              # overrides even '-b False' (ConsensusCruncher.py:143-145)
         bedfile = default_bedfile("hg38")

@@ -3,6 +3,7 @@
 #include "../../include/ccgpu.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -725,6 +726,10 @@ const char *cc_last_error(cc_ctx *ctx) { return ctx ? ctx->err.c_str() : g_creat
 int cc_set_params(cc_ctx *ctx, const cc_params *params)
 {
     if (!ctx || !params) return CC_ERR_ARG;
+    // the row lists, consensus rows and joins of the loaded batch were made with the old parameters:
+    // later stages must not hand them out as current (the grouping does not depend on either value)
+    if (params->cutoff != ctx->params.cutoff || (params->scorrect != 0) != (ctx->params.scorrect != 0))
+        ctx->voted = ctx->joined = ctx->rescued = false;
     ctx->params = *params;
     ctx->thr_valid = false;
     return CC_OK;
@@ -1124,8 +1129,7 @@ struct StaticVoteScratch {
 static __device__ __align__(256) unsigned char g_static_vote_scratch[sizeof(StaticVoteScratch)];
 
 constexpr int kMaxDevices = 64;
-void *g_static_vote_ptr[kMaxDevices];        // device address of the array, per device
-bool g_static_vote_ready[kMaxDevices];
+std::atomic<void *> g_static_vote_ptr[kMaxDevices];   // device address of the array, per device (nullptr: not looked up yet)
 
 // Everything a call relies on is rewritten here, because the array still holds the previous
 // call's contents: member list, header, the error flag and the field records of this family.
@@ -1166,19 +1170,28 @@ extern "C" int cc_consensus_maker_static(const uint8_t *d_rows, uint32_t n, uint
         return static_fail(CC_ERR_ARG, "cc_consensus_maker_static: device rows must be 4-byte aligned");
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
-        return static_fail(CC_ERR_CUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
-    if (!g_static_vote_ready[dev]) {
-        // once per device, with that device current: the symbol's device address
-        void *p = nullptr;
-        e = cudaGetSymbolAddress(&p, g_static_vote_scratch);
-        if (e != cudaSuccess || p == nullptr)
-            return static_fail(CC_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(e));
-        g_static_vote_ptr[dev] = p;
-        g_static_vote_ready[dev] = true;
-    }
-    StaticVoteScratch *s = reinterpret_cast<StaticVoteScratch *>(g_static_vote_ptr[dev]);
+    if (e != cudaSuccess) return static_fail(CC_ERR_CUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxDevices)
+        return static_fail(CC_ERR_ARG, "cc_consensus_maker_static: device index " + std::to_string(dev) +
+                                           " is outside the " + std::to_string(kMaxDevices) + " devices this entry point keeps an address for");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // the call copies the error flag back and waits for it: neither is legal on a capturing stream,
+    // and trying would invalidate the caller's capture
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    e = cudaStreamIsCapturing(st, &cap);
+    if (e != cudaSuccess) return static_fail(CC_ERR_CUDA, std::string("cudaStreamIsCapturing: ") + cudaGetErrorString(e));
+    if (cap != cudaStreamCaptureStatusNone)
+        return static_fail(CC_ERR_ARG, "cc_consensus_maker_static: the stream is capturing; this call synchronises and cannot be captured");
+    void *scratch = g_static_vote_ptr[dev].load(std::memory_order_acquire);
+    if (scratch == nullptr) {
+        // once per device, with that device current: the symbol's device address.  Two host threads
+        // making the first call together both look it up and publish the same value.
+        e = cudaGetSymbolAddress(&scratch, g_static_vote_scratch);
+        if (e != cudaSuccess || scratch == nullptr)
+            return static_fail(CC_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(e));
+        g_static_vote_ptr[dev].store(scratch, std::memory_order_release);
+    }
+    StaticVoteScratch *s = reinterpret_cast<StaticVoteScratch *>(scratch);
     static_vote_prepare_kernel<<<(n + 255) / 256 > 0 ? (n + 255) / 256 : 1, 256, 0, st>>>(n);
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(CC_ERR_CUDA, std::string("prepare launch: ") + cudaGetErrorString(e));

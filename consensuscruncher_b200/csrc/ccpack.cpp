@@ -43,9 +43,10 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
     };
     FILE *fh = fopen(path, "rb");
     if (!fh) { set_err(err, errlen, std::string("cannot open ") + path); return nullptr; }
-    fseek(fh, 0, SEEK_END);
-    long size = ftell(fh);
-    fseek(fh, 0, SEEK_SET);
+    fseeko(fh, 0, SEEK_END);
+    const int64_t size = (int64_t)ftello(fh);
+    fseeko(fh, 0, SEEK_SET);
+    if (size < 0) { fclose(fh); set_err(err, errlen, std::string("cannot size ") + path); return nullptr; }
     std::vector<uint8_t> comp((size_t)size);
     if (size && fread(comp.data(), 1, (size_t)size, fh) != (size_t)size) {
         fclose(fh);
@@ -61,12 +62,16 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
         if (!(p[0] == 0x1f && p[1] == 0x8b && p[2] == 8 && (p[3] & 4))) { set_err(err, errlen, "not a BGZF block"); return nullptr; }
         uint32_t xlen = rd16(p + 10), bsize = 0;
         bool found = false;
+        if (off + 12 + xlen > (uint64_t)size) { set_err(err, errlen, "damaged BGZF block (extra field runs past the file)"); return nullptr; }
         for (uint32_t q = 0; q + 4 <= xlen;) {
             uint32_t slen = rd16(p + 12 + q + 2);
             if (p[12 + q] == 'B' && p[12 + q + 1] == 'C') { bsize = rd16(p + 12 + q + 4); found = true; }
             q += 4 + slen;
         }
-        if (!found || off + bsize + 1 > (uint64_t)size) { set_err(err, errlen, "damaged BGZF block"); return nullptr; }
+        if (!found || off + bsize + 1 > (uint64_t)size || (uint64_t)bsize + 1 < 12ull + xlen + 8) {
+            set_err(err, errlen, "damaged BGZF block");
+            return nullptr;
+        }
         uint64_t blen = (uint64_t)bsize + 1;
         uint32_t isize = rd32(p + blen - 4);
         blocks.push_back({off + 12 + xlen, blen - 12 - xlen - 8, total, isize});
@@ -94,21 +99,34 @@ ccp_bam *ccp_bam_open(const char *path, int threads, char *err, int errlen)
     const uint8_t *d = b->data.data();
     const uint64_t n = b->data.size();
     if (n < 12 || memcmp(d, "BAM\1", 4) != 0) { delete b; set_err(err, errlen, "not a BAM file"); return nullptr; }
+    // every length field is checked against the inflated size: a truncated or corrupt file gives
+    // "damaged BAM", as bam.py raises, instead of reads past the buffer
+    auto damaged = [&](const char *what) { delete b; set_err(err, errlen, std::string("damaged BAM: ") + what); return nullptr; };
     uint32_t l_text = rd32(d + 4);
+    if (8 + (uint64_t)l_text + 4 > n) return damaged("header text runs past the data");
     b->text.assign(reinterpret_cast<const char *>(d + 8), strnlen(reinterpret_cast<const char *>(d + 8), l_text));
     uint64_t p = 8 + (uint64_t)l_text;
     uint32_t n_ref = rd32(d + p);
     p += 4;
+    if ((uint64_t)n_ref * 8 > n - p) return damaged("reference count exceeds the data");
     for (uint32_t i = 0; i < n_ref; i++) {
+        if (p + 4 > n) return damaged("reference table is truncated");
         uint32_t l_name = rd32(d + p);
+        if (p + 8 + (uint64_t)l_name > n) return damaged("reference name runs past the data");
         b->ref_names.emplace_back(reinterpret_cast<const char *>(d + p + 4), l_name ? l_name - 1 : 0);
         b->ref_lens.push_back(rdi32(d + p + 4 + l_name));
         p += 8 + l_name;
     }
     while (p + 4 <= n) {
+        const uint64_t block_size = rd32(d + p);
+        if (block_size < 32 || p + 4 + block_size > n) return damaged("alignment record runs past the data");
+        const Rec r{d + p};
+        if (32ull + r.l_name() + 4ull * r.n_cigar() + ((uint64_t)r.l_seq() + 1) / 2 + r.l_seq() > block_size)
+            return damaged("alignment record fields exceed its block_size");
         b->offsets.push_back(p);
-        p += 4 + (uint64_t)rd32(d + p);
+        p += 4 + block_size;
     }
+    if (p != n) return damaged("trailing bytes after the last alignment record");
     lap("record index");
     return b;
 }

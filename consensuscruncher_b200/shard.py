@@ -36,9 +36,25 @@ def assign_regions(weights, world):
 
 def region_of_reads(tid, pos, regions):
     """Index of the region (tid, start, end) holding each read start, -1 if none
-    (reads on contigs absent from the bed are never visited)."""
+    (reads on contigs absent from the bed are never visited).
+
+    Disjoint regions (the cytoband tables: 863 contiguous bands) are resolved by one binary
+    search over the (contig, start) keys; overlapping ones keep the last match, region by region."""
     tid = np.asarray(tid)
     pos = np.asarray(pos)
+    if len(regions) == 0:
+        return np.full(tid.shape, -1, np.int64)
+    reg = np.asarray(regions, np.int64).reshape(-1, 3)
+    key = (reg[:, 0] << 32) | reg[:, 1]
+    by_start = np.argsort(key, kind="stable")
+    skey, sreg = key[by_start], reg[by_start]
+    disjoint = bool(np.all((sreg[1:, 0] != sreg[:-1, 0]) | (sreg[1:, 1] >= sreg[:-1, 2]))) and bool(np.all(reg[:, 0] >= 0))
+    if disjoint:
+        rkey = (tid.astype(np.int64) << 32) | np.maximum(pos.astype(np.int64), 0)
+        j = np.searchsorted(skey, rkey, side="right") - 1
+        jj = np.maximum(j, 0)
+        hit = (j >= 0) & (tid >= 0) & (pos >= 0) & (sreg[jj, 0] == tid) & (pos < sreg[jj, 2])
+        return np.where(hit, by_start[jj], -1).astype(np.int64)
     out = np.full(tid.shape, -1, np.int64)
     for i, (t, a, b) in enumerate(regions):
         m = (tid == t) & (pos >= a) & (pos < b)

@@ -230,7 +230,10 @@ int cc_sort_coordinates(cc_ctx *ctx, const int32_t *tid, const int32_t *pos, con
  *
  * Runs on the current device.  Calls no cudaMalloc / cudaFree and no allocating library.
  * The first call on each device looks up the array's device address; make that first call
- * outside any stream capture.  The call waits for its own work before returning.
+ * before any stream capture begins.  Every call copies an error flag back and waits for its
+ * own work before returning, so it must never be made on a stream that is capturing: the call
+ * checks (cudaStreamIsCapturing) and returns CC_ERR_ARG there instead of breaking the capture.
+ * The address look-up may be made by several host threads at once (they publish the same value).
  * All calls on a device share the one array: two calls whose GPU work overlaps (different
  * streams or threads) race; issue them one after the other.
  * Returns CC_ERR_TOO_LARGE if n > CC_STATIC_MAX_READS, CC_ERR_BASE as cc_consensus_maker

@@ -83,8 +83,9 @@ def test_bai_structure_and_counts(tmp_path):
 def test_cli_argument_handling(tmp_path, capsys):
     assert cli.main([]) == 0                                       # prints help like the reference
     assert cli.main(["consensus"]) == 0                            # required arguments missing -> help
-    with pytest.raises(SystemExit):                                # no bedfile installed and none given
+    with pytest.raises(SystemExit):                                # missing input: an argparse error, no traceback
         cli.main(["consensus", "-i", "x.bam", "-o", str(tmp_path)])
+    assert cli.default_bedfile("hg19") and cli.default_bedfile("hg38")   # what `-b` / `-g hg38` default to
     cfg = tmp_path / "c.ini"
     cfg.write_text("[consensus]\nbam = from_config.bam\nc_output = %s\ncutoff = 0.9\nbedfile = False\n" % tmp_path)
     main_p, _ = cli.build_parser(str(cfg))

@@ -144,3 +144,47 @@ def test_q4_rows_round_trip():
     p2 = s.to_packed()
     payload4, table = pack.to_q4(p2)
     assert np.array_equal(pack.from_q4(payload4, table, p2.lpad), p2.payload)
+
+
+# ---- the shard map: the cytoband tables `-b` defaults to (ConsensusCruncher.py:382-384, :143-145) ----
+@pytest.mark.parametrize("genome", ["hg19", "hg38"])
+def test_cytoband_tables_are_863_contiguous_bands(genome):
+    from consensuscruncher_b200 import cli
+    path = cli.default_bedfile(genome)
+    assert path is not None and path.endswith("%s_cytoBand.txt" % genome)
+    bands = keys.bed_separator(path)                   # consensus_helper.py:38-54
+    assert len(bands) == 863
+    per_chrom = {}
+    for key, (a, b) in bands.items():
+        per_chrom.setdefault(key.split("_", 1)[0], []).append((a, b))
+    assert len(per_chrom) == 25
+    for chrom, spans in per_chrom.items():             # no gaps, no overlaps, bed order ascending
+        assert spans[0][0] == 0, chrom
+        for (a0, b0), (a1, b1) in zip(spans, spans[1:]):
+            assert b0 == a1 and a1 < b1, chrom
+
+
+def test_region_of_reads_binary_search_equals_the_region_loop():
+    from consensuscruncher_b200 import cli, shard
+    bands = keys.bed_separator(cli.default_bedfile("hg19"))
+    chroms = []
+    for key in bands:
+        c = key.split("_", 1)[0]
+        if c not in chroms:
+            chroms.append(c)
+    regions = [(chroms.index(k.split("_", 1)[0]), a, b) for k, (a, b) in bands.items()]
+    rng = np.random.default_rng(5)
+    tid = rng.integers(-1, len(chroms) + 2, 20000)
+    pos = rng.integers(-1, 260_000_000, 20000)
+    pick = rng.integers(0, len(regions), 2000)         # plus reads exactly on band edges
+    tid = np.concatenate([tid, [regions[i][0] for i in pick], [regions[i][0] for i in pick]])
+    pos = np.concatenate([pos, [regions[i][1] for i in pick], [regions[i][2] for i in pick]])
+    got = shard.region_of_reads(tid, pos, regions)
+    exp = np.full(tid.shape, -1, np.int64)
+    for i, (t, a, b) in enumerate(regions):
+        exp[(tid == t) & (pos >= a) & (pos < b)] = i
+    assert np.array_equal(got, exp)
+    # overlapping regions keep the loop's answer (last match)
+    odd = [(0, 0, 100), (0, 50, 150), (1, 0, 10)]
+    t2, p2 = np.array([0, 0, 0, 1, 1]), np.array([10, 60, 149, 5, 10])
+    assert shard.region_of_reads(t2, p2, odd).tolist() == [0, 1, 1, 2, -1]

@@ -6,7 +6,8 @@ after start-up, or code that must not trigger the device-wide synchronisation a 
 implies.  For them the library keeps the vote kernel's working memory in a fixed array in
 its own device image; the caller brings the family's rows and the result row as device
 pointers.  This test calls it through the C ABI twice in a row and checks each result,
-byte for byte, against the allocating entry point cc_consensus_maker on the same family.
+byte for byte, against the allocating entry point cc_consensus_maker on the same family
+and - because both run the same vote kernel - against the CPU oracle's consensus_maker too.
 
 It is collected last (file name) so that a run stopping at the first failure has already
 run everything else, and it sets up its own context so it also passes alone.
@@ -18,6 +19,7 @@ import pytest
 
 from consensuscruncher_b200 import pack
 from consensuscruncher_b200.engine import GpuConsensus, load_library
+from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -67,6 +69,8 @@ def test_static_entry_point_matches_allocating_one_twice_in_a_row():
             rc, got = _static_call(lib, torch, rows, lpad, cutoff)
             assert rc == 0, lib.cc_last_error(None).decode()
             assert np.array_equal(got, expected), "n=%d lpad=%d" % (n, lpad)
+            # both entry points share the kernel: the oracle is the independent check
+            assert np.array_equal(got, oracle.consensus_maker_rows(rows, lpad, cutoff)), "oracle, n=%d lpad=%d" % (n, lpad)
 
         # an error raised by one call must not stick to the next one
         bad, _ = _family(rng, 4, 32, n_with_q=True)
@@ -75,6 +79,20 @@ def test_static_entry_point_matches_allocating_one_twice_in_a_row():
         good, _ = _family(rng, 4, 32)
         rc, got = _static_call(lib, torch, good, 32, 0.7)
         assert rc == 0 and np.array_equal(got, eng.consensus_maker_rows(good, 32, 0.7))
+        assert np.array_equal(got, oracle.consensus_maker_rows(good, 32, 0.7))
+
+        # the call synchronises, so a capturing stream is refused instead of breaking the capture
+        side = torch.cuda.Stream()
+        d_rows = torch.from_numpy(good).cuda()
+        d_out = torch.zeros(good.shape[1], dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            graph.capture_begin()
+            rc = lib.cc_consensus_maker_static(d_rows.data_ptr(), good.shape[0], 32, good.shape[1], 0.7,
+                                               d_out.data_ptr(), ctypes.c_void_p(side.cuda_stream))
+            graph.capture_end()
+        assert rc == -2 and b"capturing" in lib.cc_last_error(None)
 
         # sizes beyond the fixed scratch are refused with a clear message, nothing is launched
         big, _ = _family(rng, 8, 32)
