@@ -9,7 +9,16 @@ Poisson(4), both strands present w.p. 0.8, cutoff 0.7, singleton correction on.
 A step is one pass of the whole path (group -> SSCS vote -> DCS join -> rescue -> DCS after
 rescue) over that batch.  With N > 1 every rank owns its own batch (genomic shards are
 independent), so scaling is weak; the only collective is the all-reduce of
-the stats counters and the family-size histogram.
+the stats counters and the family-size histogram, made once per run by libccgpu.so itself
+(cc_stats_allreduce -> ncclAllReduce on one fused buffer).
+
+sharded   extra legs on the same line: ONE dataset of BASELINE.json's stated total size - configs[2]
+          (2e8-read panel) always, configs[3] (1e9-read WGS set) when a rank's share fits (4+ GPUs) -
+          defined band by band over the 863 hg19 cytobands, every rank generating and owning the
+          bands shard.assign_regions deals it: fixed total, strong scaling.  Each leg checks itself
+          inside the run (window oracle on every rank, NCCL-reduced stats and family-size histogram
+          against the generator's own prediction) and the process exits 3 on a mismatch.
+sweep_c5  configs[4] at N = 1: cutoff 0.5-1.0 x scorrect on/off over the panel set, window-checked.
 
 value   reads/s with the batch resident in HBM when the timed region starts
 e2e     reads/s through cc_run_host / cc_run_host_q4: pinned host buffers in, every result array
@@ -58,6 +67,14 @@ def parse():
                          "codes (cc_run_host_q4), or both with the compact one reported when the batch allows it")
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"],
                     help="c2 = BASELINE.json configs[1] (the bench line); c3 / c4: panel / WGS-like batches for profiling")
+    ap.add_argument("--sharded", default="auto",
+                    help="cytoband-sharded fixed-total legs added to the line: 'auto' (c3 always; c4 when a rank's share "
+                         "fits, i.e. 4 or more GPUs), 'none', or a comma list of c3,c4")
+    ap.add_argument("--c3-reads", type=int, default=200_000_000, help="total reads of the sharded panel set (configs[2])")
+    ap.add_argument("--c4-reads", type=int, default=1_000_000_000, help="total reads of the sharded WGS set (configs[3])")
+    ap.add_argument("--shard-steps", type=int, default=5)
+    ap.add_argument("--sweep", default="auto", choices=["auto", "none"],
+                    help="configs[4]: cutoff 0.5-1.0 x scorrect on/off over the panel set on one GPU (N = 1 only)")
     return ap.parse_args()
 
 
@@ -241,6 +258,162 @@ def device_q4(batch):
     return out, table
 
 
+# ---- sharded legs -----------------------------------------------------------------------------
+def _all_ranks_agree(flag_bad, world, dev):
+    """True if any rank reports a failure (so that every rank leaves a leg the same way)."""
+    if world == 1:
+        return bool(flag_bad)
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([1 if flag_bad else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return bool(int(t.item()))
+
+
+def sharded_leg(args, wl, eng, rank, world, local, dev, stream, barrier):
+    """One dataset of BASELINE.json's stated total size (configs[2] / configs[3]), defined band by band
+    over the 863 hg19 cytobands; every rank generates and owns the bands shard.assign_regions gives it,
+    runs the whole path over them as one batch, and the stats are summed by cc_stats_allreduce.
+    Fixed total => strong scaling.  Checked inside the run, outside the timed region:
+      * size-independent properties of every rank's result,
+      * bit-exact comparison with the CPU oracle on a genomic window of every rank's shard,
+      * the NCCL-reduced counters and family-size histogram equal what the generator's molecule
+        model predicts for the whole dataset."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from consensuscruncher_b200 import workloads
+    total_reads = args.c3_reads if wl == "c3" else args.c4_reads
+    pl = workloads.plan(wl, total_reads // 2, seed=1234)
+    t_gen = time.perf_counter()
+    batch, info = workloads.generate_shard(pl, rank, world, str(dev))
+    torch.cuda.synchronize(dev)
+    t_gen = time.perf_counter() - t_gen
+    n = batch.n
+    eng.set_params(cutoff=CUTOFF, scorrect=True)
+
+    def step():
+        eng.load_device(batch.fields.data_ptr(), batch.payload.data_ptr(), n, batch.lpad, batch.stride,
+                        batch.dup_bc.data_ptr(), batch.n_bc)
+        eng.run()
+
+    out = {"workload": pl.describe, "total_reads": 2 * pl.total_pairs, "n_gpus": world, "scaling": "strong",
+           "shard_map": "hg19 cytobands (863) -> ranks by read count (shard.assign_regions)", "steps": args.shard_steps}
+    failed = None
+    try:
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize(dev)
+    except Exception as exc:                     # e.g. a shard that does not fit: no rank enters the collective then
+        failed = "run: %r" % (exc,)
+    if _all_ranks_agree(failed is not None, world, dev):
+        return dict(out, failed=failed or "another rank failed")
+    try:
+        eng.stats_allreduce()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.shard_steps):
+            step()
+        eng.stats_allreduce()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        reduced_stats = eng.fetch("stats").astype(np.int64)
+        reduced_hist = eng.fetch("fam_hist").astype(np.int64)
+    except Exception as exc:                     # a rank that cannot run its shard fails the leg for everybody
+        failed = "run: %r" % (exc,)
+        ms = 0.0
+    if _all_ranks_agree(failed is not None, world, dev):
+        return dict(out, failed=failed or "another rank failed")
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    per = torch.tensor([n, info["n_bands"]], dtype=torch.int64, device=dev)
+    gathered = [torch.zeros_like(per) for _ in range(world)]
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_gather(gathered, per)
+    else:
+        gathered = [per]
+    ms_max = float(t.item())
+
+    # ---- verification (not timed) ----------------------------------------------------------------
+    parity = {}
+    try:
+        from oracle import window as owin            # the checker; never on the measured path
+        owin.oracle.build()
+        step()                                       # a fresh, un-reduced run of this rank's shard
+        counts, _ = owin.check_shard_properties(eng, n)
+        win = workloads.pick_window(batch)
+        parity["window"] = owin.check_window(eng, batch, win, CUTOFF, True) if win is not None else None
+        parity["largest_family"] = int(eng.fetch("fam_size").max()) if n else 0
+        # the generator's prediction for the WHOLE dataset = sum of every rank's shard prediction
+        pred = torch.from_numpy(np.concatenate([info["stats"], info["hist"]])).to(dev)
+        if world > 1:
+            dist.all_reduce(pred)
+        pred = pred.cpu().numpy()
+        if not (reduced_stats[:9] == pred[:9]).all():
+            raise AssertionError("reduced stats %s != generator's %s" % (reduced_stats[:9].tolist(), pred[:9].tolist()))
+        if not (reduced_hist == pred[16:]).all():
+            raise AssertionError("reduced family-size histogram differs from the generator's")
+        parity["reduced_stats_equal_generator"] = True
+        parity["stats"] = {nm: int(reduced_stats[i]) for i, nm in
+                           enumerate(("sscs", "singletons", "dcs", "sscs_singletons", "sc_by_sscs", "sc_by_singleton",
+                                      "uncorrected", "dcs_sc", "sscs_sc_singletons"))}
+    except Exception as exc:
+        failed = "verification on rank %d: %s" % (rank, exc)
+    if _all_ranks_agree(failed is not None, world, dev):
+        out["failed"] = failed or "verification failed on another rank"
+    out.update({"ms_per_step": ms_max / args.shard_steps,
+                "value": 2 * pl.total_pairs * args.shard_steps / (ms_max * 1e-3), "unit": UNIT,
+                "reads_per_rank": [int(g[0]) for g in gathered], "bands_per_rank": [int(g[1]) for g in gathered],
+                "generate_s": round(t_gen, 2), "parity_rank0": parity})
+    batch = None
+    torch.cuda.empty_cache()
+    return out
+
+
+def sweep_leg(args, eng, dev, stream):
+    """BASELINE.json configs[4]: cutoff 0.5 - 1.0 with and without singleton correction over the panel
+    set, one GPU; every case is checked against the oracle on a window of the batch."""
+    import torch
+    from consensuscruncher_b200 import workloads
+    pl = workloads.plan("c3", args.c3_reads // 2, seed=1234)
+    batch, _ = workloads.generate_shard(pl, 0, 1, str(dev), predict=False)
+    n = batch.n
+    win = workloads.pick_window(batch, max_reads=400_000)
+    from oracle import window as owin
+    owin.oracle.build()
+    cases = []
+    for scorrect in (True, False):
+        for cutoff in (0.5, 0.6, 0.7, 0.8, 0.9, 1.0):
+            eng.set_params(cutoff=cutoff, scorrect=scorrect)
+            case = {"cutoff": cutoff, "scorrect": scorrect}
+            try:
+                ms = []
+                for _ in range(3):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(stream)
+                    eng.load_device(batch.fields.data_ptr(), batch.payload.data_ptr(), n, batch.lpad, batch.stride,
+                                    batch.dup_bc.data_ptr(), batch.n_bc)
+                    eng.run()
+                    e1.record(stream)
+                    torch.cuda.synchronize(dev)
+                    ms.append(e0.elapsed_time(e1))
+                c = eng.counts()
+                case.update({"ms_per_step": min(ms), "value": n / (min(ms) * 1e-3), "sscs": int(c["sscs"]),
+                             "dcs": int(c["dcs"]), "dcs_sc": int(c["dcssc"])})
+                w = owin.check_window(eng, batch, win, cutoff, scorrect)
+                case["window"] = {"reads": w["reads"], "families": w["families"], "rows_compared": w["rows_compared"]}
+            except Exception as exc:
+                case["failed"] = "cutoff %.1f scorrect %s: %s" % (cutoff, scorrect, exc)
+            cases.append(case)
+    eng.set_params(cutoff=CUTOFF, scorrect=True)
+    batch = None
+    torch.cuda.empty_cache()
+    return {"workload": pl.describe + "; cutoff 0.5-1.0 x scorrect on/off (BASELINE.json configs[4])",
+            "reads": n, "cases": cases}
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -276,20 +449,21 @@ def main():
     stream = torch.cuda.current_stream(dev)
     eng.set_stream(stream.cuda_stream)
 
-    def reduce_stats():
-        """The path's one collective: sum of the stage counters and the family-size histogram."""
-        if world == 1:
-            return
-        from consensuscruncher_b200.shard import device_tensor
-        for name, dt, count in (("stats", torch.int64, 16), ("fam_hist", torch.int64, 65536)):
-            t = device_tensor(eng.device_ptr(name), count, dt, local)
-            dist.all_reduce(t)
+    def exchange(payload):
+        """Rank 0's communicator id to every rank, over the launcher's process group (host plumbing)."""
+        box = [payload]
+        dist.broadcast_object_list(box, src=0)
+        return box[0]
+
+    # the path's one collective - sum of the stage counters and the family-size histogram - is made by
+    # libccgpu.so itself (cc_stats_allreduce: one ncclAllReduce on the context's stream), once per run
+    from consensuscruncher_b200 import shard
+    shard.connect(eng, rank, world, exchange)
 
     def step():
         eng.load_device(batch.fields.data_ptr(), batch.payload.data_ptr(), n_reads, batch.lpad, batch.stride,
                         batch.dup_bc.data_ptr(), batch.n_bc)
         eng.run()
-        reduce_stats()
 
     def barrier():
         if world > 1:
@@ -301,6 +475,7 @@ def main():
     counts = eng.counts()
     sizes = eng.fetch("fam_size")
     stats_once = eng.fetch("stats")
+    eng.stats_allreduce()                      # warm the collective up too (first call builds NCCL's channels)
 
     # ---- device-resident timing -------------------------------------------------------
     clocks = ClockSampler(local)
@@ -313,6 +488,7 @@ def main():
     e0.record(stream)
     for _ in range(args.steps):
         step()
+    eng.stats_allreduce()                      # once per run, as the reference writes its stats once per stage
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -349,8 +525,6 @@ def main():
         engines = [eng] + [GpuConsensus(local, cutoff=CUTOFF, scorrect=True) for _ in range(n_ctx - 1)]
         eng.set_stream(0)
         h_outs = [{} for _ in range(n_ctx)]
-        turn = {"next": 0}
-        turn_cv = threading.Condition()
 
         # Compact rows (cc_run_host_q4): 4-bit quality codes when the batch has at most 15 distinct
         # non-zero qualities, as binned instruments produce; built here, outside every timed region.
@@ -374,15 +548,6 @@ def main():
             else:
                 e._check(e.lib.cc_run_host(e.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
                                            batch.stride, h_dup.data_ptr(), batch.n_bc))
-            if world > 1:                      # the collective is issued in step order on every rank
-                with turn_cv:
-                    turn_cv.wait_for(lambda: turn["next"] == step_no)
-                    from consensuscruncher_b200.shard import device_tensor
-                    for name, dt, count in (("stats", torch.int64, 16), ("fam_hist", torch.int64, 65536)):
-                        dist.all_reduce(device_tensor(e.device_ptr(name), count, dt, local))
-                    torch.cuda.current_stream(dev).synchronize()
-                    turn["next"] = step_no + 1
-                    turn_cv.notify_all()
             total = 0
             for nm in out_names:
                 what = ARRAYS[nm][0]
@@ -404,7 +569,6 @@ def main():
             return out
 
         def run_steps(count):                  # `count` steps in total, alternating between the contexts
-            turn["next"] = 0
             with ThreadPoolExecutor(max_workers=n_ctx) as ex:
                 futs = [ex.submit(worker, w, w, (count + n_ctx - 1 - w) // n_ctx) for w in range(n_ctx)]
                 return max(f.result() for f in futs)
@@ -417,6 +581,7 @@ def main():
             barrier()
             t0 = time.perf_counter()
             d2h = run_steps(e2e_steps)
+            eng.stats_allreduce()              # the run's one collective (context 0 holds the communicator)
             torch.cuda.synchronize(dev)
             wall = (time.perf_counter() - t0) * 1e3
             barrier()
@@ -447,9 +612,36 @@ def main():
         for extra in engines[1:]:
             extra.close()
 
+    # ---- cytoband-sharded legs: ONE dataset of fixed total size, dealt to the ranks by hg19 band -------
+    sharded, sweep, verify_fail = {}, None, []
+    which = []
+    if args.sharded == "auto":
+        which = ["c3"] + (["c4"] if args.c4_reads // world <= 260_000_000 else [])
+    elif args.sharded != "none":
+        which = [w for w in args.sharded.split(",") if w]
+    if which or (args.sweep == "auto" and world == 1):
+        # release the replica batch and the end-to-end leg's pinned buffers first
+        batch = None
+        h_fields = h_payload = h_dup = h_q4 = h_outs = None
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        eng.set_stream(stream.cuda_stream)
+    for wl in which:
+        res = sharded_leg(args, wl, eng, rank, world, local, dev, stream, barrier)
+        if rank == 0:
+            sharded[wl] = res
+        if res.get("failed"):
+            verify_fail.append("%s: %s" % (wl, res["failed"]))
+    if args.sweep == "auto" and world == 1:
+        sweep = sweep_leg(args, eng, dev, stream)
+        verify_fail += ["c5 %s" % x["failed"] for x in sweep["cases"] if x.get("failed")]
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
+        if verify_fail:
+            sys.exit(3)
         return
 
     # ---- roofline of the dominant kernel (SSCS vote) ----------------------------------------
@@ -500,10 +692,16 @@ def main():
             "roofline": roofline, "cpu_baseline": cpu,
             "counts": {k: int(v) for k, v in counts.items()},
             "stats": {"sscs": int(stats_once[0]), "singletons": int(stats_once[1]), "dcs": int(stats_once[2]),
-                      "dcs_sc": int(stats_once[7])}}
+                      "dcs_sc": int(stats_once[7])},
+            "collective": {"call": "cc_stats_allreduce (libccgpu.so -> ncclAllReduce, int64 x %d, once per run)" % (16 + 65536),
+                           "comm": eng.comm_info()},
+            "sharded": sharded or None, "sweep_c5": sweep}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if verify_fail:
+        sys.stderr.write("bench.py: verification FAILED: %s\n" % "; ".join(verify_fail))
+        sys.exit(3)
 
 
 if __name__ == "__main__":

@@ -7,8 +7,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
+
+#include <dlfcn.h>
+#include <nccl.h>          // types and constants only: the library is loaded at run time (see NcclApi)
 
 #include "kernels.cuh"
 #include "radix_onesweep.cuh"
@@ -33,6 +37,50 @@ struct PhaseTimer {
     double ms = 0.0;
     uint64_t runs = 0;
 };
+
+// NCCL is bound with dlopen when the first communicator call is made, so libccgpu.so has no link-time
+// dependency on it: single-GPU users never load it, and a process that already carries a libnccl.so.2
+// (for instance the one bundled with PyTorch) shares that copy instead of loading a second one.
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetVersion)(int *) = nullptr;
+    std::string error;
+};
+
+NcclApi &nccl_api()
+{
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char *names[] = {getenv("CCGPU_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char *nm : names) {
+            if (!nm || !*nm) continue;
+            api.handle = dlopen(nm, RTLD_NOW | RTLD_LOCAL);
+            if (api.handle) break;
+            api.error = dlerror();
+        }
+        if (!api.handle) { api.error = "cannot load NCCL (" + api.error + "); set CCGPU_NCCL_LIB"; return; }
+        auto sym = [&](const char *nm) { void *p = dlsym(api.handle, nm); if (!p) api.error = std::string("NCCL lacks ") + nm; return p; };
+        api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+        api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+        api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+        api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+        api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+        api.GetVersion = reinterpret_cast<decltype(api.GetVersion)>(sym("ncclGetVersion"));
+        if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy || !api.GetErrorString) {
+            dlclose(api.handle);
+            api.handle = nullptr;
+        } else {
+            api.error.clear();
+        }
+    });
+    return api;
+}
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
            CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_COUNT = 40 };
@@ -81,6 +129,9 @@ struct cc_ctx {
     PhaseTimer phase[CC_PH_COUNT];
     uint64_t launches = 0;
     uint64_t dev_bytes = 0;
+    // multi-GPU: the communicator of cc_comm_init (one rank per context)
+    ncclComm_t comm = nullptr;
+    int comm_rank = 0, comm_nranks = 1;
 };
 
 namespace {
@@ -347,11 +398,12 @@ int do_group(cc_ctx *ctx)
     ctx->next_ticket = 0;
     ctx->gtable_mask = 0;
     TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
-    TRY(ensure(ctx, ctx->stats, 16 * sizeof(unsigned long long)));
-    TRY(ensure(ctx, ctx->hist, CC_HIST_BINS * sizeof(unsigned long long)));
+    // [16 stage counters | CC_HIST_BINS family-size bins]: one buffer, so that cc_stats_allreduce is one collective
+    TRY(ensure(ctx, ctx->stats, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long)));
+    ctx->hist.p = ptr<unsigned long long>(ctx->stats) + 16;                // a view, never released on its own
+    ctx->hist.cap = 0;
     CK(cudaMemsetAsync(ctx->counters.p, 0, CT_COUNT * sizeof(uint32_t), ctx->stream));
-    CK(cudaMemsetAsync(ctx->stats.p, 0, 16 * sizeof(unsigned long long), ctx->stream));
-    CK(cudaMemsetAsync(ctx->hist.p, 0, CC_HIST_BINS * sizeof(unsigned long long), ctx->stream));
+    CK(cudaMemsetAsync(ctx->stats.p, 0, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long), ctx->stream));
     memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
     if (n == 0) { ctx->grouped = true; return CC_OK; }
     if (ctx->group_by_hash) return do_group_hash(ctx);
@@ -706,7 +758,7 @@ void cc_destroy(cc_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
-                     &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->hist, &ctx->stats,
+                     &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->stats,
                      &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
                      &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
                      &ctx->f_dcssc, &ctx->sscs_list, &ctx->dcs_list, &ctx->corr_list, &ctx->dcssc_list, &ctx->sscs_row,
@@ -717,6 +769,7 @@ void cc_destroy(cc_ctx *ctx)
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
+    if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -1105,6 +1158,84 @@ int cc_phase_ms(cc_ctx *ctx, int phase, double *ms, uint64_t *launches)
     TRY(collect_phases(ctx));
     if (ms) *ms = ctx->phase[phase].ms;
     if (launches) *launches = ctx->phase[phase].runs;
+    return CC_OK;
+}
+
+// ---- multi-GPU: the path's one collective ---------------------------------------------------------
+int cc_comm_unique_id(uint8_t id[CC_COMM_ID_BYTES])
+{
+    if (!id) return CC_ERR_ARG;
+    NcclApi &api = nccl_api();
+    if (!api.handle) { g_create_error = api.error; return CC_ERR_COMM; }
+    static_assert(CC_COMM_ID_BYTES == sizeof(ncclUniqueId), "CC_COMM_ID_BYTES must be NCCL's unique-id size");
+    ncclUniqueId uid;
+    ncclResult_t r = api.GetUniqueId(&uid);
+    if (r != ncclSuccess) { g_create_error = std::string("ncclGetUniqueId: ") + api.GetErrorString(r); return CC_ERR_COMM; }
+    memcpy(id, &uid, sizeof(uid));
+    return CC_OK;
+}
+
+int cc_comm_init(cc_ctx *ctx, const uint8_t id[CC_COMM_ID_BYTES], int rank, int nranks)
+{
+    if (!ctx || !id || nranks < 1 || rank < 0 || rank >= nranks) return CC_ERR_ARG;
+    NcclApi &api = nccl_api();
+    if (!api.handle) return fail(ctx, CC_ERR_COMM, api.error.c_str());
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->comm) { api.CommDestroy(ctx->comm); ctx->comm = nullptr; }
+    ncclUniqueId uid;
+    memcpy(&uid, id, sizeof(uid));
+    ncclResult_t r = api.CommInitRank(&ctx->comm, nranks, uid, rank);
+    if (r != ncclSuccess) {
+        ctx->comm = nullptr;
+        ctx->err = std::string("ncclCommInitRank: ") + api.GetErrorString(r);
+        return CC_ERR_COMM;
+    }
+    ctx->comm_rank = rank;
+    ctx->comm_nranks = nranks;
+    return CC_OK;
+}
+
+int cc_comm_destroy(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (ctx->comm) {
+        CK(cudaSetDevice(ctx->device));
+        CK(cudaStreamSynchronize(ctx->stream));
+        nccl_api().CommDestroy(ctx->comm);
+        ctx->comm = nullptr;
+    }
+    ctx->comm_rank = 0;
+    ctx->comm_nranks = 1;
+    return CC_OK;
+}
+
+int cc_stats_allreduce(cc_ctx *ctx)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (!ctx->grouped) return fail(ctx, CC_ERR_ARG, "cc_stats_allreduce before cc_group / cc_run");
+    if (!ctx->comm) return ctx->comm_nranks == 1 ? CC_OK : fail(ctx, CC_ERR_ARG, "cc_stats_allreduce before cc_comm_init");
+    CK(cudaSetDevice(ctx->device));
+    // [16 counters | CC_HIST_BINS bins] is one buffer (do_group): one in-place sum over the ranks, on the
+    // context's stream, ordered after the kernels that filled it
+    ncclResult_t r = nccl_api().AllReduce(ctx->stats.p, ctx->stats.p, 16 + (size_t)CC_HIST_BINS, ncclInt64, ncclSum, ctx->comm,
+                                          ctx->stream);
+    if (r != ncclSuccess) {
+        ctx->err = std::string("ncclAllReduce: ") + nccl_api().GetErrorString(r);
+        return CC_ERR_COMM;
+    }
+    return CC_OK;
+}
+
+int cc_comm_info(cc_ctx *ctx, int *rank, int *nranks, int *nccl_version)
+{
+    if (!ctx) return CC_ERR_ARG;
+    if (rank) *rank = ctx->comm_rank;
+    if (nranks) *nranks = ctx->comm_nranks;
+    if (nccl_version) {
+        *nccl_version = 0;
+        NcclApi &api = nccl_api();
+        if (api.handle && api.GetVersion) api.GetVersion(nccl_version);
+    }
     return CC_OK;
 }
 

@@ -36,7 +36,9 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_load_reads_device", "cc_group", "cc_sscs_vote", "cc_dcs_join", "cc_sc_rescue", "cc_run",
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
-           "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4")
+           "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4",
+           "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
+COMM_ID_BYTES = 128
 
 
 class CcParams(ctypes.Structure):
@@ -98,6 +100,11 @@ def load_library(path=None):
     L.cc_kernel_launches.argtypes = [vp]
     L.cc_device_bytes.restype = u64
     L.cc_device_bytes.argtypes = [vp]
+    L.cc_comm_unique_id.argtypes = [vp]
+    L.cc_comm_init.argtypes = [vp, vp, i32, i32]
+    L.cc_stats_allreduce.argtypes = [vp]
+    L.cc_comm_destroy.argtypes = [vp]
+    L.cc_comm_info.argtypes = [vp, ctypes.POINTER(i32), ctypes.POINTER(i32), ctypes.POINTER(i32)]
     _lib = L
     return L
 
@@ -285,6 +292,37 @@ class GpuConsensus:
                                       np.fromiter((r.pos for r in records), np.int32, n),
                                       np.fromiter((r.flag for r in records), np.uint16, n))
         return [records[i] for i in order]
+
+    # -- multi-GPU: one rank per context, NCCL called by the library itself ---------------
+    @staticmethod
+    def comm_unique_id():
+        """128 bytes from ncclGetUniqueId; rank 0 makes them, the host hands them to every rank."""
+        lib = load_library()
+        buf = (ctypes.c_uint8 * COMM_ID_BYTES)()
+        rc = lib.cc_comm_unique_id(buf)
+        if rc:
+            raise GpuError("cc_comm_unique_id: %s" % lib.cc_last_error(None).decode())
+        return bytes(buf)
+
+    def comm_init(self, unique_id, rank, nranks):
+        """Collective: every rank calls it with the same id (ncclCommInitRank on this context's GPU)."""
+        if len(unique_id) != COMM_ID_BYTES:
+            raise ValueError("the communicator id is %d bytes" % COMM_ID_BYTES)
+        buf = (ctypes.c_uint8 * COMM_ID_BYTES).from_buffer_copy(unique_id)
+        self._check(self.lib.cc_comm_init(self.ctx, buf, int(rank), int(nranks)))
+
+    def stats_allreduce(self):
+        """`stats` and `fam_hist` become the sums over all ranks (one ncclAllReduce, in place, on the
+        context's stream); a no-op without a communicator."""
+        self._check(self.lib.cc_stats_allreduce(self.ctx))
+
+    def comm_destroy(self):
+        self._check(self.lib.cc_comm_destroy(self.ctx))
+
+    def comm_info(self):
+        r, n, v = ctypes.c_int(0), ctypes.c_int(1), ctypes.c_int(0)
+        self._check(self.lib.cc_comm_info(self.ctx, ctypes.byref(r), ctypes.byref(n), ctypes.byref(v)))
+        return {"rank": r.value, "nranks": n.value, "nccl_version": v.value}
 
     # -- timing ------------------------------------------------------------------------
     def profile(self, enable=True):

@@ -9,7 +9,10 @@ consensus_helper.py:38-54) is the default range set; it only ever processes them
 after the other (SSCS_maker.py:229-257).
 
 Ranks never exchange reads.  The only collective is the sum of the stage counters and of
-the family-size histogram at the end (`reduce_stats`), NCCL on GPUs, gloo in CPU tests.
+the family-size histogram at the end: on GPUs `engine.stats_allreduce()` - libccgpu.so calls
+ncclAllReduce itself on one fused buffer (`cc_stats_allreduce`, include/ccgpu.h), no torch in
+between; `connect` hands the communicator id from rank 0 to the other ranks.  `reduce_stats`
+is the same sum for host tensors (gloo) and is what the CPU tests use.
 """
 from __future__ import annotations
 
@@ -92,6 +95,41 @@ def take_pairs(packed, pair_mask):
                        src=None if packed.src is None else packed.src[m],
                        lens=None if packed.lens is None else packed.lens[m],
                        counters=dict(packed.counters))
+
+
+def connect(engine, rank, world, exchange):
+    """Join `engine`'s context to the communicator of `world` ranks.
+
+    `exchange(payload_or_None) -> bytes`: the host's own way of handing rank 0's 128-byte id to every
+    rank (rank 0 passes the id, the others None; all get the id back) - a torch.distributed /
+    MPI broadcast, a shared file, a launcher's key-value store.  Nothing to do for one rank."""
+    if world <= 1:
+        return
+    from .engine import GpuConsensus
+    uid = exchange(GpuConsensus.comm_unique_id() if rank == 0 else None)
+    engine.comm_init(uid, rank, world)
+
+
+def file_exchange(path, rank, timeout=120.0):
+    """An `exchange` for `connect` over a file every rank can see (one node: any temporary directory)."""
+    import os
+    import time
+
+    def exchange(payload):
+        if rank == 0:
+            tmp = "%s.%d" % (path, os.getpid())
+            with open(tmp, "wb") as fh:
+                fh.write(payload)
+            os.replace(tmp, path)
+            return payload
+        t0 = time.time()
+        while not os.path.exists(path):
+            if time.time() - t0 > timeout:
+                raise TimeoutError("no communicator id at %s" % path)
+            time.sleep(0.01)
+        with open(path, "rb") as fh:
+            return fh.read()
+    return exchange
 
 
 def reduce_stats(stats, hist, group=None):

@@ -23,9 +23,10 @@ from .synth import QUAL_PROBS, QUAL_VALUES, _umi_str
 class DeviceBatch:
     """Packed reads in device memory (torch tensors own the storage)."""
 
-    def __init__(self, fields, payload, dup_bc, lpad, stride, L, umi_len):
+    def __init__(self, fields, payload, dup_bc, lpad, stride, L, umi_len, predicted=None):
         self.fields, self.payload, self.dup_bc = fields, payload, dup_bc
         self.lpad, self.stride, self.L, self.umi_len = lpad, stride, L, umi_len
+        self.predicted = predicted          # what the molecule model says the stats must be (predict_stats)
 
     @property
     def n(self):
@@ -76,18 +77,59 @@ def _family_sizes(gen, n, dist, mean, device):
     raise ValueError(dist)
 
 
+def predict_stats(start, insert, umi_a, umi_b, n_plus, n_minus, nb, hist_bins=65536):
+    """Stage counters and family-size histogram the molecule model implies (int64[16], int64[hist_bins]).
+
+    Molecules that agree in start, insert and both UMIs are one molecule to the family key
+    (their strands' pairs share every key field), so they are merged first.  A strand with p pairs
+    gives two tag families of p reads (its R1 and its R2 reads); the duplex partner of a strand's
+    R1 / R2 family is the other strand's R2 / R1 family (duplex_tag swaps the barcode halves and
+    the read number).  Counter indices: include/ccgpu.h `cc_stat`."""
+    key = ((start.to(torch.int64) * 4096 + insert.to(torch.int64)) * nb + umi_a.to(torch.int64)) * nb + umi_b.to(torch.int64)
+    uniq, inv = torch.unique(key, return_inverse=True)
+    P = torch.zeros(uniq.numel(), dtype=torch.int64, device=key.device).index_add_(0, inv, n_plus)
+    M = torch.zeros(uniq.numel(), dtype=torch.int64, device=key.device).index_add_(0, inv, n_minus)
+    big_p, big_m, one_p, one_m = P >= 2, M >= 2, P == 1, M == 1
+    cnt = lambda m: 2 * int(m.sum())
+    st = torch.zeros(16, dtype=torch.int64)
+    st[0] = cnt(big_p) + cnt(big_m)                                   # SSCS
+    st[1] = cnt(one_p) + cnt(one_m)                                   # singletons
+    st[2] = cnt(big_p & big_m)                                        # DCS
+    st[3] = cnt(big_p & ~big_m) + cnt(big_m & ~big_p)                 # SSCS without a partner SSCS
+    st[4] = cnt(one_p & big_m) + cnt(one_m & big_p)                   # singletons corrected by an SSCS
+    st[5] = 2 * cnt(one_p & one_m)                                    # ... by the partner singleton
+    st[6] = cnt(one_p & (M == 0)) + cnt(one_m & (P == 0))             # uncorrected
+    st[7] = cnt((P > 0) & (M > 0))                                    # DCS after the rescue
+    st[8] = cnt(big_p & (M == 0)) + cnt(big_m & (P == 0))             # SSCS still alone after the rescue
+    sizes = torch.cat([P[P > 0], M[M > 0]]).clamp_(max=hist_bins - 1)
+    hist = 2 * torch.bincount(sizes, minlength=hist_bins).to(torch.int64).cpu()
+    return st, hist
+
+
 def generate_device(seed=1234, n_pairs=10_000_000, L=128, umi_len=2, dist="ztpoisson", fam_mean=4.0,
                     p_duplex=0.8, region=(0, 2_300_000), tid=0, insert_mean=170.0, insert_sd=20.0,
-                    err=0.005, p_n=0.001, mapq=60, device="cuda:0", chunk=1 << 20):
-    """Exactly `n_pairs` read pairs (2*n_pairs reads) of duplex-UMI data on `device`."""
+                    err=0.005, p_n=0.001, mapq=60, device="cuda:0", chunk=1 << 20, tail=None,
+                    fields_out=None, payload_out=None, predict=False):
+    """Exactly `n_pairs` read pairs (2*n_pairs reads) of duplex-UMI data on `device`.
+
+    tail = (probability, factor): that share of the strands has `factor` times its drawn size (the
+    10^3 - 10^4-read families of a deep panel).  fields_out / payload_out: write the batch into these
+    slices of a larger batch instead of allocating.  predict: also derive the expected stage counters
+    and size histogram from the molecule list (`DeviceBatch.predicted`)."""
     dev = torch.device(device)
     gen = torch.Generator(device=dev)
     gen.manual_seed(int(seed))
     mean_size = {"ztpoisson": fam_mean / (1 - math.exp(-fam_mean)), "lognormal": fam_mean, "wgs": 1.15}[dist]
     m = int(n_pairs / (mean_size * (1 + p_duplex)) * 1.02) + 16
+    if n_pairs < 2_000_000:                  # small populations (one cytoband of a sharded set) vary more
+        m += int(8 * math.sqrt(n_pairs))
     n_plus = _family_sizes(gen, m, dist, fam_mean, dev)
     has_minus = torch.rand(m, device=dev, generator=gen) < p_duplex
     n_minus = torch.where(has_minus, _family_sizes(gen, m, dist, fam_mean, dev), torch.zeros_like(n_plus))
+    if tail is not None:
+        for sizes in (n_plus, n_minus):
+            jumbo = torch.rand(m, device=dev, generator=gen) < float(tail[0])
+            sizes[jumbo] *= int(tail[1])
     per_mol = n_plus + n_minus
     cum = torch.cumsum(per_mol, 0)
     keep = int((cum <= n_pairs).sum())
@@ -120,7 +162,9 @@ def generate_device(seed=1234, n_pairs=10_000_000, L=128, umi_len=2, dist="ztpoi
     del order
 
     n = 2 * n_pairs
-    fields = torch.empty((n, 8), dtype=torch.int32, device=dev)
+    predicted = predict_stats(start, insert, umi_a, umi_b, n_plus, n_minus, nb) if predict else None
+    fields = torch.empty((n, 8), dtype=torch.int32, device=dev) if fields_out is None else fields_out
+    assert tuple(fields.shape) == (n, 8) and fields.dtype == torch.int32
     ua = torch.where(strand_of_pair == 0, umi_a[mol_of_pair], umi_b[mol_of_pair])
     ub = torch.where(strand_of_pair == 0, umi_b[mol_of_pair], umi_a[mol_of_pair])
     bc = (ua * nb + ub).to(torch.int32)
@@ -141,7 +185,12 @@ def generate_device(seed=1234, n_pairs=10_000_000, L=128, umi_len=2, dist="ztpoi
     dup_bc = ((ids % nb) * nb + ids // nb).to(torch.int32)
 
     lpad, stride = row_geometry(L)
-    payload = torch.zeros((n, stride), dtype=torch.uint8, device=dev)
+    if payload_out is None:
+        payload = torch.zeros((n, stride), dtype=torch.uint8, device=dev)
+    else:
+        payload = payload_out
+        assert tuple(payload.shape) == (n, stride) and payload.dtype == torch.uint8
+        payload.zero_()
     qv = torch.tensor(QUAL_VALUES, dtype=torch.uint8, device=dev)
     qcum = torch.tensor(np.cumsum(QUAL_PROBS)[:-1], dtype=torch.float32, device=dev)
     pairs_per_chunk = max(1, chunk // 2)
@@ -167,4 +216,4 @@ def generate_device(seed=1234, n_pairs=10_000_000, L=128, umi_len=2, dist="ztpoi
         rows[:, lpad // 2:lpad // 2 + L] = qual
     if dev.type == "cuda":
         torch.cuda.synchronize(dev)
-    return DeviceBatch(fields, payload, dup_bc, lpad, stride, L, umi_len)
+    return DeviceBatch(fields, payload, dup_bc, lpad, stride, L, umi_len, predicted)

@@ -68,7 +68,8 @@ enum cc_status {
     CC_ERR_DOMAIN = -5,      /* a read pair does not found/join its two families together:
                                 outside the domain where a consensus pair name owns exactly
                                 two equal families (SSCS_maker.py:275) */
-    CC_ERR_TOO_LARGE = -6
+    CC_ERR_TOO_LARGE = -6,
+    CC_ERR_COMM = -7         /* NCCL could not be loaded, or a communicator call failed   */
 };
 
 /* Result arrays readable with cc_fetch (element types in brackets).  Per-family
@@ -240,6 +241,32 @@ int cc_sort_coordinates(cc_ctx *ctx, const int32_t *tid, const int32_t *pos, con
  * does; the message is read with cc_last_error(NULL). */
 int cc_consensus_maker_static(const uint8_t *d_rows, uint32_t n, uint32_t lpad, uint32_t stride,
                               double cutoff, uint8_t *d_out_row, void *stream);
+
+/* ---- multi-GPU (one process or thread per GPU, one context per rank) -------------------------
+ * The path shards by genomic region: families, duplex partners and rescue partners of a read all
+ * start at that read's position, so ranks that own disjoint sets of the reference's bed regions
+ * (bed_separator, consensus_helper.py:38-54; the region loops SSCS_maker.py:229-257,
+ * DCS_maker.py:185-211, singleton_correction.py:175-213) never exchange reads.  The one exchange is
+ * the sum of what the reference prints once per stage: the stats.txt counters
+ * (SSCS_maker.py:312-318, DCS_maker.py:264-270, singleton_correction.py:294-300) and
+ * Counter(tag_dict.values()) (SSCS_maker.py:360-365).  It is a direct ncclAllReduce(sum, int64) of
+ * [16 counters | CC_HIST_BINS bins] - one buffer, one collective - on the context's stream.
+ * NCCL is loaded with dlopen("libnccl.so.2") at the first of these calls (CCGPU_NCCL_LIB names
+ * another file); nothing else in the library needs it. */
+#define CC_COMM_ID_BYTES 128
+/* Rank 0 creates the id (ncclGetUniqueId) and hands the 128 bytes to every rank by whatever
+ * means the host has (a file, a socket, MPI, a launcher's key-value store). */
+int cc_comm_unique_id(uint8_t id[CC_COMM_ID_BYTES]);
+/* Collective over all ranks: joins the communicator (ncclCommInitRank) on the context's device. */
+int cc_comm_init(cc_ctx *ctx, const uint8_t id[CC_COMM_ID_BYTES], int rank, int nranks);
+/* After cc_run / cc_group (+ later stages): CC_STATS and CC_FAM_HIST become the sums over all ranks,
+ * in place, asynchronously on the context's stream (cc_fetch synchronises).  Every rank must call it
+ * the same number of times.  Without a communicator (single GPU) it does nothing.  Call it once per
+ * run or stage, as the reference writes its stats, not once per batch. */
+int cc_stats_allreduce(cc_ctx *ctx);
+int cc_comm_destroy(cc_ctx *ctx);
+/* rank / nranks of the context's communicator (0 / 1 without one) and NCCL's version code (0 if not loaded). */
+int cc_comm_info(cc_ctx *ctx, int *rank, int *nranks, int *nccl_version);
 
 /* Phase timing with CUDA events on the context's stream. */
 int cc_profile(cc_ctx *ctx, int enable);

@@ -36,7 +36,8 @@ import pytest
 @pytest.mark.gpu
 def test_own_arm_prints_the_contract_line():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "3", "--warmup", "3", "--pairs", "300000",
-                          "--cpu-pairs", "50000"], capture_output=True, text=True, cwd=ROOT, timeout=900)
+                          "--cpu-pairs", "50000", "--c3-reads", "3000000", "--shard-steps", "2"],
+                         capture_output=True, text=True, cwd=ROOT, timeout=900)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
@@ -49,3 +50,8 @@ def test_own_arm_prints_the_contract_line():
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["value"] > 0
+    # the cytoband-sharded panel leg and the cutoff sweep check themselves inside the run
+    c3 = d["sharded"]["c3"]
+    assert "failed" not in c3 and c3["total_reads"] == 3000000 and c3["value"] > 0 and c3["scaling"] == "strong"
+    assert c3["parity_rank0"]["reduced_stats_equal_generator"] and c3["parity_rank0"]["window"]["rows_compared"] > 0
+    assert len(d["sweep_c5"]["cases"]) == 12 and not [c for c in d["sweep_c5"]["cases"] if "failed" in c]
