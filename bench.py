@@ -619,6 +619,14 @@ def main():
         which = ["c3"] + (["c4"] if args.c4_reads // world <= 260_000_000 else [])
     elif args.sharded != "none":
         which = [w for w in args.sharded.split(",") if w]
+    cpu_packed = None
+    if rank == 0 and not args.no_cpu_baseline:
+        # the CPU sample is the head of the batch the GPU just processed (whole pairs, so every kept pair still
+        # founds / joins its two families together), downloaded - not generated again on the host
+        from consensuscruncher_b200.synth_device import DeviceBatch
+        n_cpu = min(batch.n, 2 * args.cpu_pairs)
+        cpu_packed = DeviceBatch(batch.fields[:n_cpu], batch.payload[:n_cpu], batch.dup_bc, batch.lpad, batch.stride,
+                                 batch.L, batch.umi_len).to_packed()
     if which or (args.sweep == "auto" and world == 1):
         # release the replica batch and the end-to-end leg's pinned buffers first
         batch = None
@@ -671,12 +679,7 @@ def main():
     if not args.no_cpu_baseline:
         from oracle import oracle
         oracle.build()
-        # the sample is the head of the batch the GPU just processed (whole pairs, so every kept pair still
-        # founds / joins its two families together), downloaded - not generated again on the host
-        from consensuscruncher_b200.synth_device import DeviceBatch
-        n_cpu = min(batch.n, 2 * args.cpu_pairs)
-        sample = DeviceBatch(batch.fields[:n_cpu], batch.payload[:n_cpu], batch.dup_bc, batch.lpad, batch.stride,
-                             batch.L, batch.umi_len).to_packed()
+        sample = cpu_packed
         t0 = time.perf_counter()
         oracle.run(sample, CUTOFF, True)
         dt = time.perf_counter() - t0

@@ -19,6 +19,7 @@
 #include "scan.cuh"
 #include "vote.cuh"
 #include "group_hash.cuh"
+#include "group_tile.cuh"
 
 using namespace ccgpu;
 
@@ -118,8 +119,11 @@ struct cc_ctx {
     bool thr_valid = false;
     DevBuf tmp_a, tmp_b, tmp_c;   // stand-alone primitives
     DevBuf cs_in, cs_k0, cs_k1, cs_v0, cs_v1;   // cc_sort_coordinates
-    DevBuf gtable;                              // hash grouping (group_hash.cuh)
-    bool group_by_hash = true;
+    DevBuf gtable;                              // hash grouping (group_hash.cuh, group_tile.cuh)
+    DevBuf cursor;                              // tile grouping: next free place of every family's segment
+    enum GroupMode { GROUP_TILE, GROUP_HASH, GROUP_SORT };
+    GroupMode group_mode = GROUP_TILE;
+    bool tile_join = false;                     // the loaded batch was grouped by the tile path (bitmap + word ranks name families)
     uint64_t gtable_mask = 0;                   // non-zero while gtable describes the loaded batch
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
@@ -390,6 +394,62 @@ int do_group_hash(cc_ctx *ctx)
     return CC_OK;
 }
 
+// Grouping tile by tile (group_tile.cuh): the default.  Leaves what the other two paths leave.  Family-level
+// arrays are written by the same kernel that counts the families, so they are sized by their bound, n.
+int do_group_tile(cc_ctx *ctx)
+{
+    const uint64_t n = ctx->n;
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
+    TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
+    TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
+    uint32_t *link = ptr<uint32_t>(ctx->key_a), *final_rep = ptr<uint32_t>(ctx->key_b);
+    uint64_t slots = 1024;
+    while (slots < n + n / 4) slots <<= 1;                  // load factor <= 0.8 even if every read is a family
+    TRY(ensure(ctx, ctx->gtable, slots * sizeof(GroupSlot)));
+    GroupSlot *table = ptr<GroupSlot>(ctx->gtable);
+    const uint64_t words = (n + 31) / 32, tiles = gt_tiles(n);
+    TRY(ensure(ctx, ctx->bitmap, words * 4)); TRY(ensure(ctx, ctx->word_rank, words * 4));
+    TRY(ensure(ctx, ctx->tmpl, n * 4)); TRY(ensure(ctx, ctx->fam_start, n * 4)); TRY(ensure(ctx, ctx->fam_size, n * 4));
+    TRY(ensure(ctx, ctx->cursor, n * 4)); TRY(ensure(ctx, ctx->is_sscs, n + 4)); TRY(ensure(ctx, ctx->fam_mapq, n));
+    TRY(ensure(ctx, ctx->fam_rg, n)); TRY(ensure(ctx, ctx->fam_flag, n * 2)); TRY(ensure(ctx, ctx->fam_tlen, n * 4));
+    TRY(ensure(ctx, ctx->partner, n * 4));
+    TRY(ensure(ctx, ctx->scan_status, (tiles + 1) * sizeof(unsigned long long)));
+
+    TRY(phase_begin(ctx, CC_PH_HASH));
+    CK(cudaMemsetAsync(table, 0xFF, slots * sizeof(GroupSlot), ctx->stream));
+    LAUNCH(tile_insert_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, table, slots - 1, link);
+    TRY(phase_end(ctx, CC_PH_HASH));
+
+    TRY(phase_begin(ctx, CC_PH_SEGMENT));
+    CK(cudaMemsetAsync(ctx->scan_status.p, 0, (tiles + 1) * sizeof(unsigned long long), ctx->stream));
+    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    uint32_t *ticket = ctr + CT_TICKET0 + ctx->next_ticket++;
+    LAUNCH(tile_number_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, table, link, final_rep,
+           ptr<unsigned long long>(ctx->scan_status), ticket, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
+           ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->cursor),
+           ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
+           ptr<uint8_t>(ctx->fam_rg), ptr<int32_t>(ctx->partner), ptr<unsigned long long>(ctx->hist), (uint32_t)CC_HIST_BINS,
+           ctr + CT_NMID, ctr + CT_NFAM);
+    ctx->perm = ptr<uint32_t>(ctx->val_a);
+    ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family, materialised when somebody fetches it
+    ctx->sorted_keys = ctx->spare_keys = nullptr;
+    LAUNCH(tile_place_kernel, (unsigned)tiles, GT_THREADS, n, link, final_rep, ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->cursor), ctx->perm);
+    TRY(read_counters(ctx));
+    const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
+    ctx->read_fam_ready = false;
+    ctx->gtable_mask = slots - 1;
+    ctx->tile_join = true;
+    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
+           ctr + CT_FAULTS);
+    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
+    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS,
+                      ptr<int32_t>(ctx->sscs_row)));
+    TRY(phase_end(ctx, CC_PH_SEGMENT));
+    ctx->grouped = true;
+    return CC_OK;
+}
+
 int do_group(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
@@ -397,6 +457,7 @@ int do_group(cc_ctx *ctx)
     ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = ctx->n_extra = 0;
     ctx->next_ticket = 0;
     ctx->gtable_mask = 0;
+    ctx->tile_join = false;
     TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
     // [16 stage counters | CC_HIST_BINS family-size bins]: one buffer, so that cc_stats_allreduce is one collective
     TRY(ensure(ctx, ctx->stats, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long)));
@@ -406,7 +467,8 @@ int do_group(cc_ctx *ctx)
     CK(cudaMemsetAsync(ctx->stats.p, 0, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long), ctx->stream));
     memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
     if (n == 0) { ctx->grouped = true; return CC_OK; }
-    if (ctx->group_by_hash) return do_group_hash(ctx);
+    if (ctx->group_mode == cc_ctx::GROUP_TILE) return do_group_tile(ctx);
+    if (ctx->group_mode == cc_ctx::GROUP_HASH) return do_group_hash(ctx);
 
     TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
     TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
@@ -484,6 +546,13 @@ int do_join_index(cc_ctx *ctx)
     TRY(phase_begin(ctx, CC_PH_JOIN));
     CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
     if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
+    if (ctx->gtable_mask && ctx->tile_join) {
+        LAUNCH(tile_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,
+               ptr<GroupSlot>(ctx->gtable), ctx->gtable_mask, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
+               ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
+        TRY(phase_end(ctx, CC_PH_JOIN));
+        return do_classify(ctx);
+    }
     if (ctx->gtable_mask) {
         // the grouping table already maps every family tuple to its first read
         LAUNCH(group_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,
@@ -740,7 +809,8 @@ cc_ctx *cc_create(int device, const cc_params *params)
         return nullptr;
     }
     cc_ctx *ctx = new cc_ctx();
-    if (const char *g = getenv("CCGPU_GROUP")) ctx->group_by_hash = strcmp(g, "sort") != 0;   // "sort": the radix-sort grouping
+    if (const char *g = getenv("CCGPU_GROUP"))         // "sort": radix-sort grouping, "hash": one table trip per read
+        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "hash") ? cc_ctx::GROUP_HASH : cc_ctx::GROUP_TILE;
     ctx->device = device;
     if (params) ctx->params = *params;
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -765,7 +835,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
                      &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->mid_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
-                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable};
+                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable, &ctx->cursor};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
