@@ -121,8 +121,9 @@ struct cc_ctx {
     DevBuf cs_in, cs_k0, cs_k1, cs_v0, cs_v1;   // cc_sort_coordinates
     DevBuf gtable;                              // hash grouping (group_hash.cuh, group_tile.cuh)
     DevBuf cursor;                              // tile grouping: next free place of every family's segment
+    DevBuf word_reads, word_start;              // ... per bitmap word: reads in the families founded there, and their prefix
     enum GroupMode { GROUP_TILE, GROUP_HASH, GROUP_SORT };
-    GroupMode group_mode = GROUP_TILE;
+    GroupMode group_mode = GROUP_HASH;
     bool tile_join = false;                     // the loaded batch was grouped by the tile path (bitmap + word ranks name families)
     uint64_t gtable_mask = 0;                   // non-zero while gtable describes the loaded batch
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
@@ -413,7 +414,6 @@ int do_group_tile(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->cursor, n * 4)); TRY(ensure(ctx, ctx->is_sscs, n + 4)); TRY(ensure(ctx, ctx->fam_mapq, n));
     TRY(ensure(ctx, ctx->fam_rg, n)); TRY(ensure(ctx, ctx->fam_flag, n * 2)); TRY(ensure(ctx, ctx->fam_tlen, n * 4));
     TRY(ensure(ctx, ctx->partner, n * 4));
-    TRY(ensure(ctx, ctx->scan_status, (tiles + 1) * sizeof(unsigned long long)));
 
     TRY(phase_begin(ctx, CC_PH_HASH));
     CK(cudaMemsetAsync(table, 0xFF, slots * sizeof(GroupSlot), ctx->stream));
@@ -421,19 +421,22 @@ int do_group_tile(cc_ctx *ctx)
     TRY(phase_end(ctx, CC_PH_HASH));
 
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
-    CK(cudaMemsetAsync(ctx->scan_status.p, 0, (tiles + 1) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
-    uint32_t *ticket = ctr + CT_TICKET0 + ctx->next_ticket++;
-    LAUNCH(tile_number_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, table, link, final_rep,
-           ptr<unsigned long long>(ctx->scan_status), ticket, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
+    uint32_t *founder_cnt = ptr<uint32_t>(ctx->val_b);      // dead once the family records are written
+    TRY(ensure(ctx, ctx->word_reads, words * 4)); TRY(ensure(ctx, ctx->word_start, words * 4));
+    LAUNCH(tile_mark_kernel, blocks_for(n, 256), 256, n, table, link, final_rep, founder_cnt, ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->word_reads));
+    TRY(scan_popcounts(ctx, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), words, ctr + CT_NFAM));
+    TRY(scan_exclusive(ctx, ptr<uint32_t>(ctx->word_reads), ptr<uint32_t>(ctx->word_start), words));
+    LAUNCH(tile_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, n, founder_cnt,
+           ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->word_start),
            ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->cursor),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
            ptr<uint8_t>(ctx->fam_rg), ptr<int32_t>(ctx->partner), ptr<unsigned long long>(ctx->hist), (uint32_t)CC_HIST_BINS,
-           ctr + CT_NMID, ctr + CT_NFAM);
+           ctr + CT_NMID);
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family, materialised when somebody fetches it
     ctx->sorted_keys = ctx->spare_keys = nullptr;
-    LAUNCH(tile_place_kernel, (unsigned)tiles, GT_THREADS, n, link, final_rep, ptr<uint32_t>(ctx->bitmap),
+    LAUNCH(tile_place_kernel, (unsigned)tiles, GP_THREADS, n, link, final_rep, ptr<uint32_t>(ctx->bitmap),
            ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->cursor), ctx->perm);
     TRY(read_counters(ctx));
     const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
@@ -539,7 +542,6 @@ int do_join_index(cc_ctx *ctx)
     const uint32_t nf = ctx->n_fam;
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     TRY(ensure(ctx, ctx->partner, (size_t)nf * 4));
-    TRY(ensure(ctx, ctx->f_dcs, nf)); TRY(ensure(ctx, ctx->f_corr, nf)); TRY(ensure(ctx, ctx->f_dcssc, nf));
     TRY(ensure(ctx, ctx->dcs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->corr_list, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->dcssc_list, (size_t)nf * 4));
     if (nf == 0) return CC_OK;
@@ -577,20 +579,21 @@ int do_classify(cc_ctx *ctx)
     const uint32_t nf = ctx->n_fam;
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     TRY(phase_begin(ctx, CC_PH_CLASSIFY));
-    LAUNCH(classify_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
-           (int)ctx->params.scorrect, ptr<uint8_t>(ctx->f_dcs), ptr<uint8_t>(ctx->f_corr),
-           ptr<uint8_t>(ctx->f_dcssc), ptr<unsigned long long>(ctx->stats), ctr + CT_ONESIDED);
-    // the compactions also leave family -> output row; in the second DCS pass the SSCS-SSCS pairs keep
-    // their DCS row and the pairs with a corrected singleton follow in the same pool
+    // one chained scan classifies the families and writes the three lists with their family -> row maps;
+    // in the second DCS pass the SSCS-SSCS pairs keep their DCS row and the pairs with a corrected
+    // singleton follow in the same pool (dcssc_row is finished in do_lists, once n_dcs is known)
     TRY(ensure(ctx, ctx->dcs_row, (size_t)nf * 4)); TRY(ensure(ctx, ctx->corr_row, (size_t)nf * 4));
     TRY(ensure(ctx, ctx->dcssc_row, (size_t)nf * 4));
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcs), nf, ptr<uint32_t>(ctx->dcs_list), ctr + CT_NDCS,
-                      ptr<int32_t>(ctx->dcs_row)));
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_corr), nf, ptr<uint32_t>(ctx->corr_list), ctr + CT_NCORR,
-                      ptr<int32_t>(ctx->corr_row)));
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->f_dcssc), nf, ptr<uint32_t>(ctx->dcssc_list), ctr + CT_NDCSSC,
-                      ptr<int32_t>(ctx->dcssc_row), ctx->params.scorrect ? ptr<int32_t>(ctx->dcs_row) : nullptr,
-                      ctr + CT_NDCS));
+    const uint64_t tiles = ((uint64_t)nf + CLS_TILE - 1) / CLS_TILE;
+    TRY(ensure(ctx, ctx->scan_status, (2 * tiles + 2) * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * tiles + 2) * sizeof(unsigned long long), ctx->stream));
+    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    uint32_t *ticket = ctr + CT_TICKET0 + ctx->next_ticket++;
+    LAUNCH(classify_scan_kernel, (unsigned)tiles, CLS_THREADS, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
+           (int)ctx->params.scorrect, ptr<unsigned long long>(ctx->scan_status), ticket, ptr<uint32_t>(ctx->dcs_list),
+           ptr<uint32_t>(ctx->corr_list), ptr<uint32_t>(ctx->dcssc_list), ptr<int32_t>(ctx->dcs_row), ptr<int32_t>(ctx->corr_row),
+           ptr<int32_t>(ctx->dcssc_row), ptr<unsigned long long>(ctx->stats), ctr + CT_ONESIDED, ctr + CT_NDCS, ctr + CT_NCORR,
+           ctr + CT_NDCSSC);
     TRY(phase_end(ctx, CC_PH_CLASSIFY));
     return CC_OK;
 }
@@ -611,6 +614,8 @@ int do_lists(cc_ctx *ctx, bool with_join)
         ctx->n_corr = ctx->host_ctr[CT_NCORR];
         ctx->n_extra = ctx->host_ctr[CT_NDCSSC];
         ctx->n_dcssc = ctx->params.scorrect ? ctx->n_dcs + ctx->n_extra : 0;
+        if (ctx->n_fam)
+            LAUNCH(dcssc_row_finish_kernel, blocks_for(ctx->n_fam, 256), 256, ptr<int32_t>(ctx->dcssc_row), ctx->n_fam, ctx->n_dcs);
     }
     ctx->listed = true;
     return CC_OK;
@@ -810,7 +815,7 @@ cc_ctx *cc_create(int device, const cc_params *params)
     }
     cc_ctx *ctx = new cc_ctx();
     if (const char *g = getenv("CCGPU_GROUP"))         // "sort": radix-sort grouping, "hash": one table trip per read
-        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "hash") ? cc_ctx::GROUP_HASH : cc_ctx::GROUP_TILE;
+        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "tile") ? cc_ctx::GROUP_TILE : cc_ctx::GROUP_HASH;
     ctx->device = device;
     if (params) ctx->params = *params;
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -835,7 +840,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
                      &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->mid_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
-                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable, &ctx->cursor};
+                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable, &ctx->cursor, &ctx->word_reads, &ctx->word_start};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);

@@ -11,11 +11,16 @@
 //                 (claim / lower the slot's read index, subtract 2 x members from the slot's counter).
 //                 Per read one word is kept: representative and rank inside the tile's group, or -
 //                 for a representative - the global slot.
-//   tile_number   (after every tile has inserted) a representative whose slot still names it founds the
-//                 family.  One chained scan (decoupled look-back) over the tiles carries two sums - founders
-//                 and their family sizes - so the same kernel numbers the families in creation order AND
-//                 places their segments: template, size, segment start, class, singleton fields, size
-//                 histogram, the bitmap of founders with its word ranks.
+//   tile_mark     (after every tile has inserted) a representative reads its slot once: the slot's final
+//                 read index is the family's founder.  Founders are marked in a bitmap (one ballot per 32
+//                 reads) next to the number of reads their families hold.
+//   (two scans over the bitmap's words: founders before a word = family numbers in creation order,
+//    reads before a word = where the segments start)
+//   tile_family   founders write the family records: template, size, segment start, class, singleton
+//                 fields, size histogram.
+//   (A version that fused mark + numbering + records into one chained scan over the tiles ran at 0.43 ms
+//    against 0.2 ms for these pieces: every CTA sat at a barrier while its first warp looked back, behind
+//    predecessors that were themselves waiting for their table gathers.)
 //   tile_place    a representative looks its family up (rank query at the founder's bit), reserves
 //                 room for its tile's members in the family's segment with one atomic, and the
 //                 members write their places.
@@ -32,9 +37,14 @@
 
 namespace ccgpu {
 
-constexpr int GT_THREADS = 256;
-constexpr int GT_PER = 4;                       // reads per thread
-constexpr int GT_TILE = GT_THREADS * GT_PER;    // reads per tile
+#ifndef GT_INSERT_THREADS_CFG
+#define GT_INSERT_THREADS_CFG 512
+#endif
+constexpr int GT_TILE = 1024;                   // reads per tile
+constexpr int GT_THREADS = GT_INSERT_THREADS_CFG;   // tile_insert: threads per tile
+constexpr int GT_PER = GT_TILE / GT_THREADS;    // ... and reads per thread
+constexpr int GP_THREADS = 256;                 // tile_place
+constexpr int GP_PER = GT_TILE / GP_THREADS;
 constexpr uint32_t GT_HT = 2 * GT_TILE;         // shared table slots
 constexpr uint32_t GT_EMPTY = 0xFFFFFFFFu;
 constexpr uint32_t LINK_REP = 0x80000000u;      // link word of a tile representative: flag | global slot
@@ -149,142 +159,91 @@ tile_insert_kernel(const uint4 *__restrict__ fields, uint64_t n, GroupSlot *__re
     }
 }
 
-// status word of the chained scan: state (2 bits) | founders (31 bits) | reads in their families (31 bits)
-__device__ __forceinline__ unsigned long long gt_pack(uint32_t state, uint32_t fams, uint32_t reads)
+// (after every tile has inserted) one thread per read, a warp = one word of the founders' bitmap.
+// A representative reads its slot once: the slot's final read index names the family's founder; a
+// representative that IS that index founds the family and keeps the slot's counter for tile_family.
+// Also per word: the number of reads in the families its founders found (their segments' total length).
+__global__ void __launch_bounds__(256)
+tile_mark_kernel(uint64_t n, const GroupSlot *__restrict__ table, const uint32_t *__restrict__ link,
+                 uint32_t *__restrict__ final_rep, uint32_t *__restrict__ founder_cnt,
+                 uint32_t *__restrict__ bitmap, uint32_t *__restrict__ word_reads)
 {
-    return ((unsigned long long)state << 62) | ((unsigned long long)fams << 31) | reads;
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool founder = false;
+    uint32_t size = 0;
+    if (i < n) {
+        const uint32_t lk = link[i];
+        if (lk & LINK_REP) {
+            const uint2 s = *reinterpret_cast<const uint2 *>(&table[lk & ~LINK_REP]);
+            final_rep[i] = s.x;                                   // tile_place asks for the family of this read
+            if (s.x == (uint32_t)i) {
+                founder = true;
+                founder_cnt[i] = s.y;
+                size = (~s.y) >> 1;
+            }
+        }
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, founder);
+    const uint32_t reads = __reduce_add_sync(0xffffffffu, size);
+    if ((threadIdx.x & 31) == 0 && i < n) {
+        bitmap[i >> 5] = word;
+        word_reads[i >> 5] = reads;
+    }
 }
 
-__global__ void __launch_bounds__(GT_THREADS)
-tile_number_kernel(const uint4 *__restrict__ fields, uint64_t n, const GroupSlot *__restrict__ table,
-                   const uint32_t *__restrict__ link, uint32_t *__restrict__ final_rep,
-                   unsigned long long *status, uint32_t *ticket,
-                   uint32_t *__restrict__ bitmap, uint32_t *__restrict__ word_rank,
+// (after the two scans over the words: founders before a word, reads before a word) founders write
+// the family records in creation order; a family's segment starts where the earlier families' end.
+__global__ void __launch_bounds__(256)
+tile_family_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t *__restrict__ founder_cnt,
+                   const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ word_rank,
+                   const uint32_t *__restrict__ word_start,
                    uint32_t *__restrict__ tmpl, uint32_t *__restrict__ fam_size, uint32_t *__restrict__ fam_start,
                    uint32_t *__restrict__ cursor, uint8_t *__restrict__ is_sscs, uint8_t *__restrict__ fam_mapq,
                    uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
                    int32_t *__restrict__ partner, unsigned long long *__restrict__ hist, uint32_t hist_bins,
-                   uint32_t *__restrict__ n_mid, uint32_t *__restrict__ n_fam_out)
+                   uint32_t *__restrict__ n_mid)
 {
-    __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_warp_f[GT_THREADS / 32], s_warp_r[GT_THREADS / 32];
-    __shared__ uint32_t s_excl_f, s_excl_r;
     __shared__ uint32_t small_hist[256];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    small_hist[tid] = 0;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);        // tiles are numbered in the order they start: a tile only waits on started ones
+    small_hist[threadIdx.x] = 0;
     __syncthreads();
-    const uint32_t tile = s_tile;
-    const uint64_t base = (uint64_t)tile * GT_TILE + (uint64_t)tid * GT_PER;   // a thread owns 4 consecutive reads
-
-    uint32_t lk[GT_PER] = {0, 0, 0, 0};
-    if (base + GT_PER <= n) {
-        const uint4 q = *reinterpret_cast<const uint4 *>(link + base);
-        lk[0] = q.x; lk[1] = q.y; lk[2] = q.z; lk[3] = q.w;
-    } else {
+    const int lane = threadIdx.x & 31;
+    // grid-stride over words (a warp per word): a few CTAs per SM, so the shared histogram is flushed rarely
+    const uint64_t words = (n + 31) / 32;
+    for (uint64_t w = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += ((uint64_t)gridDim.x * blockDim.x) >> 5) {
+        const uint32_t word = __ldg(&bitmap[w]);
+        if (word == 0) continue;
+        const bool founder = (word >> lane) & 1u;
+        const uint64_t i = w * 32 + lane;
+        uint32_t cnt = 0, size = 0;
+        if (founder) { cnt = founder_cnt[i]; size = (~cnt) >> 1; }
+        uint32_t incl = size;                                     // starts of the word's families: prefix of their sizes
 #pragma unroll
-        for (int k = 0; k < GT_PER; k++) lk[k] = base + k < n ? link[base + k] : 0u;
-    }
-    uint32_t size[GT_PER], cnt[GT_PER];
-    uint32_t founders = 0, reads = 0, bits = 0;
-#pragma unroll
-    for (int k = 0; k < GT_PER; k++) {
-        size[k] = 0;
-        if (base + k < n && (lk[k] & LINK_REP)) {
-            const uint2 s = *reinterpret_cast<const uint2 *>(&table[lk[k] & ~LINK_REP]);
-            final_rep[base + k] = s.x;                               // tile_place asks for the family of this read
-            if (s.x == (uint32_t)(base + k)) {
-                cnt[k] = s.y;
-                size[k] = (~s.y) >> 1;
-                founders++;
-                reads += size[k];
-                bits |= 1u << k;
-            }
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
         }
-    }
-    // block-wide exclusive prefixes of (founders, reads)
-    uint32_t inc_f = founders, inc_r = reads;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t a = __shfl_up_sync(0xffffffffu, inc_f, d), b = __shfl_up_sync(0xffffffffu, inc_r, d);
-        if (lane >= d) { inc_f += a; inc_r += b; }
-    }
-    if (lane == 31) { s_warp_f[warp] = inc_f; s_warp_r[warp] = inc_r; }
-    __syncthreads();
-    uint32_t off_f = 0, off_r = 0, tot_f = 0, tot_r = 0;
-#pragma unroll
-    for (int k = 0; k < GT_THREADS / 32; k++) {
-        if (k < warp) { off_f += s_warp_f[k]; off_r += s_warp_r[k]; }
-        tot_f += s_warp_f[k]; tot_r += s_warp_r[k];
-    }
-    if (warp == 0) {
-        // look-back by a whole warp: 32 predecessors per round, nearest first (scan.cuh)
-        uint32_t ex_f = 0, ex_r = 0;
-        if (tile != 0) {
-            if (lane == 0) st_status(&status[tile], gt_pack(1, tot_f, tot_r));
-            for (int64_t p = (int64_t)tile - 1;; p -= 32) {
-                const int64_t idx = p - lane;
-                unsigned long long s = idx >= 0 ? ld_status(&status[idx]) : gt_pack(2, 0, 0);
-                while (__any_sync(0xffffffffu, (s >> 62) == 0))
-                    if ((s >> 62) == 0) s = ld_status(&status[idx]);
-                const uint32_t done = __ballot_sync(0xffffffffu, (s >> 62) == 2);
-                const int first = done ? __ffs(done) - 1 : 31;
-                uint32_t vf = lane <= first ? (uint32_t)(s >> 31) & 0x7FFFFFFFu : 0u;
-                uint32_t vr = lane <= first ? (uint32_t)s & 0x7FFFFFFFu : 0u;
-#pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) {
-                    vf += __shfl_xor_sync(0xffffffffu, vf, d);
-                    vr += __shfl_xor_sync(0xffffffffu, vr, d);
-                }
-                ex_f += vf; ex_r += vr;
-                if (done) break;
-            }
-        }
-        if (lane == 0) {
-            st_status(&status[tile], gt_pack(2, ex_f + tot_f, ex_r + tot_r));
-            s_excl_f = ex_f; s_excl_r = ex_r;
-            if (tile == gridDim.x - 1) *n_fam_out = ex_f + tot_f;
-        }
-    }
-    __syncthreads();
-    uint32_t c = s_excl_f + off_f + (inc_f - founders);          // family number of this thread's first founder
-    uint32_t start = s_excl_r + off_r + (inc_r - reads);
-
-    // bitmap of founders: 8 threads x 4 reads = one word; word_rank = founders before the word
-    uint32_t word = bits << (4 * (lane & 7));
-    word |= __shfl_xor_sync(0xffffffffu, word, 1);
-    word |= __shfl_xor_sync(0xffffffffu, word, 2);
-    word |= __shfl_xor_sync(0xffffffffu, word, 4);
-    if ((lane & 7) == 0 && base < n) {
-        bitmap[base >> 5] = word;
-        word_rank[base >> 5] = c;
-    }
-#pragma unroll
-    for (int k = 0; k < GT_PER; k++) {
-        if (!(bits & (1u << k))) continue;
-        const uint64_t i = base + k;
-        const uint32_t sz = size[k];
+        if (!founder) continue;
+        const uint32_t c = __ldg(&word_rank[w]) + __popc(word & ((1u << lane) - 1u));
+        const uint32_t start = __ldg(&word_start[w]) + incl - size;
         tmpl[c] = (uint32_t)i;
-        fam_size[c] = sz;
+        fam_size[c] = size;
         fam_start[c] = start;
         cursor[c] = start;
-        is_sscs[c] = sz >= 2 ? ((cnt[k] & 1u) ? 1 : 3) : 0;      // bit 0: has a consensus row, bit 1: mode fields differ
+        is_sscs[c] = size >= 2 ? ((cnt & 1u) ? 1 : 3) : 0;       // bit 0: has a consensus row, bit 1: mode fields differ
         const uint4 b = __ldg(&fields[2 * i + 1]);
         fam_tlen[c] = (int32_t)b.z;
         fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
         fam_mapq[c] = (uint8_t)((b.w >> 16) & 0xFF);
         fam_rg[c] = (uint8_t)(b.w >> 24);
         partner[c] = -1;
-        const uint32_t bin = sz < hist_bins - 1 ? sz : hist_bins - 1;
+        const uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
         if (bin < 256) atomicAdd(&small_hist[bin], 1u);
         else atomicAdd(&hist[bin], 1ull);
-        c++;
-        start += sz;
     }
     __syncthreads();
-    const uint32_t v = small_hist[tid];
-    if (v) atomicAdd(&hist[tid], (unsigned long long)v);
-    if (v && tid >= 16 && tid < 128) atomicAdd(n_mid, v);          // families of 16..127 reads
+    const uint32_t v = small_hist[threadIdx.x];
+    if (v) atomicAdd(&hist[threadIdx.x], (unsigned long long)v);
+    if (v && threadIdx.x >= 16 && threadIdx.x < 128) atomicAdd(n_mid, v);          // families of 16..127 reads
 }
 
 // family number of the family founded by read `first` (its bit is set in the bitmap)
@@ -294,7 +253,7 @@ __device__ __forceinline__ uint32_t family_of_founder(const uint32_t *__restrict
     return __ldg(&word_rank[first >> 5]) + __popc(__ldg(&bitmap[first >> 5]) & ((1u << (first & 31)) - 1u));
 }
 
-__global__ void __launch_bounds__(GT_THREADS)
+__global__ void __launch_bounds__(GP_THREADS)
 tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t *__restrict__ final_rep,
                   const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ word_rank,
                   uint32_t *__restrict__ cursor, uint32_t *__restrict__ perm)
@@ -303,32 +262,33 @@ tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t 
     const int tid = threadIdx.x;
     const uint64_t base = (uint64_t)blockIdx.x * GT_TILE;
     const uint32_t here = (uint32_t)min((uint64_t)GT_TILE, n - base);
-    uint32_t lk[GT_PER];
+    uint32_t lk[GP_PER], fam[GP_PER];
 #pragma unroll
-    for (int k = 0; k < GT_PER; k++) {
-        const uint32_t li = k * GT_THREADS + tid;
+    for (int k = 0; k < GP_PER; k++) {
+        const uint32_t li = k * GP_THREADS + tid;
         members[li] = 0;
         lk[k] = li < here ? link[base + li] : 0u;
+        fam[k] = 0;
+        // the representatives' trips to the bitmap start before the members are counted
+        if (li < here && (lk[k] & LINK_REP)) fam[k] = family_of_founder(bitmap, word_rank, final_rep[base + li]);
     }
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < GT_PER; k++) {
-        const uint32_t li = k * GT_THREADS + tid;
+    for (int k = 0; k < GP_PER; k++) {
+        const uint32_t li = k * GP_THREADS + tid;
         if (li < here && !(lk[k] & LINK_REP)) atomicAdd(&members[lk[k] & (GT_TILE - 1)], 1u);
     }
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < GT_PER; k++) {
-        const uint32_t li = k * GT_THREADS + tid;
-        if (li < here && (lk[k] & LINK_REP)) {
-            const uint32_t c = family_of_founder(bitmap, word_rank, final_rep[base + li]);
-            members[li] = atomicAdd(&cursor[c], members[li] + 1u);     // room for the tile's whole group, one atomic
-        }
+    for (int k = 0; k < GP_PER; k++) {
+        const uint32_t li = k * GP_THREADS + tid;
+        if (li < here && (lk[k] & LINK_REP))
+            members[li] = atomicAdd(&cursor[fam[k]], members[li] + 1u);     // room for the tile's whole group, one atomic
     }
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < GT_PER; k++) {
-        const uint32_t li = k * GT_THREADS + tid;
+    for (int k = 0; k < GP_PER; k++) {
+        const uint32_t li = k * GP_THREADS + tid;
         if (li >= here) continue;
         const uint32_t at = (lk[k] & LINK_REP) ? members[li] : members[lk[k] & (GT_TILE - 1)] + (lk[k] >> LINK_RANK_SHIFT);
         perm[at] = (uint32_t)(base + li);

@@ -4,6 +4,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "scan.cuh"
+
 namespace ccgpu {
 
 constexpr uint32_t NO_ID = 0xFFFFFFFFu;
@@ -360,6 +362,150 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
     }
     __syncthreads();
     if (threadIdx.x < 16 && s_st[threadIdx.x]) atomicAdd(&stats[threadIdx.x], (unsigned long long)s_st[threadIdx.x]);
+}
+
+// classify_kernel and the three compactions behind it in one chained scan: every family decides its
+// output classes, the running counts of the three classes travel from tile to tile (scan.cuh:
+// lookback_pairs), and the lists (row -> family) and maps (family -> row) are written on the spot.
+// dcssc_row holds the rank among the second-pass rows, or ~(row of the shared DCS) / -1: the rows of the
+// second pass follow the n_dcs shared ones, and n_dcs is only known when the scan ends (dcssc_row_finish).
+constexpr int CLS_THREADS = 256, CLS_ITEMS = 8, CLS_TILE = CLS_THREADS * CLS_ITEMS;
+
+__global__ void __launch_bounds__(CLS_THREADS)
+classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict__ partner, uint32_t n_fam, int scorrect,
+                     unsigned long long *status, uint32_t *ticket,
+                     uint32_t *__restrict__ dcs_list, uint32_t *__restrict__ corr_list, uint32_t *__restrict__ dcssc_list,
+                     int32_t *__restrict__ dcs_row, int32_t *__restrict__ corr_row, int32_t *__restrict__ dcssc_row,
+                     unsigned long long *__restrict__ stats, uint32_t *__restrict__ one_sided,
+                     uint32_t *__restrict__ n_dcs, uint32_t *__restrict__ n_corr, uint32_t *__restrict__ n_extra)
+{
+    __shared__ unsigned int s_st[16];
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp[CLS_THREADS / 32][3];
+    __shared__ uint32_t s_excl[4];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 16) s_st[tid] = 0;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t base = tile * CLS_TILE + tid * CLS_ITEMS;
+    uint32_t f_dcs = 0, f_corr = 0, f_x = 0;          // bit k: family base + k is in the class
+    uint32_t mine[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t size[CLS_ITEMS];
+    int32_t par[CLS_ITEMS];
+    if (base + CLS_ITEMS <= n_fam) {
+        const uint4 a = *reinterpret_cast<const uint4 *>(fam_size + base), b = *reinterpret_cast<const uint4 *>(fam_size + base + 4);
+        const int4 c = *reinterpret_cast<const int4 *>(partner + base), d = *reinterpret_cast<const int4 *>(partner + base + 4);
+        size[0] = a.x; size[1] = a.y; size[2] = a.z; size[3] = a.w; size[4] = b.x; size[5] = b.y; size[6] = b.z; size[7] = b.w;
+        par[0] = c.x; par[1] = c.y; par[2] = c.z; par[3] = c.w; par[4] = d.x; par[5] = d.y; par[6] = d.z; par[7] = d.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < CLS_ITEMS; k++) {
+            size[k] = base + k < n_fam ? fam_size[base + k] : 0u;
+            par[k] = base + k < n_fam ? partner[base + k] : -1;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < CLS_ITEMS; k++) {
+        const uint32_t c = base + k;
+        if (c >= n_fam) continue;
+        const bool big = size[k] >= 2;
+        const int32_t p = par[k];
+        // a partner that has another partner (undotted barcode of odd length): which strand leads, and
+        // whether the reference survives, depends on file order (DCS_maker.py:231-247) - outside the domain
+        if (p >= 0 && __ldg(&partner[p]) != (int32_t)c) atomicAdd(one_sided, 1u);
+        const bool p_big = p >= 0 && __ldg(&fam_size[p]) >= 2;
+        const bool dcs = big && p_big && c < (uint32_t)p;
+        const bool corr = scorrect && !big && p >= 0;
+        const bool dcssc = scorrect && p >= 0 && leads_after_sc(c, (uint32_t)p, big, p_big);
+        // a pair of two SSCS gives the same record before and after the rescue: its row is shared,
+        // only pairs that involve a corrected singleton get a row of their own in the second pass
+        f_dcs |= (uint32_t)dcs << k; f_corr |= (uint32_t)corr << k; f_x |= (uint32_t)(dcssc && !dcs) << k;
+        mine[big ? 0 : 1]++;
+        mine[2] += dcs;
+        mine[3] += big && !p_big;
+        if (scorrect) {
+            mine[4] += !big && p_big;
+            mine[5] += !big && p >= 0 && !p_big;
+            mine[6] += !big && p < 0;
+            mine[7] += dcssc;
+            mine[8] += big && p < 0;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const uint32_t v = __reduce_add_sync(0xffffffffu, mine[k]);
+        if (lane == 0 && v) atomicAdd(&s_st[k], v);
+    }
+    // block-wide exclusive prefixes of the three class counts
+    const uint32_t own[3] = {(uint32_t)__popc(f_dcs), (uint32_t)__popc(f_corr), (uint32_t)__popc(f_x)};
+    uint32_t inc[3] = {own[0], own[1], own[2]};
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+        for (int v = 0; v < 3; v++) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc[v], d);
+            if (lane >= d) inc[v] += t;
+        }
+    }
+    if (lane == 31) { s_warp[warp][0] = inc[0]; s_warp[warp][1] = inc[1]; s_warp[warp][2] = inc[2]; }
+    __syncthreads();
+    uint32_t off[3] = {0, 0, 0}, tot[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < CLS_THREADS / 32; k++) {
+#pragma unroll
+        for (int v = 0; v < 3; v++) {
+            if (k < warp) off[v] += s_warp[k][v];
+            tot[v] += s_warp[k][v];
+        }
+    }
+    if (warp == 0) {
+        uint32_t excl[4];
+        lookback_pairs<2>(status, tile, tot, excl, lane);
+        if (lane == 0) {
+            s_excl[0] = excl[0]; s_excl[1] = excl[1]; s_excl[2] = excl[2];
+            if (tile == gridDim.x - 1) { *n_dcs = excl[0] + tot[0]; *n_corr = excl[1] + tot[1]; *n_extra = excl[2] + tot[2]; }
+        }
+    }
+    __syncthreads();
+    uint32_t r_dcs = s_excl[0] + off[0] + inc[0] - own[0];
+    uint32_t r_corr = s_excl[1] + off[1] + inc[1] - own[1];
+    uint32_t r_x = s_excl[2] + off[2] + inc[2] - own[2];
+    int32_t o_dcs[CLS_ITEMS], o_corr[CLS_ITEMS], o_x[CLS_ITEMS];
+#pragma unroll
+    for (int k = 0; k < CLS_ITEMS; k++) {
+        const uint32_t c = base + k;
+        o_dcs[k] = -1; o_corr[k] = -1; o_x[k] = -1;
+        if ((f_dcs >> k) & 1u) { dcs_list[r_dcs] = c; o_dcs[k] = (int32_t)r_dcs++; }
+        if ((f_corr >> k) & 1u) { corr_list[r_corr] = c; o_corr[k] = (int32_t)r_corr++; }
+        if ((f_x >> k) & 1u) { dcssc_list[r_x] = c; o_x[k] = (int32_t)r_x++; }
+        else if (scorrect && o_dcs[k] >= 0) o_x[k] = ~o_dcs[k];            // <= -2: shares DCS row ~value
+    }
+    if (base + CLS_ITEMS <= n_fam) {
+        *reinterpret_cast<int4 *>(dcs_row + base) = make_int4(o_dcs[0], o_dcs[1], o_dcs[2], o_dcs[3]);
+        *reinterpret_cast<int4 *>(dcs_row + base + 4) = make_int4(o_dcs[4], o_dcs[5], o_dcs[6], o_dcs[7]);
+        *reinterpret_cast<int4 *>(corr_row + base) = make_int4(o_corr[0], o_corr[1], o_corr[2], o_corr[3]);
+        *reinterpret_cast<int4 *>(corr_row + base + 4) = make_int4(o_corr[4], o_corr[5], o_corr[6], o_corr[7]);
+        *reinterpret_cast<int4 *>(dcssc_row + base) = make_int4(o_x[0], o_x[1], o_x[2], o_x[3]);
+        *reinterpret_cast<int4 *>(dcssc_row + base + 4) = make_int4(o_x[4], o_x[5], o_x[6], o_x[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < CLS_ITEMS; k++)
+            if (base + k < n_fam) { dcs_row[base + k] = o_dcs[k]; corr_row[base + k] = o_corr[k]; dcssc_row[base + k] = o_x[k]; }
+    }
+    __syncthreads();
+    if (tid < 16 && s_st[tid]) atomicAdd(&stats[tid], (unsigned long long)s_st[tid]);
+}
+
+// dcssc_row as the C ABI describes it: rows of the second pass follow the n_dcs shared rows
+__global__ void __launch_bounds__(256)
+dcssc_row_finish_kernel(int32_t *__restrict__ dcssc_row, uint32_t n_fam, uint32_t n_dcs)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_fam) return;
+    const int32_t v = dcssc_row[c];
+    if (v >= 0) dcssc_row[c] = (int32_t)n_dcs + v;
+    else if (v <= -2) dcssc_row[c] = ~v;
 }
 
 // ---- K4 + K5: SSCS vote and family mode fields ------------------------------------------------

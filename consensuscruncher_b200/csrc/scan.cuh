@@ -165,4 +165,46 @@ scan_kernel(const InT *in, uint32_t *out, uint32_t *carry,
 
 inline uint64_t scan_tiles(uint64_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
 
+// ---- chained scan of several sums at once -------------------------------------------------------
+// A status word carries a state (2 bits: 0 nothing yet, 1 this tile's own sums, 2 sums of every tile up to
+// and including this one) and two 31-bit sums; a tile owns W consecutive words (status[tile * W + w]), so
+// one kernel can carry 2 * W running sums.  Each word is looked back on its own: predecessors publish
+// their words one after the other.  Called by the first warp of the CTA; tot[] / excl[] hold 2 * W sums.
+__device__ __forceinline__ unsigned long long pair_pack(uint32_t state, uint32_t a, uint32_t b)
+{
+    return ((unsigned long long)state << 62) | ((unsigned long long)a << 31) | b;
+}
+
+template <int W>
+__device__ __forceinline__ void lookback_pairs(unsigned long long *status, uint32_t tile, const uint32_t *tot, uint32_t *excl,
+                                               int lane)
+{
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+        uint32_t ea = 0, eb = 0;
+        if (tile != 0) {
+            if (lane == 0) st_status(&status[(uint64_t)tile * W + w], pair_pack(1, tot[2 * w], tot[2 * w + 1]));
+            for (int64_t p = (int64_t)tile - 1;; p -= 32) {
+                const int64_t idx = p - lane;
+                unsigned long long s = idx >= 0 ? ld_status(&status[idx * W + w]) : pair_pack(2, 0, 0);   // before tile 0: nothing
+                while (__any_sync(0xffffffffu, (s >> 62) == 0))
+                    if ((s >> 62) == 0) s = ld_status(&status[idx * W + w]);
+                const uint32_t done = __ballot_sync(0xffffffffu, (s >> 62) == 2);
+                const int first = done ? __ffs(done) - 1 : 31;            // nearest tile that already knows its prefix
+                uint32_t va = lane <= first ? (uint32_t)(s >> 31) & 0x7FFFFFFFu : 0u;
+                uint32_t vb = lane <= first ? (uint32_t)s & 0x7FFFFFFFu : 0u;
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) {
+                    va += __shfl_xor_sync(0xffffffffu, va, d);
+                    vb += __shfl_xor_sync(0xffffffffu, vb, d);
+                }
+                ea += va; eb += vb;
+                if (done) break;
+            }
+        }
+        if (lane == 0) st_status(&status[(uint64_t)tile * W + w], pair_pack(2, ea + tot[2 * w], eb + tot[2 * w + 1]));
+        excl[2 * w] = ea; excl[2 * w + 1] = eb;
+    }
+}
+
 }  // namespace ccgpu

@@ -2,7 +2,7 @@
 # Short device-resident bench of every library in variants/ (and the in-tree one): phase table per variant.
 for lib in consensuscruncher_b200/libccgpu.so variants/*.so; do
   [ -f "$lib" ] || continue
-  CCGPU_LIB=$PWD/$lib python bench.py --steps 10 --no-e2e --no-cpu-baseline 2>gpurun_out/var.err | tail -1 > gpurun_out/var.json
+  CCGPU_LIB=$PWD/$lib python bench.py --steps 10 --no-e2e --no-cpu-baseline --sharded none --sweep none 2>gpurun_out/var.err | tail -1 > gpurun_out/var.json
   python - "$lib" <<'PY'
 import json, sys
 try:
