@@ -99,7 +99,7 @@ struct cc_ctx {
     const uint32_t *dup_bc = nullptr;
     uint64_t n = 0;
     uint32_t lpad = 0, stride = 0, n_bc = 0;
-    DevBuf in_fields, in_payload, in_dup, in_q4;
+    DevBuf in_fields, in_payload, in_dup, in_q4, in_pairs;
     // grouping scratch
     DevBuf key_a, key_b, val_a, val_b, head, radix_counts, scan_status, counters, hist, stats;
     uint32_t *perm = nullptr, *sorted_keys = nullptr, *spare_keys = nullptr, *spare_vals = nullptr;
@@ -122,8 +122,9 @@ struct cc_ctx {
     DevBuf gtable;                              // hash grouping (group_hash.cuh, group_tile.cuh)
     DevBuf cursor;                              // tile grouping: next free place of every family's segment
     DevBuf word_reads, word_start;              // ... per bitmap word: reads in the families founded there, and their prefix
+    DevBuf gt_state;                            // ... device-side scalars + the contig stretch table (group_tile.cuh)
     enum GroupMode { GROUP_TILE, GROUP_HASH, GROUP_SORT };
-    GroupMode group_mode = GROUP_HASH;
+    GroupMode group_mode = GROUP_TILE;
     bool tile_join = false;                     // the loaded batch was grouped by the tile path (bitmap + word ranks name families)
     uint64_t gtable_mask = 0;                   // non-zero while gtable describes the loaded batch
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
@@ -396,47 +397,66 @@ int do_group_hash(cc_ctx *ctx)
 }
 
 // Grouping tile by tile (group_tile.cuh): the default.  Leaves what the other two paths leave.  Family-level
-// arrays are written by the same kernel that counts the families, so they are sized by their bound, n.
+// arrays written before the family count reaches the host are sized by their bound, n.
 int do_group_tile(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
     TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
-    uint32_t *link = ptr<uint32_t>(ctx->key_a), *final_rep = ptr<uint32_t>(ctx->key_b);
+    uint32_t *link = ptr<uint32_t>(ctx->key_a), *aux = ptr<uint32_t>(ctx->key_b);
+    uint32_t *stash = ptr<uint32_t>(ctx->val_b);            // group / family counter words; dead once the family records are written
+    uint32_t *edge_list = ptr<uint32_t>(ctx->val_a);        // dead before tile_place writes `perm` there
     uint64_t slots = 1024;
-    while (slots < n + n / 4) slots <<= 1;                  // load factor <= 0.8 even if every read is a family
+    while (slots < n + n / 4) slots <<= 1;                  // the most the device may use: every read a listed family, load <= 0.8
     TRY(ensure(ctx, ctx->gtable, slots * sizeof(GroupSlot)));
     GroupSlot *table = ptr<GroupSlot>(ctx->gtable);
     const uint64_t words = (n + 31) / 32, tiles = gt_tiles(n);
     TRY(ensure(ctx, ctx->bitmap, words * 4)); TRY(ensure(ctx, ctx->word_rank, words * 4));
+    TRY(ensure(ctx, ctx->word_reads, words * 4)); TRY(ensure(ctx, ctx->word_start, words * 4));
     TRY(ensure(ctx, ctx->tmpl, n * 4)); TRY(ensure(ctx, ctx->fam_start, n * 4)); TRY(ensure(ctx, ctx->fam_size, n * 4));
     TRY(ensure(ctx, ctx->cursor, n * 4)); TRY(ensure(ctx, ctx->is_sscs, n + 4)); TRY(ensure(ctx, ctx->fam_mapq, n));
     TRY(ensure(ctx, ctx->fam_rg, n)); TRY(ensure(ctx, ctx->fam_flag, n * 2)); TRY(ensure(ctx, ctx->fam_tlen, n * 4));
     TRY(ensure(ctx, ctx->partner, n * 4));
+    TRY(ensure(ctx, ctx->sscs_list, (n / 2 + 1) * 4)); TRY(ensure(ctx, ctx->sscs_row, n * 4));
+    const uint64_t ws_tiles = (words + WS_TILE - 1) / WS_TILE;
+    TRY(ensure(ctx, ctx->scan_status, (2 * ws_tiles + 2) * sizeof(unsigned long long)));
+    TRY(ensure(ctx, ctx->gt_state, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t)));
+    uint32_t *gtc = ptr<uint32_t>(ctx->gt_state), *stretch = gtc + GTC_COUNT;
 
     TRY(phase_begin(ctx, CC_PH_HASH));
-    CK(cudaMemsetAsync(table, 0xFF, slots * sizeof(GroupSlot), ctx->stream));
-    LAUNCH(tile_insert_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, table, slots - 1, link);
+    CK(cudaMemsetAsync(gtc, 0, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t), ctx->stream));
+    if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
+    LAUNCH(tile_local_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, 0, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM, gtc, stretch,
+           link, aux, stash, edge_list, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_reads), ptr<uint32_t>(ctx->word_start));
+    // input out of order (flag raised on the device): the same tiles again, every family through the table
+    LAUNCH(tile_redo_kernel, 1, 1, gtc);
+    LAUNCH(tile_local_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, 1, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM, gtc, stretch,
+           link, aux, stash, edge_list, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_reads), ptr<uint32_t>(ctx->word_start));
+    LAUNCH(table_prepare_kernel, 148 * 4, 256, gtc, table, slots);
+    LAUNCH(edge_insert_kernel, 148 * 8, 256, ctx->fields, edge_list, gtc, table, stash, aux);
     TRY(phase_end(ctx, CC_PH_HASH));
 
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
-    uint32_t *founder_cnt = ptr<uint32_t>(ctx->val_b);      // dead once the family records are written
-    TRY(ensure(ctx, ctx->word_reads, words * 4)); TRY(ensure(ctx, ctx->word_start, words * 4));
-    LAUNCH(tile_mark_kernel, blocks_for(n, 256), 256, n, table, link, final_rep, founder_cnt, ptr<uint32_t>(ctx->bitmap),
-           ptr<uint32_t>(ctx->word_reads));
-    TRY(scan_popcounts(ctx, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), words, ctr + CT_NFAM));
-    TRY(scan_exclusive(ctx, ptr<uint32_t>(ctx->word_reads), ptr<uint32_t>(ctx->word_start), words));
-    LAUNCH(tile_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, n, founder_cnt,
-           ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->word_start),
+    // word_reads -> segment starts, word_start (until here: SSCS families per word) -> consensus rows, both in place
+    uint32_t *word_sscs = ptr<uint32_t>(ctx->word_start);
+    LAUNCH(edge_mark_kernel, 148 * 8, 256, edge_list, gtc, table, aux, stash, ptr<uint32_t>(ctx->bitmap),
+           ptr<uint32_t>(ctx->word_reads), word_sscs);
+    CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * ws_tiles + 2) * sizeof(unsigned long long), ctx->stream));
+    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    LAUNCH(word_scan_kernel, (unsigned)ws_tiles, WS_THREADS, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
+           ptr<uint32_t>(ctx->word_reads), word_sscs, words, ptr<unsigned long long>(ctx->scan_status),
+           ctr + CT_TICKET0 + ctx->next_ticket++, ctr + CT_NFAM, ctr + CT_NSSCS);
+    LAUNCH(tile_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 16), 256, ctx->fields, n, stash,
+           ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->word_reads),
            ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->cursor),
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
            ptr<uint8_t>(ctx->fam_rg), ptr<int32_t>(ctx->partner), ptr<unsigned long long>(ctx->hist), (uint32_t)CC_HIST_BINS,
-           ctr + CT_NMID);
+           ctr + CT_NMID, word_sscs, ptr<uint32_t>(ctx->sscs_list), ptr<int32_t>(ctx->sscs_row));
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family, materialised when somebody fetches it
     ctx->sorted_keys = ctx->spare_keys = nullptr;
-    LAUNCH(tile_place_kernel, (unsigned)tiles, GP_THREADS, n, link, final_rep, ptr<uint32_t>(ctx->bitmap),
+    LAUNCH(tile_place_kernel, (unsigned)tiles, GP_THREADS, n, link, aux, ptr<uint32_t>(ctx->bitmap),
            ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->cursor), ctx->perm);
     TRY(read_counters(ctx));
     const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
@@ -445,9 +465,6 @@ int do_group_tile(cc_ctx *ctx)
     ctx->tile_join = true;
     LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
            ctr + CT_FAULTS);
-    TRY(ensure(ctx, ctx->sscs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
-    TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS,
-                      ptr<int32_t>(ctx->sscs_row)));
     TRY(phase_end(ctx, CC_PH_SEGMENT));
     ctx->grouped = true;
     return CC_OK;
@@ -546,15 +563,16 @@ int do_join_index(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->dcssc_list, (size_t)nf * 4));
     if (nf == 0) return CC_OK;
     TRY(phase_begin(ctx, CC_PH_JOIN));
-    CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
-    if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
     if (ctx->gtable_mask && ctx->tile_join) {
+        // (the barcode swap's symmetry was established before the tiles were grouped)
         LAUNCH(tile_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,
-               ptr<GroupSlot>(ctx->gtable), ctx->gtable_mask, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
-               ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
+               ptr<GroupSlot>(ctx->gtable), ptr<uint32_t>(ctx->gt_state), ptr<uint32_t>(ctx->key_a), ptr<uint32_t>(ctx->key_b),
+               ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
         TRY(phase_end(ctx, CC_PH_JOIN));
         return do_classify(ctx);
     }
+    CK(cudaMemsetAsync(ctr + CT_ASYM, 0, 4, ctx->stream));
+    if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
     if (ctx->gtable_mask) {
         // the grouping table already maps every family tuple to its first read
         LAUNCH(group_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,
@@ -815,7 +833,7 @@ cc_ctx *cc_create(int device, const cc_params *params)
     }
     cc_ctx *ctx = new cc_ctx();
     if (const char *g = getenv("CCGPU_GROUP"))         // "sort": radix-sort grouping, "hash": one table trip per read
-        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "tile") ? cc_ctx::GROUP_TILE : cc_ctx::GROUP_HASH;
+        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "hash") ? cc_ctx::GROUP_HASH : cc_ctx::GROUP_TILE;
     ctx->device = device;
     if (params) ctx->params = *params;
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -832,7 +850,7 @@ void cc_destroy(cc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
+    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->in_pairs, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
                      &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->stats,
                      &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
                      &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
@@ -840,7 +858,7 @@ void cc_destroy(cc_ctx *ctx)
                      &ctx->dcs_row, &ctx->corr_row, &ctx->dcssc_row, &ctx->sscs_rows, &ctx->corr_rows, &ctx->dcs_rows,
                      &ctx->dcs_mapq, &ctx->dcs_flag, &ctx->dcs_tlen, &ctx->dcs_rg, &ctx->tmp_a, &ctx->tmp_b, &ctx->tmp_c,
                      &ctx->vstart, &ctx->vsize, &ctx->big_list, &ctx->mid_list, &ctx->thr_table, &ctx->bitmap, &ctx->word_rank,
-                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable, &ctx->cursor, &ctx->word_reads, &ctx->word_start};
+                     &ctx->first_read, &ctx->cs_in, &ctx->cs_k0, &ctx->cs_k1, &ctx->cs_v0, &ctx->cs_v1, &ctx->gtable, &ctx->cursor, &ctx->word_reads, &ctx->word_start, &ctx->gt_state};
     for (DevBuf *b : all) release(ctx, *b);
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
@@ -919,6 +937,50 @@ int cc_load_reads_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payloa
         memcpy(table.q, qual_table, 16);
         LAUNCH(expand_q4_kernel, blocks_for(n * (lpad / 16), 256), 256, ptr<uint8_t>(ctx->in_q4), stride4,
                ptr<uint8_t>(ctx->in_payload), stride, lpad, n, table);
+    }
+    if (n_bc) CK(cudaMemcpyAsync(ctx->in_dup.p, dup_bc, (size_t)n_bc * 4, cudaMemcpyHostToDevice, ctx->stream));
+    TRY(phase_end(ctx, CC_PH_H2D));
+    ctx->fields = ptr<uint4>(ctx->in_fields);
+    ctx->payload = ptr<uint8_t>(ctx->in_payload);
+    ctx->dup_bc = ptr<uint32_t>(ctx->in_dup);
+    ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
+    ctx->have_reads = true;
+    ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
+    return CC_OK;
+}
+
+int cc_load_reads_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes, uint64_t n, uint32_t lpad,
+                          uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
+                          const uint32_t *dup_bc, uint32_t n_bc)
+{
+    if (!ctx || !qual_table || !base_table) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (qbits < 1 || qbits > 4) return fail(ctx, CC_ERR_ARG, "cc_load_reads_compact: qbits must be 1..4");
+    if (lpad == 0 || lpad % 32 || stride_c % 16 || stride_c < lpad / 4 + lpad * qbits / 8)
+        return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride_c % 16 == 0, stride_c >= lpad/4 + lpad*qbits/8");
+    const uint32_t stride = (lpad / 2 + lpad + 63) / 64 * 64;           // the standard row the kernels read
+    TRY(check_geometry(ctx, pairs, planes, n, lpad, stride));
+    TRY(ensure(ctx, ctx->in_fields, n * sizeof(cc_fields)));
+    TRY(ensure(ctx, ctx->in_pairs, (n / 2) * sizeof(cc_pair)));
+    TRY(ensure(ctx, ctx->in_q4, n * (size_t)stride_c));
+    TRY(ensure(ctx, ctx->in_payload, n * (size_t)stride));
+    TRY(ensure(ctx, ctx->in_dup, (size_t)n_bc * 4));
+    TRY(phase_begin(ctx, CC_PH_H2D));
+    if (n) {
+        CK(cudaMemcpyAsync(ctx->in_pairs.p, pairs, (n / 2) * sizeof(cc_pair), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->in_q4.p, planes, n * (size_t)stride_c, cudaMemcpyHostToDevice, ctx->stream));
+        LAUNCH(expand_pairs_kernel, blocks_for(n / 2, 256), 256, ptr<uint2>(ctx->in_pairs), n / 2, ptr<uint4>(ctx->in_fields));
+        CodeTable table;
+        memcpy(table.qual, qual_table, 16);
+        memcpy(table.base, base_table, 16);
+        const unsigned grid = blocks_for(n * (lpad / 16), 256);
+        uint8_t *in = ptr<uint8_t>(ctx->in_q4), *out = ptr<uint8_t>(ctx->in_payload);
+        switch (qbits) {
+        case 1: LAUNCH(expand_planes_kernel<1>, grid, 256, in, stride_c, out, stride, lpad, n, table); break;
+        case 2: LAUNCH(expand_planes_kernel<2>, grid, 256, in, stride_c, out, stride, lpad, n, table); break;
+        case 3: LAUNCH(expand_planes_kernel<3>, grid, 256, in, stride_c, out, stride, lpad, n, table); break;
+        default: LAUNCH(expand_planes_kernel<4>, grid, 256, in, stride_c, out, stride, lpad, n, table); break;
+        }
     }
     if (n_bc) CK(cudaMemcpyAsync(ctx->in_dup.p, dup_bc, (size_t)n_bc * 4, cudaMemcpyHostToDevice, ctx->stream));
     TRY(phase_end(ctx, CC_PH_H2D));
@@ -1023,6 +1085,14 @@ int cc_run_host_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload4
     return cc_run(ctx);
 }
 
+int cc_run_host_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes, uint64_t n, uint32_t lpad,
+                        uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
+                        const uint32_t *dup_bc, uint32_t n_bc)
+{
+    TRY(cc_load_reads_compact(ctx, pairs, planes, n, lpad, stride_c, qbits, qual_table, base_table, dup_bc, n_bc));
+    return cc_run(ctx);
+}
+
 int cc_counts(cc_ctx *ctx, uint64_t counts[8])
 {
     if (!ctx || !counts) return CC_ERR_ARG;
@@ -1114,6 +1184,24 @@ int cc_fetch(cc_ctx *ctx, int what, void *host_dst, uint64_t bytes)
     TRY(materialise(ctx, what));
     CK(cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return CC_OK;
+}
+
+int cc_fetch_many(cc_ctx *ctx, uint32_t count, const int *what, void *const *host_dst, const uint64_t *bytes)
+{
+    if (!ctx || (count && (!what || !host_dst || !bytes))) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    for (uint32_t k = 0; k < count; k++) {
+        uint64_t have = 0;
+        const void *p = array_ptr(ctx, what[k], &have);
+        if (bytes[k] != have) return fail(ctx, CC_ERR_ARG, "cc_fetch_many: size mismatch (use cc_array_bytes)");
+        if (have == 0) continue;
+        if (!p) return fail(ctx, CC_ERR_ARG, "cc_fetch_many: array not produced yet");
+        if (!host_dst[k]) return fail(ctx, CC_ERR_ARG, "cc_fetch_many: NULL destination");
+        TRY(materialise(ctx, what[k]));
+        CK(cudaMemcpyAsync(host_dst[k], p, have, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));                  // one wait for all the copies
     return CC_OK;
 }
 

@@ -367,7 +367,7 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
 // classify_kernel and the three compactions behind it in one chained scan: every family decides its
 // output classes, the running counts of the three classes travel from tile to tile (scan.cuh:
 // lookback_pairs), and the lists (row -> family) and maps (family -> row) are written on the spot.
-// dcssc_row holds the rank among the second-pass rows, or ~(row of the shared DCS) / -1: the rows of the
+// dcssc_row holds the rank among the second-pass rows, or -2 - (row of the shared DCS) / -1: the rows of the
 // second pass follow the n_dcs shared ones, and n_dcs is only known when the scan ends (dcssc_row_finish).
 constexpr int CLS_THREADS = 256, CLS_ITEMS = 8, CLS_TILE = CLS_THREADS * CLS_ITEMS;
 
@@ -479,7 +479,7 @@ classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__res
         if ((f_dcs >> k) & 1u) { dcs_list[r_dcs] = c; o_dcs[k] = (int32_t)r_dcs++; }
         if ((f_corr >> k) & 1u) { corr_list[r_corr] = c; o_corr[k] = (int32_t)r_corr++; }
         if ((f_x >> k) & 1u) { dcssc_list[r_x] = c; o_x[k] = (int32_t)r_x++; }
-        else if (scorrect && o_dcs[k] >= 0) o_x[k] = ~o_dcs[k];            // <= -2: shares DCS row ~value
+        else if (scorrect && o_dcs[k] >= 0) o_x[k] = -2 - o_dcs[k];        // <= -2: shares DCS row -2 - value
     }
     if (base + CLS_ITEMS <= n_fam) {
         *reinterpret_cast<int4 *>(dcs_row + base) = make_int4(o_dcs[0], o_dcs[1], o_dcs[2], o_dcs[3]);
@@ -505,7 +505,7 @@ dcssc_row_finish_kernel(int32_t *__restrict__ dcssc_row, uint32_t n_fam, uint32_
     if (c >= n_fam) return;
     const int32_t v = dcssc_row[c];
     if (v >= 0) dcssc_row[c] = (int32_t)n_dcs + v;
-    else if (v <= -2) dcssc_row[c] = ~v;
+    else if (v <= -2) dcssc_row[c] = -2 - v;
 }
 
 // ---- K4 + K5: SSCS vote and family mode fields ------------------------------------------------
@@ -782,6 +782,73 @@ expand_q4_kernel(const uint8_t *__restrict__ in, uint32_t stride_in, uint8_t *__
     }
     *reinterpret_cast<uint2 *>(dst + lane * 8) = bases;
     *reinterpret_cast<uint4 *>(dst + half + lane * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    for (uint32_t x = half + lpad + lane * 4; x < stride_out; x += lanes * 4) *reinterpret_cast<uint32_t *>(dst + x) = 0;
+}
+
+// ---- compact upload (cc_load_reads_compact) ---------------------------------------------------------
+// Pair records: the two mates of a pair share barcode and cigar pair and mirror each other's coordinates,
+// so 40 bytes describe both reads' 32-byte field records.
+struct PairRec {
+    uint32_t bc, cig;
+    int32_t tid, pos, mtid, mpos;      // of the first-seen mate
+    int32_t tlen1, tlen2;
+    uint32_t flags;                    // flag1 | flag2 << 16
+    uint32_t meta;                     // mapq1 | mapq2 << 8 | rg1 << 16 | rg2 << 24
+};
+static_assert(sizeof(PairRec) == 40, "cc_pair is 40 bytes");
+
+__global__ void __launch_bounds__(256)
+expand_pairs_kernel(const uint2 *__restrict__ pairs, uint64_t n_pairs, uint4 *__restrict__ fields)
+{
+    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_pairs) return;
+    const uint2 a = pairs[5 * k], b = pairs[5 * k + 1], c = pairs[5 * k + 2], d = pairs[5 * k + 3], e = pairs[5 * k + 4];
+    // a = (bc, cig)  b = (tid, pos)  c = (mtid, mpos)  d = (tlen1, tlen2)  e = (flags, meta)
+    const uint32_t m1 = (e.x & 0xFFFFu) | ((e.y & 0xFFu) << 16) | (((e.y >> 16) & 0xFFu) << 24);
+    const uint32_t m2 = (e.x >> 16) | (((e.y >> 8) & 0xFFu) << 16) | ((e.y >> 24) << 24);
+    fields[4 * k] = make_uint4(a.x, a.y, b.x, b.y);
+    fields[4 * k + 1] = make_uint4(c.x, c.y, d.x, m1);
+    fields[4 * k + 2] = make_uint4(a.x, a.y, c.x, c.y);
+    fields[4 * k + 3] = make_uint4(b.x, b.y, d.y, m2);
+}
+
+// Rows in bit planes: lpad/4 bytes of 2-bit bases (A,C,G,T = 0..3, position p at bits 2p..2p+1) followed by
+// lpad * QBITS / 8 bytes of QBITS-bit codes (position p at bit p * QBITS, little endian).  A code names
+// a quality and, where base_of[code] != 0xFF, the literal 4-bit base code of the position (N, a pad, an
+// IUPAC letter) instead of the 2-bit base.  One thread expands 16 positions into the standard row.
+struct CodeTable { uint8_t qual[16]; uint8_t base[16]; };
+
+template <int QBITS>
+__global__ void __launch_bounds__(256)
+expand_planes_kernel(const uint8_t *__restrict__ in, uint32_t stride_in, uint8_t *__restrict__ out, uint32_t stride_out,
+                     uint32_t lpad, uint64_t n, CodeTable table)
+{
+    __shared__ uint8_t s_qual[16], s_base[16];
+    if (threadIdx.x < 16) { s_qual[threadIdx.x] = table.qual[threadIdx.x]; s_base[threadIdx.x] = table.base[threadIdx.x]; }
+    __syncthreads();
+    const uint32_t lanes = lpad / 16, half = lpad / 2;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t row = t / lanes;
+    const uint32_t lane = (uint32_t)(t % lanes);
+    if (row >= n) return;
+    const uint8_t *src = in + row * stride_in;
+    uint8_t *dst = out + row * stride_out;
+    const uint32_t b2 = *reinterpret_cast<const uint32_t *>(src + lane * 4);              // 16 bases
+    const uint16_t *qsrc = reinterpret_cast<const uint16_t *>(src + lpad / 4 + lane * 2 * QBITS);
+    unsigned long long codes = 0;                                                          // 16 codes, QBITS bits each
+#pragma unroll
+    for (int k = 0; k < QBITS; k++) codes |= (unsigned long long)qsrc[k] << (16 * k);
+    uint32_t seq[2] = {0, 0}, q[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int p = 0; p < 16; p++) {
+        const uint32_t code = (uint32_t)(codes >> (p * QBITS)) & ((1u << QBITS) - 1u);
+        const uint32_t lit = s_base[code];
+        const uint32_t base = lit != 0xFFu ? lit : (1u << ((b2 >> (2 * p)) & 3u));
+        seq[p >> 3] |= base << (4 * (p & 7));                       // even position in the low nibble
+        q[p >> 2] |= (uint32_t)s_qual[code] << (8 * (p & 3));
+    }
+    *reinterpret_cast<uint2 *>(dst + lane * 8) = make_uint2(seq[0], seq[1]);
+    *reinterpret_cast<uint4 *>(dst + half + lane * 16) = make_uint4(q[0], q[1], q[2], q[3]);
     for (uint32_t x = half + lpad + lane * 4; x < stride_out; x += lanes * 4) *reinterpret_cast<uint32_t *>(dst + x) = 0;
 }
 

@@ -37,7 +37,7 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
            "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4",
-           "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
+           "cc_load_reads_compact", "cc_run_host_compact", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
 COMM_ID_BYTES = 128
 
 
@@ -100,6 +100,9 @@ def load_library(path=None):
     L.cc_kernel_launches.argtypes = [vp]
     L.cc_device_bytes.restype = u64
     L.cc_device_bytes.argtypes = [vp]
+    L.cc_load_reads_compact.argtypes = [vp, vp, vp, u64, u32, u32, u32, vp, vp, vp, u32]
+    L.cc_run_host_compact.argtypes = [vp, vp, vp, u64, u32, u32, u32, vp, vp, vp, u32]
+    L.cc_fetch_many.argtypes = [vp, u32, vp, vp, vp]
     L.cc_comm_unique_id.argtypes = [vp]
     L.cc_comm_init.argtypes = [vp, vp, i32, i32]
     L.cc_stats_allreduce.argtypes = [vp]
@@ -190,6 +193,21 @@ class GpuConsensus:
         self._check(self.lib.cc_load_reads_q4(self.ctx, fields.ctypes.data, payload4.ctypes.data, packed.n, packed.lpad,
                                               payload4.shape[1], table.ctypes.data, dup.ctypes.data, len(dup)))
 
+    def load_compact(self, packed: PackedReads, compact=None):
+        """Pair records + bit-plane rows -> device (cc_load_reads_compact); raises if the batch does not fit
+        the format (pairs that do not mirror, more than 16 quality / literal-base combinations)."""
+        from .pack import row_geometry, to_compact
+        compact = compact or to_compact(packed)
+        if compact is None:
+            raise GpuError("the batch does not fit the compact format: use load()")
+        pairs, planes, qbits, qual_table, base_table = compact
+        dup = np.ascontiguousarray(packed.dup_bc, dtype=np.uint32)
+        self._keep = (pairs, planes, dup, qual_table, base_table)
+        self.lpad, self.stride = packed.lpad, row_geometry(packed.lpad)[1]
+        self._check(self.lib.cc_load_reads_compact(self.ctx, pairs.ctypes.data, planes.ctypes.data, packed.n, packed.lpad,
+                                                   planes.shape[1], int(qbits), qual_table.ctypes.data,
+                                                   base_table.ctypes.data, dup.ctypes.data, len(dup)))
+
     def load_device(self, fields_ptr, payload_ptr, n, lpad, stride, dup_ptr, n_bc):
         """Adopt buffers that already live in device memory (cc_load_reads_device)."""
         self.lpad, self.stride = int(lpad), int(stride)
@@ -235,17 +253,34 @@ class GpuConsensus:
     def device_ptr(self, name):
         return self.lib.cc_device_ptr(self.ctx, ARRAYS[name][0])
 
+    def fetch_many(self, names):
+        """Several result arrays with one wait for all the copies (cc_fetch_many)."""
+        k = len(names)
+        whats = (ctypes.c_int * k)(*[ARRAYS[nm][0] for nm in names])
+        sizes = (ctypes.c_uint64 * k)(*[self.lib.cc_array_bytes(self.ctx, ARRAYS[nm][0]) for nm in names])
+        outs = [np.zeros(sizes[j] // np.dtype(ARRAYS[nm][1]).itemsize, ARRAYS[nm][1]) for j, nm in enumerate(names)]
+        dsts = (ctypes.c_void_p * k)(*[o.ctypes.data if o.size else None for o in outs])
+        self._check(self.lib.cc_fetch_many(self.ctx, k, whats, dsts, sizes))
+        return {nm: (o.reshape(-1, self.stride) if nm.endswith("_rows") else o) for nm, o in zip(names, outs)}
+
     def result(self) -> ConsensusResult:
         from .result import ALL_ARRAYS
-        arrays = {k: self.fetch(k) for k in ALL_ARRAYS}
+        arrays = self.fetch_many(list(ALL_ARRAYS))
         return ConsensusResult(self.lpad, self.stride, bool(self.params.scorrect), **arrays)
 
     def consensus(self, packed: PackedReads, compact=False) -> ConsensusResult:
         """The whole path on one batch: host SoA in, family-level results out.
         compact=True sends the rows with 4-bit quality codes (cc_load_reads_q4)."""
         q4 = None
-        if compact == "auto":                  # compact rows whenever the batch's qualities allow them
-            from .pack import to_q4
+        if compact in ("auto", "planes"):      # the most compact rows the batch's qualities allow
+            from .pack import to_compact, to_q4
+            planes = to_compact(packed)
+            if planes is not None:
+                self.load_compact(packed, planes)
+                self.run()
+                return self.result()
+            if compact == "planes":
+                raise GpuError("the batch does not fit the compact format")
             q4 = to_q4(packed)
             compact = q4 is not None
         if compact:

@@ -247,6 +247,70 @@ def to_q4(packed):
     return out, table
 
 
+PAIR_DT = np.dtype([("bc", "<u4"), ("cig", "<u4"), ("tid", "<i4"), ("pos", "<i4"), ("mtid", "<i4"), ("mpos", "<i4"),
+                    ("tlen1", "<i4"), ("tlen2", "<i4"), ("flag1", "<u2"), ("flag2", "<u2"),
+                    ("mapq1", "u1"), ("mapq2", "u1"), ("rg1", "u1"), ("rg2", "u1")])       # include/ccgpu.h cc_pair
+assert PAIR_DT.itemsize == 40
+
+
+def to_pairs(fields):
+    """cc_pair records of a packed batch (one per read pair), or None when some pair's mates do not share
+    barcode / cigar pair or do not mirror each other's coordinates."""
+    a, b = fields[0::2], fields[1::2]
+    ok = ((a["bc"] == b["bc"]) & (a["cig"] == b["cig"]) & (a["tid"] == b["mtid"]) & (a["pos"] == b["mpos"]) &
+          (a["mtid"] == b["tid"]) & (a["mpos"] == b["pos"]))
+    if not ok.all():
+        return None
+    out = np.zeros(a.shape[0], PAIR_DT)
+    for nm in ("bc", "cig", "tid", "pos", "mtid", "mpos"):
+        out[nm] = a[nm]
+    out["tlen1"], out["tlen2"] = a["tlen"], b["tlen"]
+    out["flag1"], out["flag2"] = a["flag"], b["flag"]
+    out["mapq1"], out["mapq2"] = a["mapq"], b["mapq"]
+    out["rg1"], out["rg2"] = a["rg"], b["rg"]
+    return out
+
+
+def to_compact(packed):
+    """Input of `cc_load_reads_compact`: (pairs, planes u8[n][stride_c], qbits, qual_table u8[16], base_table u8[16])
+    or None when the batch does not fit (pairs that do not mirror, more than 16 codes).
+
+    A position is a 2-bit base (A,C,G,T) plus a code that names its quality and - for anything that is not
+    A/C/G/T: N, the padding after the read, IUPAC letters - its literal 4-bit base code."""
+    pairs = to_pairs(packed.fields)
+    if pairs is None:
+        return None
+    lpad, half = packed.lpad, packed.lpad // 2
+    n = packed.n
+    seq = packed.payload[:, :half]
+    base = np.empty((n, lpad), np.uint8)
+    base[:, 0::2] = seq & 15
+    base[:, 1::2] = seq >> 4
+    qual = packed.payload[:, half:half + lpad]
+    two_bit = np.full(16, 255, np.uint8)
+    two_bit[[1, 2, 4, 8]] = [0, 1, 2, 3]
+    b2 = two_bit[base]
+    literal = np.where(b2 == 255, base, 255).astype(np.uint16)          # 255: an A/C/G/T position
+    combo = (qual.astype(np.uint16) << 8) | literal
+    present = np.flatnonzero(np.bincount(combo.reshape(-1), minlength=65536)) if combo.size else np.zeros(0, np.int64)
+    if len(present) > 16:
+        return None
+    qbits = max(1, int(np.ceil(np.log2(max(2, len(present))))))
+    qual_table, base_table = np.zeros(16, np.uint8), np.full(16, 255, np.uint8)
+    code_of = np.zeros(65536, np.uint8)
+    for c, v in enumerate(present.tolist()):
+        qual_table[c], base_table[c] = v >> 8, v & 255
+        code_of[v] = c
+    codes = code_of[combo]
+    stride_c = (lpad // 4 + lpad * qbits // 8 + 15) // 16 * 16
+    planes = np.zeros((n, stride_c), np.uint8)
+    b2 = np.where(b2 == 255, 0, b2)
+    planes[:, :lpad // 4] = b2[:, 0::4] | (b2[:, 1::4] << 2) | (b2[:, 2::4] << 4) | (b2[:, 3::4] << 6)
+    bits = ((codes[:, :, None] >> np.arange(qbits, dtype=np.uint8)) & 1).reshape(n, lpad * qbits)
+    planes[:, lpad // 4:lpad // 4 + lpad * qbits // 8] = np.packbits(bits, axis=1, bitorder="little")
+    return pairs, planes, qbits, qual_table, base_table
+
+
 def from_q4(payload4, table, lpad):
     """Inverse of `to_q4`: the standard payload rows (what the device expands to)."""
     half = lpad // 2

@@ -184,11 +184,42 @@ int cc_load_reads_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payloa
 int cc_run_host_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload4, uint64_t n, uint32_t lpad,
                    uint32_t stride4, const uint8_t qual_table[16], const uint32_t *dup_bc, uint32_t n_bc);
 
+/* The most compact input: half the bytes of cc_load_reads for binned instruments.  Every byte of a batch
+ * crosses PCIe once, so the bytes a read costs there set the end-to-end rate.
+ *   pairs   n/2 x 40-byte cc_pair: the mates of a pair share barcode and cigar pair and mirror each other's
+ *           coordinates (read 2k+1 has tid/pos and mtid/mpos of read 2k swapped), so one record describes
+ *           both cc_fields records.  A batch whose pairs do not mirror must use cc_load_reads.
+ *   planes  n x stride_c bytes: lpad/4 bytes of 2-bit bases (A,C,G,T = 0..3; position p in bits 2p, 2p+1 of the
+ *           plane, little endian) then lpad*qbits/8 bytes of qbits-bit codes (position p at bit p*qbits);
+ *           stride_c % 16 == 0.  qual_table[code] is the position's quality; base_table[code] is 0xff for
+ *           "take the 2-bit base" or the literal 4-bit BAM base code of the position (15 for N, 0 for the
+ *           padding after the read's end, an IUPAC code).  The host picks the smallest qbits (1..4) that
+ *           names every (quality, literal base) combination of the batch; none fits: cc_load_reads.
+ * Expanded on the device into cc_fields records and standard rows; everything after that is as with
+ * cc_load_reads.  Same reference code as cc_load_reads (read_bam, consensus_helper.py:376-436).
+ * At lpad = 128 with 7 codes: 20 + 80 = 100 bytes per read against 224. */
+typedef struct {
+    uint32_t bc, cig;
+    int32_t tid, pos, mtid, mpos;      /* of the first-seen mate (read 2k)                   */
+    int32_t tlen1, tlen2;
+    uint16_t flag1, flag2;
+    uint8_t mapq1, mapq2, rg1, rg2;
+} cc_pair;
+int cc_load_reads_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes, uint64_t n, uint32_t lpad,
+                          uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
+                          const uint32_t *dup_bc, uint32_t n_bc);
+int cc_run_host_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes, uint64_t n, uint32_t lpad,
+                        uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
+                        const uint32_t *dup_bc, uint32_t n_bc);
+
 /* counts[CC_N_*] after the stage that produces them (synchronises). */
 int cc_counts(cc_ctx *ctx, uint64_t counts[8]);
 
 /* Copy result array `what` (enum cc_array) into host memory; `bytes` must be the exact size. */
 int cc_fetch(cc_ctx *ctx, int what, void *host_dst, uint64_t bytes);
+/* Several result arrays at once: every copy is issued before the one wait (cc_fetch waits per array).
+ * what[k] / host_dst[k] / bytes[k] as for cc_fetch; arrays of size 0 are skipped. */
+int cc_fetch_many(cc_ctx *ctx, uint32_t count, const int *what, void *const *host_dst, const uint64_t *bytes);
 /* Size in bytes of result array `what` (0 if not produced yet). */
 uint64_t cc_array_bytes(cc_ctx *ctx, int what);
 /* Device address of result array `what` (NULL if not produced yet); valid until the next load. */

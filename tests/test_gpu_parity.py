@@ -318,17 +318,60 @@ def test_one_sided_duplex_partnerships_are_outside_the_domain(engine):
     assert len(linked) and np.array_equal(q[q[linked]], linked)
 
 
-def test_sort_grouping_path_gives_the_same_result(monkeypatch):
-    # CCGPU_GROUP=sort selects the radix-sort grouping (hash keys, stable onesweep sort, exact boundaries);
-    # the default is the hash table of group_hash.cuh.  Same families, same numbering, same everything.
-    monkeypatch.setenv("CCGPU_GROUP", "sort")
+def _reordered(packed, order):
+    """The same pairs in another order (pair k = reads 2k, 2k+1 stay together)."""
+    from consensuscruncher_b200.pack import PackedReads
+    idx = np.stack([2 * order, 2 * order + 1], 1).reshape(-1)
+    return PackedReads(packed.fields[idx].copy(), packed.payload[idx].copy(), packed.lpad, packed.barcodes, packed.dup_bc,
+                       packed.cigar_pairs, packed.rgs)
+
+
+def test_inputs_out_of_order_and_pairs_across_contigs(engine):
+    """The default grouping finishes families inside a tile when completion coordinates come in order, and
+    checks that order itself.  Out-of-order inputs (shuffled pairs, a contig in two stretches, descending
+    positions) must take the all-through-the-table pass; pairs whose mates lie on two contigs always go
+    through the table.  The oracle does not care about order, so every variant is compared with it."""
+    base = synth.generate(seed=71, n_molecules=9000, L=48, n_tid=3, region=(0, 60000), fam_mean=3.0).to_packed()
+    n_pairs = base.n // 2
+    rng = np.random.default_rng(71)
+    ident = np.arange(n_pairs)
+    variants = {"sorted": ident, "shuffled": rng.permutation(n_pairs), "reversed": ident[::-1].copy(),
+                "two stretches": np.concatenate([ident[n_pairs // 2:], ident[:n_pairs // 2]]),
+                "one pair moved to the front": np.concatenate([[n_pairs - 1], ident[:-1]])}
+    for name, order in variants.items():
+        packed = _reordered(base, order)
+        engine.set_params(cutoff=0.7, scorrect=True)
+        helpers.assert_same_result(engine.consensus(packed), oracle.run(packed, 0.7, True))
+    # pairs across contigs: every pair starting in a window gets its second mate moved to another contig
+    # (consistently for whole families and their duplex partners: the choice depends on coordinates only)
+    cross = _reordered(base, ident)
+    f = cross.fields
+    sel = (f["pos"][0::2] % 7 == 3)
+    odd, even = np.nonzero(np.repeat(sel, 2) & (np.arange(cross.n) % 2 == 1))[0], np.nonzero(np.repeat(sel, 2) & (np.arange(cross.n) % 2 == 0))[0]
+    f["tid"][odd] = 9
+    f["mtid"][even] = 9
+    res = engine.consensus(cross)
+    helpers.assert_same_result(res, oracle.run(cross, 0.7, True))
+    assert res.n_fam > 1000 and (res.partner >= 0).sum() > 100
+    # long runs: thousands of pairs complete at one coordinate, so whole tiles are edge runs
+    deep = synth.generate(seed=72, n_molecules=3000, L=40, umi_len=4, region=(0, 700), insert_sd=1.0, fam_mean=6.0).to_packed()
+    helpers.assert_same_result(engine.consensus(deep), oracle.run(deep, 0.7, True))
+
+
+@pytest.mark.parametrize("mode", ["hash", "sort"])
+def test_other_grouping_paths_give_the_same_result(monkeypatch, mode):
+    # CCGPU_GROUP=sort selects the radix-sort grouping (hash keys, stable onesweep sort, exact boundaries),
+    # CCGPU_GROUP=hash the table with one trip per read (group_hash.cuh); the default groups tile by tile
+    # (group_tile.cuh).  Same families, same numbering, same everything.
+    monkeypatch.setenv("CCGPU_GROUP", mode)
     cases = [synth.generate(seed=41, n_molecules=2500, L=128).to_packed(),
              synth.generate(seed=42, n_molecules=800, L=64, mapq_mixed=True, max_family=40, dist="const", fam_mean=20).to_packed(),
              synth.generate(seed=61, n_molecules=30000, L=32, umi_len=2, region=(0, 1200), fam_mean=1.5, insert_sd=8.0).to_packed(),
              helpers.load_case("mode_ties")[2]]
-    with GpuConsensus(0, cutoff=0.7, scorrect=True) as by_sort:
+    cases.append(_reordered(cases[0], np.random.default_rng(3).permutation(cases[0].n // 2)))
+    with GpuConsensus(0, cutoff=0.7, scorrect=True) as other:
         for packed in cases:
-            helpers.assert_same_result(by_sort.consensus(packed), oracle.run(packed, 0.7, True))
+            helpers.assert_same_result(other.consensus(packed), oracle.run(packed, 0.7, True))
 
 
 def test_one_huge_family_and_all_singletons(engine):
