@@ -32,6 +32,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -62,7 +63,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-contexts", type=int, default=2, help="contexts the end-to-end leg rotates over")
-    ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4"],
+    ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4", "planes"],
                     help="host row format of the end-to-end leg: 8-bit qualities (cc_run_host), 4-bit quality "
                          "codes (cc_run_host_q4), or both with the compact one reported when the batch allows it")
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"],
@@ -414,6 +415,66 @@ def sweep_leg(args, eng, dev, stream):
             "reads": n, "cases": cases}
 
 
+def device_compact(batch):
+    """Input of `cc_run_host_compact` built on the device (pack.to_compact is the host statement):
+    (pairs i32[n/2][10], planes u8[n][stride_c], qbits, qual_table u8[16], base_table u8[16]) or None."""
+    import torch
+    f = batch.fields
+    a, b = f[0::2], f[1::2]
+    mirror = (a[:, 0] == b[:, 0]) & (a[:, 1] == b[:, 1]) & (a[:, 2] == b[:, 4]) & (a[:, 3] == b[:, 5]) & \
+             (a[:, 4] == b[:, 2]) & (a[:, 5] == b[:, 3])
+    if not bool(mirror.all()):
+        return None
+    pairs = torch.empty((a.shape[0], 10), dtype=torch.int32, device=f.device)
+    pairs[:, 0:6] = a[:, 0:6]
+    pairs[:, 6], pairs[:, 7] = a[:, 6], b[:, 6]
+    ma, mb = a[:, 7].to(torch.int64) & 0xFFFFFFFF, b[:, 7].to(torch.int64) & 0xFFFFFFFF
+    flags = (ma & 0xFFFF) | ((mb & 0xFFFF) << 16)
+    meta = ((ma >> 16) & 0xFF) | (((mb >> 16) & 0xFF) << 8) | ((ma >> 24) << 16) | ((mb >> 24) << 24)
+    as_i32 = lambda x: torch.where(x >= 2 ** 31, x - 2 ** 32, x).to(torch.int32)
+    pairs[:, 8], pairs[:, 9] = as_i32(flags), as_i32(meta)
+
+    lpad, half = batch.lpad, batch.lpad // 2
+    pay = batch.payload
+    n = pay.shape[0]
+    rows = 1 << 19
+    two_bit = torch.full((16,), 255, dtype=torch.int64, device=pay.device)
+    two_bit[torch.tensor([1, 2, 4, 8], device=pay.device)] = torch.arange(4, device=pay.device)
+
+    def split(chunk):                          # -> 2-bit base (255: none), literal base (255: A/C/G/T), quality
+        seq = chunk[:, :half].to(torch.int64)
+        base = torch.empty((chunk.shape[0], lpad), dtype=torch.int64, device=pay.device)
+        base[:, 0::2], base[:, 1::2] = seq & 15, seq >> 4
+        b2 = two_bit[base]
+        return b2, torch.where(b2 == 255, base, torch.full_like(base, 255)), chunk[:, half:half + lpad].to(torch.int64)
+
+    hist = torch.zeros(65536, dtype=torch.int64, device=pay.device)
+    for s0 in range(0, n, rows):
+        b2, lit, q = split(pay[s0:s0 + rows])
+        hist += torch.bincount(((q << 8) | lit).reshape(-1), minlength=65536)
+    present = torch.nonzero(hist).reshape(-1)
+    if present.numel() > 16:
+        return None
+    qbits = max(1, int(math.ceil(math.log2(max(2, present.numel())))))
+    qual_table = torch.zeros(16, dtype=torch.uint8)
+    base_table = torch.full((16,), 255, dtype=torch.uint8)
+    qual_table[:present.numel()] = (present >> 8).to(torch.uint8).cpu()
+    base_table[:present.numel()] = (present & 255).to(torch.uint8).cpu()
+    code_of = torch.zeros(65536, dtype=torch.int64, device=pay.device)
+    code_of[present] = torch.arange(present.numel(), device=pay.device)
+    stride_c = (lpad // 4 + lpad * qbits // 8 + 15) // 16 * 16
+    planes = torch.zeros((n, stride_c), dtype=torch.uint8, device=pay.device)
+    w8 = (1 << torch.arange(8, device=pay.device)).to(torch.int64)
+    for s0 in range(0, n, rows):
+        b2, lit, q = split(pay[s0:s0 + rows])
+        codes = code_of[(q << 8) | lit]
+        b2 = torch.where(b2 == 255, torch.zeros_like(b2), b2)
+        planes[s0:s0 + rows, :lpad // 4] = (b2[:, 0::4] | (b2[:, 1::4] << 2) | (b2[:, 2::4] << 4) | (b2[:, 3::4] << 6)).to(torch.uint8)
+        bits = ((codes.unsqueeze(2) >> torch.arange(qbits, device=pay.device)) & 1).reshape(codes.shape[0], lpad * qbits // 8, 8)
+        planes[s0:s0 + rows, lpad // 4:lpad // 4 + lpad * qbits // 8] = (bits * w8).sum(2).to(torch.uint8)
+    return pairs, planes, qbits, qual_table, base_table
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -538,17 +599,35 @@ def main():
             h_table = q4[1].cpu().contiguous()
             torch.cuda.synchronize(dev)
             q4 = None
+        # Most compact (cc_run_host_compact): 40-byte pair records + 2-bit bases + few-bit quality codes
+        planes = device_compact(batch) if args.e2e_format in ("auto", "planes") else None
+        if args.e2e_format == "planes" and planes is None:
+            raise SystemExit("--e2e-format planes: the batch does not fit the compact format")
+        h_pairs = h_planes = None
+        if planes is not None:
+            h_pairs = torch.empty(planes[0].shape, dtype=torch.int32, pin_memory=True)
+            h_planes = torch.empty(planes[1].shape, dtype=torch.uint8, pin_memory=True)
+            h_pairs.copy_(planes[0]); h_planes.copy_(planes[1])
+            p_qbits, p_qual, p_base = planes[2], planes[3].contiguous(), planes[4].contiguous()
+            torch.cuda.synchronize(dev)
+            planes = None
         fmt = {"name": "q8"}
+        import ctypes
 
         def e2e_step(which, step_no):
             e = engines[which]
-            if fmt["name"] == "q4":
+            if fmt["name"] == "planes":
+                e._check(e.lib.cc_run_host_compact(e.ctx, h_pairs.data_ptr(), h_planes.data_ptr(), n_reads, batch.lpad,
+                                                   h_planes.shape[1], p_qbits, p_qual.data_ptr(), p_base.data_ptr(),
+                                                   h_dup.data_ptr(), batch.n_bc))
+            elif fmt["name"] == "q4":
                 e._check(e.lib.cc_run_host_q4(e.ctx, h_fields.data_ptr(), h_q4.data_ptr(), n_reads, batch.lpad,
                                               h_q4.shape[1], h_table.data_ptr(), h_dup.data_ptr(), batch.n_bc))
             else:
                 e._check(e.lib.cc_run_host(e.ctx, h_fields.data_ptr(), h_payload.data_ptr(), n_reads, batch.lpad,
                                            batch.stride, h_dup.data_ptr(), batch.n_bc))
             total = 0
+            whats, dsts, sizes = [], [], []
             for nm in out_names:
                 what = ARRAYS[nm][0]
                 nbytes = e.lib.cc_array_bytes(e.ctx, what)
@@ -557,8 +636,11 @@ def main():
                 buf = h_outs[which].get(nm)
                 if buf is None or buf.numel() < nbytes:
                     buf = h_outs[which][nm] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8, pin_memory=True)
-                e._check(e.lib.cc_fetch(e.ctx, what, buf.data_ptr(), nbytes))
+                whats.append(what); dsts.append(buf.data_ptr()); sizes.append(nbytes)
                 total += nbytes
+            k = len(whats)                     # every copy is issued, then one wait (cc_fetch_many)
+            e._check(e.lib.cc_fetch_many(e.ctx, k, (ctypes.c_int * k)(*whats), (ctypes.c_void_p * k)(*dsts),
+                                         (ctypes.c_uint64 * k)(*sizes)))
             return total
 
         def worker(which, first, count):
@@ -588,8 +670,11 @@ def main():
             t = torch.tensor([wall], dtype=torch.float64, device=dev)
             if world > 1:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            payload_bytes = h_q4.numel() if name == "q4" else h_payload.numel()
-            h2d = h_fields.numel() * h_fields.element_size() + payload_bytes + h_dup.numel() * h_dup.element_size()
+            if name == "planes":
+                h2d = h_pairs.numel() * 4 + h_planes.numel() + h_dup.numel() * h_dup.element_size()
+            else:
+                payload_bytes = h_q4.numel() if name == "q4" else h_payload.numel()
+                h2d = h_fields.numel() * h_fields.element_size() + payload_bytes + h_dup.numel() * h_dup.element_size()
             return {"value": n_reads * world * e2e_steps / (float(t.item()) * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "ms_per_step": float(t.item()) / e2e_steps}
@@ -599,13 +684,20 @@ def main():
             legs["q8"] = measure("q8")
         if h_q4 is not None:
             legs["q4"] = measure("q4")
-        best = "q4" if "q4" in legs else "q8"
+        if h_planes is not None:
+            legs["planes"] = measure("planes")
+        best = "planes" if "planes" in legs else "q4" if "q4" in legs else "q8"
         e2e = dict(legs[best])
-        e2e["input_format"] = ("cc_run_host_q4: rows with 4-bit quality codes (the batch has %d distinct qualities)"
-                               % int((h_table != 0).sum() + 1)) if best == "q4" else \
-                              "cc_run_host: rows with 8-bit qualities"
-        if best == "q4" and "q8" in legs:
+        e2e["input_format"] = {
+            "planes": "cc_run_host_compact: 40-byte pair records + rows of 2-bit bases and %d-bit quality codes "
+                      "(%d bytes per read)" % (p_qbits if h_planes is not None else 0,
+                                               20 + (h_planes.shape[1] if h_planes is not None else 0)),
+            "q4": "cc_run_host_q4: rows with 4-bit quality codes",
+            "q8": "cc_run_host: rows with 8-bit qualities"}[best]
+        if best != "q8" and "q8" in legs:
             e2e["q8_rows"] = {k: legs["q8"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
+        if best == "planes" and "q4" in legs:
+            e2e["q4_rows"] = {k: legs["q4"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
         e2e["pipeline"] = ("%d contexts take turns: read-back of batch k overlaps upload of batch k+1; "
                            "host wall clock" % n_ctx)
         e2e["numa"] = numa
@@ -630,7 +722,7 @@ def main():
     if which or (args.sweep == "auto" and world == 1):
         # release the replica batch and the end-to-end leg's pinned buffers first
         batch = None
-        h_fields = h_payload = h_dup = h_q4 = h_outs = None
+        h_fields = h_payload = h_dup = h_q4 = h_outs = h_pairs = h_planes = None
         import gc
         gc.collect()
         torch.cuda.empty_cache()

@@ -125,7 +125,10 @@ struct cc_ctx {
     DevBuf gt_state;                            // ... device-side scalars + the contig stretch table (group_tile.cuh)
     enum GroupMode { GROUP_TILE, GROUP_HASH, GROUP_SORT };
     GroupMode group_mode = GROUP_TILE;
-    bool tile_join = false;                     // the loaded batch was grouped by the tile path (bitmap + word ranks name families)
+    bool tile_join = false;
+    uint64_t fam_bound = 0;                     // grids / buffers of family-level work cover this many families: the count itself
+                                                // (paths that learn it while grouping) or n (tile path: it stays on the device
+                                                // until the one synchronisation that also brings the row counts)                     // the loaded batch was grouped by the tile path (bitmap + word ranks name families)
     uint64_t gtable_mask = 0;                   // non-zero while gtable describes the loaded batch
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
@@ -386,7 +389,8 @@ int do_group_hash(cc_ctx *ctx)
     LAUNCH(group_place_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->bitmap), n, cursor, ctx->perm, ctx->spare_vals);
     ctx->read_fam_ready = true;
     ctx->gtable_mask = slots - 1;
-    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
+    ctx->fam_bound = nf;
+    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ctr + CT_NFAM,
            ctr + CT_FAULTS);
     TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS,
@@ -458,12 +462,12 @@ int do_group_tile(cc_ctx *ctx)
     ctx->sorted_keys = ctx->spare_keys = nullptr;
     LAUNCH(tile_place_kernel, (unsigned)tiles, GP_THREADS, n, link, aux, ptr<uint32_t>(ctx->bitmap),
            ptr<uint32_t>(ctx->word_rank), ptr<uint32_t>(ctx->cursor), ctx->perm);
-    TRY(read_counters(ctx));
-    const uint32_t nf = ctx->n_fam = ctx->host_ctr[CT_NFAM];
+    ctx->n_fam = 0;                                          // known after do_lists
+    ctx->fam_bound = n;
     ctx->read_fam_ready = false;
     ctx->gtable_mask = slots - 1;
     ctx->tile_join = true;
-    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
+    LAUNCH(domain_check_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ctr + CT_NFAM,
            ctr + CT_FAULTS);
     TRY(phase_end(ctx, CC_PH_SEGMENT));
     ctx->grouped = true;
@@ -475,6 +479,7 @@ int do_group(cc_ctx *ctx)
     const uint64_t n = ctx->n;
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = ctx->read_fam_ready = false;
     ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = ctx->n_extra = 0;
+    ctx->fam_bound = 0;
     ctx->next_ticket = 0;
     ctx->gtable_mask = 0;
     ctx->tile_join = false;
@@ -541,7 +546,8 @@ int do_group(cc_ctx *ctx)
            ptr<uint8_t>(ctx->is_sscs), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag),
            ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg), ptr<unsigned long long>(ctx->hist),
            (uint32_t)CC_HIST_BINS, ctr + CT_NMID, ptr<int32_t>(ctx->partner));
-    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), nf,
+    ctx->fam_bound = nf;
+    LAUNCH(domain_check_kernel, blocks_for(nf, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ctr + CT_NFAM,
            ctr + CT_FAULTS);
     TRY(ensure(ctx, ctx->sscs_row, (size_t)nf * 4));
     TRY(compact_flags(ctx, ptr<uint8_t>(ctx->is_sscs), nf, ptr<uint32_t>(ctx->sscs_list), ctr + CT_NSSCS,
@@ -556,16 +562,17 @@ int do_classify(cc_ctx *ctx);
 
 int do_join_index(cc_ctx *ctx)
 {
+    const uint64_t bound = ctx->fam_bound;
     const uint32_t nf = ctx->n_fam;
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
-    TRY(ensure(ctx, ctx->partner, (size_t)nf * 4));
-    TRY(ensure(ctx, ctx->dcs_list, (size_t)nf * 4)); TRY(ensure(ctx, ctx->corr_list, (size_t)nf * 4));
-    TRY(ensure(ctx, ctx->dcssc_list, (size_t)nf * 4));
-    if (nf == 0) return CC_OK;
+    TRY(ensure(ctx, ctx->partner, bound * 4));
+    TRY(ensure(ctx, ctx->dcs_list, bound * 4)); TRY(ensure(ctx, ctx->corr_list, bound * 4));
+    TRY(ensure(ctx, ctx->dcssc_list, bound * 4));
+    if (bound == 0) return CC_OK;
     TRY(phase_begin(ctx, CC_PH_JOIN));
     if (ctx->gtable_mask && ctx->tile_join) {
         // (the barcode swap's symmetry was established before the tiles were grouped)
-        LAUNCH(tile_join_kernel, blocks_for(nf, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), nf, ctx->dup_bc, ctx->n_bc,
+        LAUNCH(tile_join_kernel, blocks_for(bound, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), ctr + CT_NFAM, ctx->dup_bc, ctx->n_bc,
                ptr<GroupSlot>(ctx->gtable), ptr<uint32_t>(ctx->gt_state), ptr<uint32_t>(ctx->key_a), ptr<uint32_t>(ctx->key_b),
                ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
         TRY(phase_end(ctx, CC_PH_JOIN));
@@ -594,7 +601,7 @@ int do_join_index(cc_ctx *ctx)
 
 int do_classify(cc_ctx *ctx)
 {
-    const uint32_t nf = ctx->n_fam;
+    const uint64_t nf = ctx->fam_bound;
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     TRY(phase_begin(ctx, CC_PH_CLASSIFY));
     // one chained scan classifies the families and writes the three lists with their family -> row maps;
@@ -607,7 +614,7 @@ int do_classify(cc_ctx *ctx)
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * tiles + 2) * sizeof(unsigned long long), ctx->stream));
     if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
     uint32_t *ticket = ctr + CT_TICKET0 + ctx->next_ticket++;
-    LAUNCH(classify_scan_kernel, (unsigned)tiles, CLS_THREADS, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), nf,
+    LAUNCH(classify_scan_kernel, (unsigned)tiles, CLS_THREADS, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), ctr + CT_NFAM,
            (int)ctx->params.scorrect, ptr<unsigned long long>(ctx->scan_status), ticket, ptr<uint32_t>(ctx->dcs_list),
            ptr<uint32_t>(ctx->corr_list), ptr<uint32_t>(ctx->dcssc_list), ptr<int32_t>(ctx->dcs_row), ptr<int32_t>(ctx->corr_row),
            ptr<int32_t>(ctx->dcssc_row), ptr<unsigned long long>(ctx->stats), ctr + CT_ONESIDED, ctr + CT_NDCS, ctr + CT_NCORR,
@@ -626,6 +633,7 @@ int do_lists(cc_ctx *ctx, bool with_join)
         return fail(ctx, CC_ERR_DOMAIN, "a duplex partnership is not mutual (undotted barcodes of odd length: duplex_tag "
                                         "applied twice gives another barcode, consensus_helper.py:629-639); what the "
                                         "reference writes then depends on file order: outside the GPU path's domain");
+    ctx->n_fam = ctx->host_ctr[CT_NFAM];
     ctx->n_sscs = ctx->host_ctr[CT_NSSCS];               // family -> row maps were written by the compactions
     if (with_join) {
         ctx->n_dcs = ctx->host_ctr[CT_NDCS];

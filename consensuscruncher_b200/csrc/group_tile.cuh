@@ -81,6 +81,16 @@ inline uint64_t gt_tiles(uint64_t n) { return (n + GT_TILE - 1) / GT_TILE; }
 // every member subtracts 2, bit 0 is cleared when mode fields differ
 __device__ __forceinline__ uint32_t group_cnt(uint32_t members, bool mixed) { return (0xFFFFFFFFu - 2u * members) & (mixed ? ~1u : ~0u); }
 
+// slot of a tuple in the tile's shared table: a short 32-bit mix is enough to spread one tile's families
+// (the 64-bit rec_hash, 7 wide multiplies, is kept for the global table)
+__device__ __forceinline__ uint32_t tile_hash(const uint4 &a, const uint4 &b)
+{
+    uint32_t h = a.x * 0x9E3779B1u ^ a.w * 0x85EBCA6Bu ^ b.y * 0xC2B2AE35u ^ a.y * 0x27D4EB2Fu;
+    h ^= (a.z * 31u + b.x + key_bits(b.w) * 0x10001u) * 0x165667B1u;
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12;
+    return h & (GT_HT - 1);
+}
+
 // mode 0: first pass.  mode 1: only if the first pass found the input out of order; then nothing is local.
 __global__ void __launch_bounds__(GT_THREADS)
 tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const uint32_t *__restrict__ dup_bc, uint32_t n_bc,
@@ -105,7 +115,7 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
     for (int k = tid; k < (int)GT_HT; k += GT_THREADS) ht[k] = GT_EMPTY;
     if (tid == 0) { n_reps = 0; n_edge = 0; }
     if (tid < GT_TILE / 32) { bm[tid] = 0; bm_reads[tid] = 0; bm_sscs[tid] = 0; }
-    uint64_t h[GT_PER];
+    uint32_t h[GT_PER];
 #pragma unroll
     for (int k = 0; k < GT_PER; k++) {
         const uint32_t li = k * GT_THREADS + tid;
@@ -114,7 +124,7 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
             const Rec r = load_rec(fields, (uint32_t)(base + li));
             key_a[li] = r.a;
             key_b[li] = r.b;
-            h[k] = rec_hash(r);
+            h[k] = tile_hash(r.a, r.b);
         }
     }
     static_assert(GT_THREADS >= 64, "two warps look for the tile's neighbours");
@@ -148,7 +158,7 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
         const uint32_t li = k * GT_THREADS + tid;
         if (li >= here) continue;
         const Rec r{key_a[li], key_b[li]};
-        uint32_t s = (uint32_t)(h[k] >> 7) & (GT_HT - 1);
+        uint32_t s = h[k];
         for (;;) {
             uint32_t cur = ht[s];
             if (cur == GT_EMPTY) {
@@ -233,7 +243,7 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
                 if (d != NO_ID) {
                     q.a.x = d;
                     q.b.w ^= 0x40u;
-                    uint32_t s = (uint32_t)(rec_hash(q) >> 7) & (GT_HT - 1);
+                    uint32_t s = tile_hash(q.a, q.b);
                     for (;;) {
                         const uint32_t cur = ht[s];
                         if (cur == GT_EMPTY) break;
@@ -546,14 +556,14 @@ tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t 
 // (group_hash.cuh's group_join_kernel).  Symmetric / asymmetric as join_probe_kernel: with *asym set
 // nothing was treated as interior and every family probes.
 __global__ void __launch_bounds__(256)
-tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, uint32_t n_fam,
+tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ tmpl, const uint32_t *__restrict__ n_fam_ptr,
                  const uint32_t *__restrict__ dup_bc, uint32_t n_bc, const GroupSlot *__restrict__ table,
                  const uint32_t *__restrict__ gtc, const uint32_t *__restrict__ link, const uint32_t *__restrict__ aux,
                  const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ word_rank,
                  int32_t *__restrict__ partner, const uint32_t *__restrict__ asym)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n_fam) return;
+    if (c >= *n_fam_ptr) return;                    // the family count lives on the device; the grid covers the host's bound
     const uint32_t first = tmpl[c];
     const uint4 meta = __ldg(&fields[2 * (uint64_t)first + 1]);
     const bool symmetric = !*asym;

@@ -233,8 +233,9 @@ family_build_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict
 // the mate of a family's template must be the template of the neighbouring family, of equal size.
 __global__ void __launch_bounds__(256)
 domain_check_kernel(const uint32_t *__restrict__ tmpl, const uint32_t *__restrict__ fam_size,
-                    uint32_t n_fam, uint32_t *__restrict__ faults)
+                    const uint32_t *__restrict__ n_fam_ptr, uint32_t *__restrict__ faults)
 {
+    const uint32_t n_fam = *n_fam_ptr;              // on the device: the grid covers the bound the host knows
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_fam) return;
     uint32_t o = c ^ 1u;
@@ -372,7 +373,8 @@ classify_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict
 constexpr int CLS_THREADS = 256, CLS_ITEMS = 8, CLS_TILE = CLS_THREADS * CLS_ITEMS;
 
 __global__ void __launch_bounds__(CLS_THREADS)
-classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict__ partner, uint32_t n_fam, int scorrect,
+classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__restrict__ partner,
+                     const uint32_t *__restrict__ n_fam_ptr, int scorrect,
                      unsigned long long *status, uint32_t *ticket,
                      uint32_t *__restrict__ dcs_list, uint32_t *__restrict__ corr_list, uint32_t *__restrict__ dcssc_list,
                      int32_t *__restrict__ dcs_row, int32_t *__restrict__ corr_row, int32_t *__restrict__ dcssc_row,
@@ -388,6 +390,11 @@ classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__res
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
+    // the family count lives on the device; the grid covers the host's bound and the tiles beyond the
+    // last family leave at once (they come after every tile that matters: nobody looks back at them)
+    const uint32_t n_fam = *n_fam_ptr;
+    const uint32_t last_tile = n_fam ? (n_fam - 1) / CLS_TILE : 0;
+    if (n_fam == 0 || tile > last_tile) return;
     const uint32_t base = tile * CLS_TILE + tid * CLS_ITEMS;
     uint32_t f_dcs = 0, f_corr = 0, f_x = 0;          // bit k: family base + k is in the class
     uint32_t mine[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -464,7 +471,7 @@ classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__res
         lookback_pairs<2>(status, tile, tot, excl, lane);
         if (lane == 0) {
             s_excl[0] = excl[0]; s_excl[1] = excl[1]; s_excl[2] = excl[2];
-            if (tile == gridDim.x - 1) { *n_dcs = excl[0] + tot[0]; *n_corr = excl[1] + tot[1]; *n_extra = excl[2] + tot[2]; }
+            if (tile == last_tile) { *n_dcs = excl[0] + tot[0]; *n_corr = excl[1] + tot[1]; *n_extra = excl[2] + tot[2]; }
         }
     }
     __syncthreads();

@@ -311,6 +311,35 @@ def to_compact(packed):
     return pairs, planes, qbits, qual_table, base_table
 
 
+def from_compact(pairs, planes, qbits, qual_table, base_table, lpad):
+    """Inverse of `to_compact`: (fields, standard payload rows) - what the device expands to."""
+    n = 2 * pairs.shape[0]
+    f = np.zeros(n, FIELDS_DT)
+    a, b = f[0::2], f[1::2]
+    for nm in ("bc", "cig"):
+        a[nm] = b[nm] = pairs[nm]
+    a["tid"], a["pos"], a["mtid"], a["mpos"] = pairs["tid"], pairs["pos"], pairs["mtid"], pairs["mpos"]
+    b["tid"], b["pos"], b["mtid"], b["mpos"] = pairs["mtid"], pairs["mpos"], pairs["tid"], pairs["pos"]
+    a["tlen"], b["tlen"] = pairs["tlen1"], pairs["tlen2"]
+    a["flag"], b["flag"] = pairs["flag1"], pairs["flag2"]
+    a["mapq"], b["mapq"] = pairs["mapq1"], pairs["mapq2"]
+    a["rg"], b["rg"] = pairs["rg1"], pairs["rg2"]
+    half = lpad // 2
+    _, stride = row_geometry(lpad)
+    bp = planes[:, :lpad // 4]
+    b2 = np.empty((n, lpad), np.uint8)
+    for k in range(4):
+        b2[:, k::4] = (bp >> (2 * k)) & 3
+    bits = np.unpackbits(planes[:, lpad // 4:lpad // 4 + lpad * qbits // 8], axis=1, bitorder="little").reshape(n, lpad, qbits)
+    codes = (bits << np.arange(qbits, dtype=np.uint8)).sum(axis=2).astype(np.uint8)
+    lit = base_table[codes]
+    base = np.where(lit != 255, lit, (1 << b2).astype(np.uint8)).astype(np.uint8)
+    out = np.zeros((n, stride), np.uint8)
+    out[:, :half] = base[:, 0::2] | (base[:, 1::2] << 4)
+    out[:, half:half + lpad] = qual_table[codes]
+    return f, out
+
+
 def from_q4(payload4, table, lpad):
     """Inverse of `to_q4`: the standard payload rows (what the device expands to)."""
     half = lpad // 2

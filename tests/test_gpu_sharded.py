@@ -162,3 +162,16 @@ def test_batches_with_many_distinct_qualities_take_the_8_bit_rows(engine):
     few = synth.generate(seed=62, n_molecules=800, L=100).to_packed()
     assert pack.to_q4(few) is not None
     helpers.assert_same_result(engine.consensus(few, compact="auto"), oracle.run(few, 0.7, True))
+
+
+@pytest.mark.parametrize("kw", [dict(seed=81, n_molecules=1500, L=128), dict(seed=82, n_molecules=900, L=33, n_tid=3),
+                                dict(seed=83, n_molecules=600, L=250, mapq_mixed=True), dict(seed=84, n_molecules=3, L=40)])
+def test_compact_upload_gives_the_same_result(engine, kw):
+    """cc_load_reads_compact: pair records + 2-bit bases + few-bit quality codes, expanded on the device."""
+    from consensuscruncher_b200 import pack, synth
+    packed = synth.generate(**kw).to_packed()
+    assert pack.to_compact(packed) is not None
+    engine.set_params(cutoff=0.7, scorrect=True)
+    got = engine.consensus(packed, compact="planes")
+    helpers.assert_same_result(got, oracle.run(packed, 0.7, True))
+    helpers.assert_same_result(got, engine.consensus(packed))

@@ -188,3 +188,29 @@ def test_region_of_reads_binary_search_equals_the_region_loop():
     odd = [(0, 0, 100), (0, 50, 150), (1, 0, 10)]
     t2, p2 = np.array([0, 0, 0, 1, 1]), np.array([10, 60, 149, 5, 10])
     assert shard.region_of_reads(t2, p2, odd).tolist() == [0, 1, 1, 2, -1]
+
+
+def test_compact_upload_format_round_trips():
+    """pack.to_compact (input of cc_load_reads_compact): pair records + bit planes decode to the very same
+    field records and payload rows; batches that do not fit are refused."""
+    for kw in (dict(seed=5, n_molecules=300, L=100), dict(seed=6, n_molecules=200, L=33, n_tid=3),
+               dict(seed=7, n_molecules=150, L=150, mapq_mixed=True)):
+        packed = synth.generate(**kw).to_packed()
+        c = pack.to_compact(packed)
+        assert c is not None
+        pairs, planes, qbits, qt, bt = c
+        assert pairs.dtype.itemsize == 40 and pairs.shape[0] == packed.n // 2 and 1 <= qbits <= 4
+        assert planes.shape[1] % 16 == 0 and planes.shape[1] >= packed.lpad // 4 + packed.lpad * qbits // 8
+        f, rows = pack.from_compact(pairs, planes, qbits, qt, bt, packed.lpad)
+        assert f.tobytes() == np.ascontiguousarray(packed.fields).tobytes()
+        assert np.array_equal(rows, packed.payload)
+    # too many (quality, literal base) combinations for 4 bits
+    packed = synth.generate(seed=8, n_molecules=200, L=64).to_packed()
+    half = packed.lpad // 2
+    q = packed.payload[:, half:half + 64]
+    q[...] = np.where(q > 2, np.random.default_rng(1).integers(3, 42, q.shape).astype(np.uint8), q)
+    assert pack.to_compact(packed) is None
+    # mates that do not mirror each other
+    packed = synth.generate(seed=9, n_molecules=50, L=64).to_packed()
+    packed.fields["mpos"][0] += 1
+    assert pack.to_pairs(packed.fields) is None and pack.to_compact(packed) is None
