@@ -467,7 +467,7 @@ int do_group_tile(cc_ctx *ctx)
     ctx->read_fam_ready = false;
     ctx->gtable_mask = slots - 1;
     ctx->tile_join = true;
-    LAUNCH(domain_check_kernel, blocks_for(n, 256), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ctr + CT_NFAM,
+    LAUNCH(domain_check_kernel, (unsigned)std::min<uint64_t>(blocks_for(n, 256), 148 * 32), 256, ptr<uint32_t>(ctx->tmpl), ptr<uint32_t>(ctx->fam_size), ctr + CT_NFAM,
            ctr + CT_FAULTS);
     TRY(phase_end(ctx, CC_PH_SEGMENT));
     ctx->grouped = true;
@@ -572,7 +572,7 @@ int do_join_index(cc_ctx *ctx)
     TRY(phase_begin(ctx, CC_PH_JOIN));
     if (ctx->gtable_mask && ctx->tile_join) {
         // (the barcode swap's symmetry was established before the tiles were grouped)
-        LAUNCH(tile_join_kernel, blocks_for(bound, 256), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), ctr + CT_NFAM, ctx->dup_bc, ctx->n_bc,
+        LAUNCH(tile_join_kernel, (unsigned)std::min<uint64_t>(blocks_for(bound, 256), 148 * 32), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), ctr + CT_NFAM, ctx->dup_bc, ctx->n_bc,
                ptr<GroupSlot>(ctx->gtable), ptr<uint32_t>(ctx->gt_state), ptr<uint32_t>(ctx->key_a), ptr<uint32_t>(ctx->key_b),
                ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
         TRY(phase_end(ctx, CC_PH_JOIN));

@@ -562,12 +562,12 @@ tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ 
                  const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ word_rank,
                  int32_t *__restrict__ partner, const uint32_t *__restrict__ asym)
 {
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= *n_fam_ptr) return;                    // the family count lives on the device; the grid covers the host's bound
+    const uint32_t n_fam = *n_fam_ptr;              // the family count lives on the device: a grid-stride loop up to it
+    const bool symmetric = !*asym;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n_fam; c += gridDim.x * blockDim.x) {
     const uint32_t first = tmpl[c];
     const uint4 meta = __ldg(&fields[2 * (uint64_t)first + 1]);
-    const bool symmetric = !*asym;
-    if (symmetric && !(meta.w & 0x40u)) return;     // an R2 family hears from its R1 partner (partner[] starts at -1)
+    if (symmetric && !(meta.w & 0x40u)) continue;   // an R2 family hears from its R1 partner (partner[] starts at -1)
     int32_t found = -1;
     if (__ldg(&link[first]) & LINK_LOCAL) {
         const uint32_t p = __ldg(&aux[first]);
@@ -591,6 +591,7 @@ tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ 
     }
     partner[c] = found;
     if (symmetric && found >= 0) partner[found] = (int32_t)c;
+    }
 }
 
 }  // namespace ccgpu

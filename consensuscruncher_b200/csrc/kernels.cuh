@@ -235,12 +235,12 @@ __global__ void __launch_bounds__(256)
 domain_check_kernel(const uint32_t *__restrict__ tmpl, const uint32_t *__restrict__ fam_size,
                     const uint32_t *__restrict__ n_fam_ptr, uint32_t *__restrict__ faults)
 {
-    const uint32_t n_fam = *n_fam_ptr;              // on the device: the grid covers the bound the host knows
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n_fam) return;
-    uint32_t o = c ^ 1u;
-    bool ok = o < n_fam && tmpl[o] == (tmpl[c] ^ 1u) && fam_size[o] == fam_size[c];
-    if (!ok) atomicAdd(faults, 1u);
+    const uint32_t n_fam = *n_fam_ptr;              // on the device: a grid-stride loop up to it
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n_fam; c += gridDim.x * blockDim.x) {
+        uint32_t o = c ^ 1u;
+        bool ok = o < n_fam && tmpl[o] == (tmpl[c] ^ 1u) && fam_size[o] == fam_size[c];
+        if (!ok) atomicAdd(faults, 1u);
+    }
 }
 
 // read -> family (only materialised when a caller fetches CC_READ_FAM)
