@@ -57,26 +57,36 @@ def regions_from_bed(bedfile, header):
 
 
 def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bdelim="|", cleanup=False,
-                  device=0, engine=None, log=print):
-    """Everything `consensus()` does in the reference.  Returns the sample directory."""
+                  device=0, engine=None, log=print, gpus=1, chunk_reads=20_000_000):
+    """Everything `consensus()` does in the reference.  Returns the sample directory.
+
+    The packed reads go through the GPU(s) in chunks of consecutive bed regions of about `chunk_reads`
+    reads (stream.py): `gpus` contexts, one per device starting at `device`, take the chunks in turn; the
+    output does not depend on either number."""
+    from . import stream
     from .engine import GpuConsensus
     t0 = time.time()
     identifier = os.path.basename(bam_path).split(".bam", 1)[0]
     sample_dir = os.path.join(out_dir, identifier)
-    os.makedirs(os.path.join(sample_dir, "sscs"))          # like the reference: fails if it exists (Q19)
+    if os.path.exists(sample_dir):                         # like the reference, a re-run needs a clean directory (Q19) -
+        raise FileExistsError(sample_dir)                  # but nothing is created before the input has been read
     header, reads = fastpack.open_bam(bam_path)            # native inflate + pack; records decode lazily
     regions = None if bedfile in (None, "False", False) else regions_from_bed(bedfile, header)
     packed = fastpack.pack_reads(reads, "sscs", bdelim, regions)
     t_pack = time.time()
     own = engine is None
-    eng = engine or GpuConsensus(device, cutoff=cutoff, scorrect=scorrect)
+    engines = [engine] if engine is not None else [GpuConsensus(device + k, cutoff=cutoff, scorrect=scorrect)
+                                                   for k in range(max(1, int(gpus)))]
     try:
-        eng.set_params(cutoff=cutoff, scorrect=scorrect)
-        res = eng.consensus(packed)
+        for eng in engines:
+            eng.set_params(cutoff=cutoff, scorrect=scorrect)
+        res, packed, n_chunks = stream.consensus_chunked(packed, engines, regions, chunk_reads, log=log)
     finally:
         if own:
-            eng.close()
+            for eng in engines:
+                eng.close()
     t_gpu = time.time()
+    os.makedirs(os.path.join(sample_dir, "sscs"))
     # record assembly, the sort / merge steps between the stages and the BAM + BAI writing are native
     # host code (csrc/ccemit.cpp); emit.emit_all + bam.write_bam are the same thing in Python
     where = {"sscs.sorted": "sscs", "singleton.sorted": "sscs", "badReads": "sscs",
@@ -98,8 +108,8 @@ def run_consensus(bam_path, out_dir, cutoff=0.7, scorrect=True, bedfile=None, bd
         fh.write(fam_txt)
     t_end = time.time()
     with open(os.path.join(sample_dir, identifier + ".time_tracker.txt"), "w") as fh:
-        fh.write("decode+pack: %s\nGPU consensus: %s\nemit+write: %s\n" %
-                 ((t_pack - t0) / 60, (t_gpu - t_pack) / 60, (t_end - t_gpu) / 60))
+        fh.write("decode+pack: %s\nGPU consensus (%d chunks, %d GPUs): %s\nemit+write: %s\n" %
+                 ((t_pack - t0) / 60, n_chunks, len(engines), (t_gpu - t_pack) / 60, (t_end - t_gpu) / 60))
     if cleanup:
         _cleanup(sample_dir, identifier, scorrect)
     log(stats)
@@ -145,7 +155,10 @@ def build_parser(config_path=None):
     p.add_argument("--cutoff", type=float, help="consensus cut-off, default 0.7")
     p.add_argument("-d", "--bdelim", metavar="DELIMITER", type=str, help="delimiter before the barcode, default '|'")
     p.add_argument("--cleanup", choices=["True", "False"], help="remove intermediate files")
-    p.add_argument("--device", type=int, default=0, help="CUDA device")
+    p.add_argument("--device", type=int, default=0, help="first CUDA device")
+    p.add_argument("--gpus", type=int, default=1, help="GPUs that take the region chunks in turn (devices --device ...)")
+    p.add_argument("--chunk-reads", type=int, default=20_000_000,
+                   help="reads per chunk of consecutive bed regions (bounds the device memory a sample needs)")
     p.set_defaults(**defaults)
     return main_p, p
 
@@ -178,8 +191,15 @@ def main(argv=None):
         if bedfile is None:
             cons_p.error("no -b/--bedfile given and hg19_cytoBand.txt is not installed; "
                          "pass -b FILE or -b False")
-    run_consensus(args.bam, args.c_output, cutoff=float(args.cutoff), scorrect=str(args.scorrect) != "False",
-                  bedfile=bedfile, bdelim=args.bdelim, cleanup=str(args.cleanup) == "True", device=args.device)
+    from .engine import GpuError
+    try:
+        run_consensus(args.bam, args.c_output, cutoff=float(args.cutoff), scorrect=str(args.scorrect) != "False",
+                      bedfile=bedfile, bdelim=args.bdelim, cleanup=str(args.cleanup) == "True", device=args.device,
+                      gpus=args.gpus, chunk_reads=args.chunk_reads)
+    except (pack.DomainError, GpuError, ValueError, FileExistsError) as exc:
+        # one line, no traceback, nothing half-written: the sample directory is only created once the GPU pass is done
+        print("ConsensusCruncher.py consensus: %s: %s" % (type(exc).__name__, exc), file=sys.stderr)
+        return 1
     return 0
 
 

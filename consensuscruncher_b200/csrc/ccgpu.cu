@@ -626,6 +626,7 @@ int do_classify(cc_ctx *ctx)
 int do_lists(cc_ctx *ctx, bool with_join)
 {
     TRY(read_counters(ctx));
+    ctx->n_fam = ctx->host_ctr[CT_NFAM];                 // (before the checks: the family arrays stay fetchable after a fault)
     if (ctx->host_ctr[CT_FAULTS])
         return fail(ctx, CC_ERR_DOMAIN, "a read pair does not found/join its two families together "
                                         "(SSCS_maker.py:275 would not emit this pair name): outside the GPU path's domain");
@@ -633,7 +634,6 @@ int do_lists(cc_ctx *ctx, bool with_join)
         return fail(ctx, CC_ERR_DOMAIN, "a duplex partnership is not mutual (undotted barcodes of odd length: duplex_tag "
                                         "applied twice gives another barcode, consensus_helper.py:629-639); what the "
                                         "reference writes then depends on file order: outside the GPU path's domain");
-    ctx->n_fam = ctx->host_ctr[CT_NFAM];
     ctx->n_sscs = ctx->host_ctr[CT_NSSCS];               // family -> row maps were written by the compactions
     if (with_join) {
         ctx->n_dcs = ctx->host_ctr[CT_NDCS];

@@ -75,9 +75,55 @@ __device__ __forceinline__ uint32_t nz7u(uint32_t x) { return x + 0x7F7F7F7Fu; }
 
 __device__ __forceinline__ uint32_t sel(uint32_t a, uint32_t b, uint32_t mask) { return (a & mask) | (b & ~mask); }
 
+// Experiment kept behind a switch (profiles/r2_vote_sass.md): the ALU pipe (LOP3 / PRMT / IADD3 / SHF) is 78 %
+// busy while the FMA pipe idles at 25 %, so VOTE_FMA_CFG >= 1 writes the additions that feed the byte-lane
+// compares - and >= 2 the constant right shifts too - as integer multiply-adds with a run-time 1 / -1 / power
+// of two (same value mod 2^32, issued on the FMA pipe).  Measured slower (1.031 / 1.054 ms against 1.013):
+// a + C - b is ONE three-input add but TWO multiply-adds, and the kernel is bound by issue slots, not by a pipe.
+#ifndef VOTE_FMA_CFG
+#define VOTE_FMA_CFG 0
+#endif
+
 // x + y as an integer multiply-add: with `one` a run-time 1 the compiler cannot fold it back
 // into an add, so it issues on the FMA pipe instead of the (saturated) ALU pipe.
 __device__ __forceinline__ uint32_t fadd(uint32_t x, uint32_t y, uint32_t one) { return x * one + y; }
+
+// ge7u / nz7u on the FMA pipe (`one` is the run-time 1 of fadd)
+__device__ __forceinline__ uint32_t ge7f(uint32_t a, uint32_t b, uint32_t one)
+{
+#if VOTE_FMA_CFG >= 1
+    return fadd(b * (0u - one) + a, 0x80808080u, one);
+#else
+    return ge7u(a, b);
+#endif
+}
+template <uint32_t B>
+__device__ __forceinline__ uint32_t ge7c(uint32_t a, uint32_t one)      // b a compile-time constant: one multiply-add
+{
+#if VOTE_FMA_CFG >= 1
+    return fadd(a, 0x80808080u - B, one);
+#else
+    return ge7u(a, B);
+#endif
+}
+__device__ __forceinline__ uint32_t nz7f(uint32_t x, uint32_t one)
+{
+#if VOTE_FMA_CFG >= 1
+    return fadd(x, 0x7F7F7F7Fu, one);
+#else
+    return nz7u(x);
+#endif
+}
+// x >> S for a constant S: the high word of x * 2^(32-S)
+template <int S>
+__device__ __forceinline__ uint32_t shr(uint32_t x, uint32_t one)
+{
+#if VOTE_FMA_CFG >= 2
+    return __umulhi(x, one << (32 - S));
+#else
+    return x >> S;
+#endif
+}
 
 __device__ __forceinline__ uint32_t prmt(uint32_t lo, uint32_t hi, uint32_t selector)
 {
@@ -131,6 +177,10 @@ __device__ __forceinline__ uint32_t expand_sel(uint32_t sel16)
 {
     return __byte_perm(sel16 & 0x0F0Fu, (sel16 >> 4) & 0x0F0Fu, 0x5140);
 }
+__device__ __forceinline__ uint32_t expand_sel(uint32_t sel16, uint32_t one)
+{
+    return __byte_perm(sel16 & 0x0F0Fu, shr<4>(sel16, one) & 0x0F0Fu, 0x5140);
+}
 
 __device__ __forceinline__ uint32_t cap60(uint32_t q)
 {
@@ -143,6 +193,10 @@ __device__ __forceinline__ uint32_t cap60(uint32_t q)
 __device__ __forceinline__ uint32_t cap60_lo(uint32_t q)
 {
     return sel(0x3C3C3C3Cu, q, bytes_of(ge7u(q, 0x3C3C3C3Cu)));
+}
+__device__ __forceinline__ uint32_t cap60_lo(uint32_t q, uint32_t one)
+{
+    return sel(0x3C3C3C3Cu, q, bytes_of(ge7c<0x3C3C3C3Cu>(q, one)));
 }
 
 struct QuadOut {
@@ -161,32 +215,33 @@ struct ThrMagic {       // thr[p] == (p * k + r) >> 8 for every p the kernel can
 
 template <bool TOTALS>
 __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr, bool unanimous_ok, ThrMagic tm,
-                                               uint32_t &err)
+                                               uint32_t &err, uint32_t one)
 {
     QuadOut o;
-    const uint32_t tnow = (a.gt >> 4) & 0x0F0F0F0Fu;
-    uint32_t cA = a.ac & 0x0F0F0F0Fu, cC = (a.ac >> 4) & 0x0F0F0F0Fu, cT = tnow, cG = (a.gt & 0x0F0F0F0Fu) - tnow;
+    const uint32_t tnow = shr<4>(a.gt, one) & 0x0F0F0F0Fu;
+    uint32_t cA = a.ac & 0x0F0F0F0Fu, cC = shr<4>(a.ac, one) & 0x0F0F0F0Fu, cT = tnow;
+    uint32_t cG = fadd(tnow, a.gt & 0x0F0F0F0Fu, 0u - one);
     if (TOTALS) { cA += a.tA; cC += a.tC; cT += a.tT; cG += a.tG; }
-    uint32_t m1 = bytes_of(ge7u(cA, cC));                  // ties keep the earlier base: A,C,G,T order
-    uint32_t m2 = bytes_of(ge7u(cG, cT));
+    uint32_t m1 = bytes_of(ge7f(cA, cC, one));             // ties keep the earlier base: A,C,G,T order
+    uint32_t m2 = bytes_of(ge7f(cG, cT, one));
     uint32_t bAC = sel(cA, cC, m1), wAC = sel(0x01010101u, 0x02020202u, m1);
     uint32_t bGT = sel(cG, cT, m2), wGT = sel(0x04040404u, 0x08080808u, m2);
-    uint32_t m3 = bytes_of(ge7u(bAC, bGT));
+    uint32_t m3 = bytes_of(ge7f(bAC, bGT, one));
     uint32_t best = sel(bAC, bGT, m3);
     o.win = sel(wAC, wGT, m3);
-    uint32_t sum = cA + cC + (a.gt & 0x0F0F0F0Fu);         // the G+T nibble already holds cG + cT
+    uint32_t sum = fadd(cA, fadd(cC, a.gt & 0x0F0F0F0Fu, one), one);   // the G+T nibble already holds cG + cT
     if (TOTALS) sum += a.tG + a.tT;
     err |= sum ^ a.pc;                                     // a passing base that is none of A,C,G,T (N, IUPAC, '=')
     uint32_t pass = a.pc;
     uint32_t ok;
     if (!tm.use_table) {
         // threshold of every position at once: two 16-bit lanes per multiply, no table, no divergence
-        uint32_t te = (((pass & 0x00FF00FFu) * tm.k + tm.r2) >> 8) & 0x00FF00FFu;
-        uint32_t to = (((pass >> 8) & 0x00FF00FFu) * tm.k + tm.r2) & 0xFF00FF00u;
-        ok = bytes_of(ge7u(best, te | to)) & bytes_of(nz7u(best));
+        uint32_t te = shr<8>((pass & 0x00FF00FFu) * tm.k + tm.r2, one) & 0x00FF00FFu;
+        uint32_t to = ((shr<8>(pass, one) & 0x00FF00FFu) * tm.k + tm.r2) & 0xFF00FF00u;
+        ok = bytes_of(ge7f(best, te | to, one)) & bytes_of(nz7f(best, one));
     } else {
         uint32_t split = nz7(best ^ pass);                 // not unanimous
-        ok = bytes_of(nz7u(best)) & ~bytes_of(split);       // unanimous and at least one passing read
+        ok = bytes_of(nz7f(best, one)) & ~bytes_of(split);  // unanimous and at least one passing read
         if (!unanimous_ok) ok = 0;
         while (split) {                                    // look the threshold up per position
             int k = (__ffs(split) - 1) >> 3;
@@ -196,11 +251,11 @@ __device__ __forceinline__ QuadOut quad_finish(const Quad &a, const uint8_t *thr
         }
     }
     o.code = sel(o.win, 0x0F0F0F0Fu, ok);
-    uint32_t two = bytes_of(ge7u(best, 0x02020202u));
-    uint32_t lone = bytes_of(nz7u(best)) & ~two;            // winner has exactly one supporter
-    uint32_t one_pass = lone & ~bytes_of(ge7u(pass, 0x02020202u));   // ... and it is the only passing read
+    uint32_t two = bytes_of(ge7c<0x02020202u>(best, one));
+    uint32_t lone = bytes_of(nz7f(best, one)) & ~two;       // winner has exactly one supporter
+    uint32_t one_pass = lone & ~bytes_of(ge7c<0x02020202u>(pass, one));   // ... and it is the only passing read
     o.single = lone & ~one_pass;                           // several passing reads, all different: needs a re-walk
-    o.qual = (two & 0x3C3C3C3Cu) | (cap60_lo(a.qany) & one_pass);     // 60 where two or more passing reads agree
+    o.qual = (two & 0x3C3C3C3Cu) | (cap60_lo(a.qany, one) & one_pass);    // 60 where two or more passing reads agree
     return o;
 }
 
@@ -231,6 +286,11 @@ __device__ __forceinline__ LaneRow load_lane_row(const uint8_t *__restrict__ pay
 __device__ __forceinline__ void split_row(const LaneRow &r, uint32_t sel[4], uint32_t q[4])
 {
     sel[0] = r.s.x; sel[1] = r.s.x >> 16; sel[2] = r.s.y; sel[3] = r.s.y >> 16;     // PRMT reads the low 16 bits
+    q[0] = r.q.x; q[1] = r.q.y; q[2] = r.q.z; q[3] = r.q.w;
+}
+__device__ __forceinline__ void split_row(const LaneRow &r, uint32_t sel[4], uint32_t q[4], uint32_t one)
+{
+    sel[0] = r.s.x; sel[1] = shr<16>(r.s.x, one); sel[2] = r.s.y; sel[3] = shr<16>(r.s.y, one);
     q[0] = r.q.x; q[1] = r.q.y; q[2] = r.q.z; q[3] = r.q.w;
 }
 
@@ -284,16 +344,16 @@ __device__ __forceinline__ void quad_pair(uint32_t nib1, uint32_t q1, uint32_t n
     uint32_t m1 = bytes_of(fadd(q1, 0x62626262u, one)), m2 = bytes_of(fadd(q2, 0x62626262u, one));   // q < 128, as in quad_add
     uint32_t b1 = nib1 & m1, b2 = nib2 & m2;
     err |= (((b1 | 0x80808080u) - 0x01010101u) & b1) | (((b2 | 0x80808080u) - 0x01010101u) & b2);
-    err |= (m1 & ~bytes_of(nz7u(b1))) | (m2 & ~bytes_of(nz7u(b2)));      // passing base that is none of A,C,G,T
-    uint32_t both = m1 & m2, differ = bytes_of(nz7u(b1 ^ b2));
+    err |= (m1 & ~bytes_of(nz7f(b1, one))) | (m2 & ~bytes_of(nz7f(b2, one)));      // passing base that is none of A,C,G,T
+    uint32_t both = m1 & m2, differ = bytes_of(nz7f(b1 ^ b2, one));
     uint32_t agree = both & ~differ, clash = both & differ;
-    uint32_t first = bytes_of(ge7u(b2, b1));                              // read 1 holds the earlier base
+    uint32_t first = bytes_of(ge7f(b2, b1, one));                         // read 1 holds the earlier base
     uint32_t win = sel(b1, b2, (m1 & ~m2) | (clash & first) | agree);
     uint32_t wq = sel(q1, q2, (m1 & ~m2) | (clash & first));
     uint32_t ok = (agree | (m1 ^ m2)) & (unanimous_ok ? 0xFFFFFFFFu : 0u);
     if (tie_ok) ok |= clash;
     code = sel(win, 0x0F0F0F0Fu, ok);
-    qual = sel(0x3C3C3C3Cu, cap60_lo(wq), agree) & (m1 | m2);
+    qual = sel(0x3C3C3C3Cu, cap60_lo(wq, one), agree) & (m1 | m2);
 }
 
 // vsize[row] = family size | flags
@@ -475,12 +535,12 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                         if (h != 0 && pos0 + 16 * h >= lpad) break;
                         LaneRow r1 = slot_row(c_slot, 0, h), r2 = slot_row(c_slot, 1, h);
                         uint32_t n1[4], q1[4], n2[4], q2[4], code[4], qual[4];
-                        split_row(r1, n1, q1);
-                        split_row(r2, n2, q2);
+                        split_row(r1, n1, q1, one);
+                        split_row(r2, n2, q2, one);
                         hi |= q1[0] | q1[1]; hi |= q1[2] | q1[3]; hi |= q2[0] | q2[1]; hi |= q2[2] | q2[3];
 #pragma unroll
                         for (int g = 0; g < 4; g++)
-                            quad_pair(expand_sel(n1[g]), q1[g], expand_sel(n2[g]), q2[g], tie_ok, unanimous_ok != 0, one, code[g], qual[g], ferr);
+                            quad_pair(expand_sel(n1[g], one), q1[g], expand_sel(n2[g], one), q2[g], tie_ok, unanimous_ok != 0, one, code[g], qual[g], ferr);
                         uint2 so;
                         uint4 qo;
                         join_row(code, qual, so, qo);
@@ -507,7 +567,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                                 for (int h = 0; h < CH; h++) {
                                     if (h == 0 || pos0 + 16 * h < lpad) {
                                         uint32_t sel4[4], q[4];
-                                        split_row(slot_row(c_slot, k, h), sel4, q);
+                                        split_row(slot_row(c_slot, k, h), sel4, q, one);
                                         hi |= q[0] | q[1]; hi |= q[2] | q[3];
 #pragma unroll
                                         for (int g = 0; g < 4; g++) quad_add(acc[h][g], sel4[g], q[g], one);
@@ -532,7 +592,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
                         uint32_t any_single = 0;
 #pragma unroll
                         for (int g = 0; g < 4; g++) {
-                            o[g] = quad_finish<FLUSH>(acc[h][g], thr, unanimous_ok != 0, tm, ferr);
+                            o[g] = quad_finish<FLUSH>(acc[h][g], thr, unanimous_ok != 0, tm, ferr, one);
                             any_single |= o[g].single;
                         }
                         if (any_single) {                  // lane-local: re-walk the rows for the lone supporters
