@@ -140,9 +140,10 @@ int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, 
 int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
                          uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
 
-/* Family grouping: an open-addressing table keyed by the exact family tuple (or, with
- * CCGPU_GROUP=sort in the environment at cc_create, key hash + stable radix sort + exact
- * boundaries); families in creation order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
+/* Family grouping by the exact family tuple: tile by tile in shared memory, with a small global table for the
+ * families at tile edges (CCGPU_GROUP=hash in the environment at cc_create: one table trip per read;
+ * CCGPU_GROUP=sort: key hash + stable radix sort + exact boundaries - same results); families in creation
+ * order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
  * construction (consensus_helper.py:438-475) and Counter(tag_dict.values())
  * (SSCS_maker.py:361). */
 int cc_group(cc_ctx *ctx);
@@ -163,7 +164,7 @@ int cc_dcs_join(cc_ctx *ctx);
 int cc_sc_rescue(cc_ctx *ctx);
 
 /* cc_group, cc_sscs_vote, cc_dcs_join and (if params.scorrect) cc_sc_rescue in one call
- * with one host synchronisation for the family count, one for the row counts and one at the end. */
+ * with one host synchronisation for the row counts (the family count stays on the device) and one at the end. */
 int cc_run(cc_ctx *ctx);
 
 /* Whole path from host buffers to host results: cc_load_reads + cc_run; afterwards
