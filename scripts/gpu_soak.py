@@ -1,6 +1,9 @@
 #!/usr/bin/env python
-"""One-off soak: many random small and medium batches through the GPU path against the oracle, each batch
-several times (the hash grouping places members in arrival order, so repeats exercise different orders).
+"""Soak: many random small and medium batches through the GPU path against the oracle, each batch several times
+(members land in a family's segment in arrival order, so repeats exercise different interleavings of the atomics),
+every third one also with its pairs shuffled (the all-through-the-table grouping pass) and through the compact
+upload.  compute-sanitizer is closed on this pool (its wrapper refuses to run), so this - bit-exact agreement with
+the CPU oracle over hundreds of cases and repeats, in every grouping mode (CCGPU_GROUP) - stands in for racecheck.
 python scripts/gpu_soak.py [first_seed] [count]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -28,11 +31,20 @@ with GpuConsensus(0) as eng:
         if faults:
             continue
         for rep in range(3):
-            got = eng.consensus(packed)
+            got = eng.consensus(packed, compact="auto" if rep == 2 else False)
             d = got.diff(exp)
             if d:
                 bad += 1
                 print("seed", seed, "rep", rep, "differs in", d)
                 break
+        if seed % 3 == 0 and packed.n >= 4:
+            order = np.random.default_rng(seed).permutation(packed.n // 2)
+            idx = np.stack([2 * order, 2 * order + 1], 1).reshape(-1)
+            mixed = pack.PackedReads(packed.fields[idx].copy(), packed.payload[idx].copy(), packed.lpad, packed.barcodes,
+                                     packed.dup_bc, packed.cigar_pairs, packed.rgs)
+            d = eng.consensus(mixed).diff(oracle.run(mixed, cutoff, scorrect))
+            if d:
+                bad += 1
+                print("seed", seed, "shuffled differs in", d)
 print("soak done:", count, "cases,", bad, "bad")
 sys.exit(1 if bad else 0)
