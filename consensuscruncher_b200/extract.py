@@ -76,6 +76,7 @@ def extract_pattern(read1, read2, outfile, bpattern, stats_path=None):
     spacer = "".join(bpattern[i] for i in s_index)
     counts = [np.zeros((plen, 5), np.int64), np.zeros((plen, 5), np.int64)]      # [mate][position][A,C,G,T,N]
     col = {c: i for i, c in enumerate(NUC)}
+    seen = [{}, {}]                              # prefix -> times seen; turned into per-position counts at the end
     total = bad_spacer = bad_barcode = good = 0
     with open("%s_barcode_R1.fastq" % outfile, "w") as o1, open("%s_barcode_R2.fastq" % outfile, "w") as o2:
         for (t1, s1, q1), (t2, s2, q2) in zip(read_fastq(read1), read_fastq(read2)):
@@ -87,9 +88,8 @@ def extract_pattern(read1, read2, outfile, bpattern, stats_path=None):
             if _NOT_ACGT.search(b1) or _NOT_ACGT.search(b2):
                 bad_barcode += 1
                 continue
-            for m, b in ((0, b1), (1, b2)):
-                for i, c in enumerate(b):
-                    counts[m][i, col[c]] += 1
+            seen[0][b1] = seen[0].get(b1, 0) + 1
+            seen[1][b2] = seen[1].get(b2, 0) + 1
             bc1 = "".join(b1[i] for i in b_index if i < len(b1))
             bc2 = "".join(b2[i] for i in b_index if i < len(b2))
             if "".join(b1[i] for i in s_index if i < len(b1)) == spacer and \
@@ -99,6 +99,10 @@ def extract_pattern(read1, read2, outfile, bpattern, stats_path=None):
                 o2.write("@%s|%s.%s/2\n%s\n+\n%s\n" % (id2, bc1, bc2, s2[plen:], q2[plen:]))
             else:
                 bad_spacer += 1
+    for m in (0, 1):
+        for b, k in seen[m].items():
+            for i, c in enumerate(b):
+                counts[m][i, col[c]] += k
     if stats_path:
         frames = [pd.DataFrame(c, index=np.arange(plen), columns=list(NUC)).apply(lambda x: x / x.sum(), axis=1)
                   for c in counts]
