@@ -109,7 +109,10 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
     const int tid = threadIdx.x;
     if (mode == 1 && !gtc[GTC_UNSORTED]) return;
     const bool nothing_local = mode == 1 || *asym != 0;   // one-sided duplex partnerships are resolved through the table
-    const uint64_t base = (uint64_t)blockIdx.x * GT_TILE;
+    // (first pass: one tile per CTA; the second pass is launched with a small grid, which costs nothing when
+    //  it has nothing to do, and walks the tiles)
+    for (uint64_t tile = blockIdx.x; tile * GT_TILE < n; tile += gridDim.x) {
+    const uint64_t base = tile * GT_TILE;
     const uint32_t here = (uint32_t)min((uint64_t)GT_TILE, n - base);
 
     for (int k = tid; k < (int)GT_HT; k += GT_THREADS) ht[k] = GT_EMPTY;
@@ -273,6 +276,8 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
     for (int k = 0; k < GT_PER; k++) {
         const uint32_t li = k * GT_THREADS + tid;
         if (li < here && lrep[k] != li) link[base + li] = lrep[k] | (rank[k] << LINK_RANK_SHIFT);
+    }
+    __syncthreads();                                       // the shared arrays are free for the next tile
     }
 }
 
@@ -514,9 +519,14 @@ tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t 
                   uint32_t *__restrict__ cursor, uint32_t *__restrict__ perm)
 {
     __shared__ uint32_t members[GT_TILE];                  // per representative: members besides itself, then its segment base
+    __shared__ uint32_t t_bits[GT_TILE / 32], t_rank[GT_TILE / 32];     // the tile's own words of the founders' bitmap
     const int tid = threadIdx.x;
     const uint64_t base = (uint64_t)blockIdx.x * GT_TILE;
     const uint32_t here = (uint32_t)min((uint64_t)GT_TILE, n - base);
+    if (tid < GT_TILE / 32 && (uint32_t)tid * 32 < here) {
+        t_bits[tid] = bitmap[(base >> 5) + tid];
+        t_rank[tid] = word_rank[(base >> 5) + tid];
+    }
     uint32_t lk[GP_PER], fam[GP_PER];
 #pragma unroll
     for (int k = 0; k < GP_PER; k++) {
@@ -524,9 +534,8 @@ tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t 
         members[li] = 0;
         lk[k] = li < here ? link[base + li] : 0u;
         fam[k] = 0;
-        // the representatives' trips to the bitmap start before the members are counted
-        if (li < here && (lk[k] & LINK_REP))
-            fam[k] = family_of_founder(bitmap, word_rank, (lk[k] & LINK_LOCAL) ? (uint32_t)(base + li) : aux[base + li]);
+        // an edge representative's trip to the founder's bitmap word starts before the members are counted
+        if (li < here && (lk[k] & LINK_REP) && !(lk[k] & LINK_LOCAL)) fam[k] = family_of_founder(bitmap, word_rank, aux[base + li]);
     }
     __syncthreads();
 #pragma unroll
@@ -538,8 +547,14 @@ tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t 
 #pragma unroll
     for (int k = 0; k < GP_PER; k++) {
         const uint32_t li = k * GP_THREADS + tid;
-        if (li < here && (lk[k] & LINK_REP))
+        if (li >= here || !(lk[k] & LINK_REP)) continue;
+        if (lk[k] & LINK_LOCAL) {
+            // the tile holds the whole family: its segment is this group's, nobody else asks for room in it
+            const uint32_t c = t_rank[li >> 5] + __popc(t_bits[li >> 5] & ((1u << (li & 31)) - 1u));
+            members[li] = cursor[c];
+        } else {
             members[li] = atomicAdd(&cursor[fam[k]], members[li] + 1u);     // room for the tile's whole group, one atomic
+        }
     }
     __syncthreads();
 #pragma unroll
