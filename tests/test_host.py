@@ -214,3 +214,31 @@ def test_compact_upload_format_round_trips():
     packed = synth.generate(seed=9, n_molecules=50, L=64).to_packed()
     packed.fields["mpos"][0] += 1
     assert pack.to_pairs(packed.fields) is None and pack.to_compact(packed) is None
+
+
+@pytest.mark.parametrize("wl,total", [("c3", 60_000), ("c4", 120_000)])
+def test_cytoband_sharded_dataset_is_the_same_whoever_makes_it(wl, total):
+    """workloads.py: band b's reads depend on (seed, b) only, ranks own disjoint bands, and the generator's own
+    prediction of the stage counters equals what the oracle computes (CPU tensors; the GPU tests repeat it at size)."""
+    pytest.importorskip("torch")
+    from consensuscruncher_b200 import workloads
+    from oracle import oracle
+    pl = workloads.plan(wl, total // 2, seed=5)
+    assert pl.total_pairs == total // 2 and len(pl.bands) == 863
+    whole, iw = workloads.generate_shard(pl, 0, 1, "cpu")
+    res = oracle.run(whole.to_packed(), 0.7, True)
+    assert (res.stats[:9] == iw["stats"][:9]).all()
+    assert (np.bincount(res.fam_size, minlength=65536) == iw["hist"]).all()
+    owner = pl.owners(3)
+    parts = [workloads.generate_shard(pl, r, 3, "cpu") for r in range(3)]
+    assert sorted(b for _, ip in parts for b in ip["bands"]) == iw["bands"]
+    assert all(owner[b] == r for r, (_, ip) in enumerate(parts) for b in ip["bands"])
+    assert (sum(ip["stats"] for _, ip in parts) == iw["stats"]).all() and (sum(ip["hist"] for _, ip in parts) == iw["hist"]).all()
+    f = whole.fields.numpy()
+    for part, ip in parts:                                   # a rank's reads are exactly its bands' reads of the whole set
+        fp = part.fields.numpy()
+        keep = np.zeros(f.shape[0], bool)
+        for b in ip["bands"]:
+            tid, lo, hi = pl.regions[b]
+            keep |= (f[:, 2] == tid) & (f[:, 3] >= lo) & (f[:, 3] < hi) & (f[:, 5] >= lo) & (f[:, 5] < hi)
+        assert np.array_equal(f[keep], fp)
