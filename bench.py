@@ -791,7 +791,15 @@ def main():
                       "dcs_sc": int(stats_once[7])},
             "collective": {"call": "cc_stats_allreduce (libccgpu.so -> ncclAllReduce, int64 x %d, once per run)" % (16 + 65536),
                            "comm": eng.comm_info()},
-            "sharded": sharded or None, "sweep_c5": sweep}
+            "sharded": sharded or None, "sweep_c5": sweep,
+            "definitions": {
+                "value": "device-resident: the batch is in HBM when the timed region starts; whole path, CUDA events, max over ranks",
+                "e2e": "the same path through the C ABI from pinned host buffers, every result array read back, copies timed; "
+                       "this is the number to set against the CPU arm (bench.py --impl reference)",
+                "cpu_baseline": "oracle/cc_oracle.c, the builder's C restatement of the reference's algorithm (kind 'port'), pinned "
+                                "against outputs of the unmodified reference; the reference's own Python runs ~227x slower per "
+                                "core (BASELINE.md section 2), so ratios against this arm understate the ratio against the reference",
+                "not_included": "BAM decode / pack and record assembly / BAM writing on the host (the consensus command; DESIGN.md section 8)"}}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -431,11 +431,11 @@ int do_group_tile(cc_ctx *ctx)
     TRY(phase_begin(ctx, CC_PH_HASH));
     CK(cudaMemsetAsync(gtc, 0, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t), ctx->stream));
     if (ctx->n_bc) LAUNCH(dup_symmetry_kernel, blocks_for(ctx->n_bc, 256), 256, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM);
-    LAUNCH(tile_local_kernel, (unsigned)tiles, GT_THREADS, ctx->fields, n, 0, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM, gtc, stretch,
+    LAUNCH(tile_local_kernel<0>, (unsigned)tiles, GT_THREADS, ctx->fields, n, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM, gtc, stretch,
            link, aux, stash, edge_list, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_reads), ptr<uint32_t>(ctx->word_start));
     // input out of order (flag raised on the device): the same tiles again, every family through the table
     LAUNCH(tile_redo_kernel, 1, 1, gtc);
-    LAUNCH(tile_local_kernel, (unsigned)std::min<uint64_t>(tiles, 148 * 4), GT_THREADS, ctx->fields, n, 1, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM, gtc, stretch,
+    LAUNCH(tile_local_kernel<1>, (unsigned)std::min<uint64_t>(tiles, 148 * 4), GT_THREADS, ctx->fields, n, ctx->dup_bc, ctx->n_bc, ctr + CT_ASYM, gtc, stretch,
            link, aux, stash, edge_list, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_reads), ptr<uint32_t>(ctx->word_start));
     LAUNCH(table_prepare_kernel, 148 * 4, 256, gtc, table, slots);
     LAUNCH(edge_insert_kernel, 148 * 8, 256, ctx->fields, edge_list, gtc, table, stash, aux);

@@ -91,9 +91,11 @@ __device__ __forceinline__ uint32_t tile_hash(const uint4 &a, const uint4 &b)
     return h & (GT_HT - 1);
 }
 
-// mode 0: first pass.  mode 1: only if the first pass found the input out of order; then nothing is local.
-__global__ void __launch_bounds__(GT_THREADS)
-tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const uint32_t *__restrict__ dup_bc, uint32_t n_bc,
+// MODE 0: first pass, one tile per CTA.  MODE 1: only if the first pass found the input out of order; then nothing is
+// local; launched with a small grid that walks the tiles, so it costs nothing when it has nothing to do.
+template <int MODE>
+__global__ void __launch_bounds__(GT_THREADS, 3)
+tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t *__restrict__ dup_bc, uint32_t n_bc,
                   const uint32_t *__restrict__ asym, uint32_t *__restrict__ gtc, uint32_t *__restrict__ stretch,
                   uint32_t *__restrict__ link, uint32_t *__restrict__ aux, uint32_t *__restrict__ stash,
                   uint32_t *__restrict__ edge_list, uint32_t *__restrict__ bitmap, uint32_t *__restrict__ word_reads,
@@ -107,11 +109,11 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
     __shared__ int2 neighbour[2];
     __shared__ uint32_t bm[GT_TILE / 32], bm_reads[GT_TILE / 32], bm_sscs[GT_TILE / 32];   // founders known here, per bitmap word
     const int tid = threadIdx.x;
+    constexpr int mode = MODE;
     if (mode == 1 && !gtc[GTC_UNSORTED]) return;
     const bool nothing_local = mode == 1 || *asym != 0;   // one-sided duplex partnerships are resolved through the table
-    // (first pass: one tile per CTA; the second pass is launched with a small grid, which costs nothing when
-    //  it has nothing to do, and walks the tiles)
-    for (uint64_t tile = blockIdx.x; tile * GT_TILE < n; tile += gridDim.x) {
+    uint64_t tile = blockIdx.x;
+    do {
     const uint64_t base = tile * GT_TILE;
     const uint32_t here = (uint32_t)min((uint64_t)GT_TILE, n - base);
 
@@ -277,8 +279,8 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, int mode, const 
         const uint32_t li = k * GT_THREADS + tid;
         if (li < here && lrep[k] != li) link[base + li] = lrep[k] | (rank[k] << LINK_RANK_SHIFT);
     }
-    __syncthreads();                                       // the shared arrays are free for the next tile
-    }
+    if (MODE == 1) __syncthreads();                        // the shared arrays are free for the next tile
+    } while (MODE == 1 && (tile += gridDim.x) * GT_TILE < n);
 }
 
 // start the second pass from an empty list (only if the first pass found the input out of order)

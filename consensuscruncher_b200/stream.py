@@ -119,7 +119,7 @@ def _faulty_pairs(engine, n_reads):
     return np.unique(np.flatnonzero(bad_read) // 2)
 
 
-def run_chunk(engine, chunk, compact="auto", max_rounds=8):
+def run_chunk(engine, chunk, compact=False, max_rounds=8):
     """One chunk on one context -> (result, kept pair mask or None).  Pairs outside the domain are set aside."""
     keep = None
     cur = chunk
@@ -142,8 +142,10 @@ def run_chunk(engine, chunk, compact="auto", max_rounds=8):
     raise DomainError("pairs outside the domain could not be separated from the rest")
 
 
-def consensus_chunked(packed, engines, regions=None, max_reads=20_000_000, compact="auto", log=None):
-    """The whole batch through `engines` (one GpuConsensus per GPU).  Returns (result, packed') where packed'
+def consensus_chunked(packed, engines, regions=None, max_reads=20_000_000, compact=False, log=None):
+    """The whole batch through `engines` (one GpuConsensus per GPU).  `compact`: upload format (False = plain rows; the
+    compact formats pay off when the host side packs them natively - numpy's packing costs more than the link saves).
+    Returns (result, packed') where packed'
     is `packed` without the pairs that were set aside (their records are added to packed'.bad)."""
     cuts = chunk_bounds(packed, regions, max_reads)
     chunks = [take(packed, a, b) for a, b in zip(cuts, cuts[1:])]

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Full ncu capture of every kernel of ONE step of the bench command (after warm-up): bash scripts/gpu_ncu_step.sh <tag> [skip] [count]
-# (22 launches per step with the tile grouping: 3 warm-up steps are skipped by default)
-TAG=${1:-r2}; SKIP=${2:-66}; CNT=${3:-22}
+# (21 launches per step with the tile grouping: 3 warm-up steps are skipped by default)
+TAG=${1:-r2}; SKIP=${2:-63}; CNT=${3:-21}
 OUT=gpurun_out; mkdir -p $OUT
 CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --sharded none --sweep none"
 $CMD > $OUT/plain_step_$TAG.log 2>&1 &&
