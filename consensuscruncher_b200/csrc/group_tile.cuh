@@ -268,7 +268,7 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t *
     __syncthreads();
     e = 0;
     for (uint32_t x = tid; x < reps; x += GT_THREADS, e++)
-        if (edge_at[e] != GT_EMPTY) edge_list[edge_base + edge_at[e]] = (uint32_t)(base + rep_list[x]);
+        if (edge_at[e] != GT_EMPTY) { CC_CHECK(edge_base + edge_at[e] < n); edge_list[edge_base + edge_at[e]] = (uint32_t)(base + rep_list[x]); }
     if (tid < GT_TILE / 32 && (uint32_t)tid * 32 < here) {     // edge founders are added by edge_mark_kernel
         bitmap[(base >> 5) + tid] = bm[tid];
         word_reads[(base >> 5) + tid] = bm_reads[tid];
@@ -311,6 +311,7 @@ edge_insert_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict_
     const uint64_t mask = gtc[GTC_MASK];
     for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < total; x += gridDim.x * blockDim.x) {
         const uint32_t i = edge_list[x];
+        CC_CHECK((i & 1u) < 2u && x < total);
         const Rec r = load_rec(fields, i);
         const uint32_t mine = stash[i];                          // group_cnt of the tile's group
         bool mixed = !(mine & 1u);
@@ -329,6 +330,7 @@ edge_insert_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict_
             }
             slot = (slot + 1) & mask;
         }
+        CC_CHECK(slot <= mask);
         atomicSub(&table[slot].cnt, (~mine) & ~1u);              // 2 x members of the tile's group
         if (mixed) atomicAnd(&table[slot].cnt, ~1u);
         aux[i] = (uint32_t)slot;
@@ -487,6 +489,7 @@ tile_family_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t 
             sscs_list[row] = c;
         }
         sscs_row[c] = row;
+        CC_CHECK(c < n && start < n && (uint64_t)start + size <= n && i < n);
         tmpl[c] = (uint32_t)i;
         fam_size[c] = size;
         fam_start[c] = start;
@@ -564,6 +567,7 @@ tile_place_kernel(uint64_t n, const uint32_t *__restrict__ link, const uint32_t 
         const uint32_t li = k * GP_THREADS + tid;
         if (li >= here) continue;
         const uint32_t at = (lk[k] & LINK_REP) ? members[li] : members[lk[k] & (GT_TILE - 1)] + (lk[k] >> LINK_RANK_SHIFT);
+        CC_CHECK(at < n);
         perm[at] = (uint32_t)(base + li);
     }
 }
@@ -588,6 +592,7 @@ tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ 
     int32_t found = -1;
     if (__ldg(&link[first]) & LINK_LOCAL) {
         const uint32_t p = __ldg(&aux[first]);
+        CC_CHECK(p == NO_ID || p < (uint32_t)GT_TILE);
         if (p != NO_ID) found = (int32_t)family_of_founder(bitmap, word_rank, (first & ~(uint32_t)(GT_TILE - 1)) + p);
     } else {
         Rec r = load_rec(fields, first);
@@ -606,6 +611,7 @@ tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ 
             }
         }
     }
+    CC_CHECK(found < (int32_t)n_fam);
     partner[c] = found;
     if (symmetric && found >= 0) partner[found] = (int32_t)c;
     }

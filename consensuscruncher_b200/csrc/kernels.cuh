@@ -6,6 +6,16 @@
 
 #include "scan.cuh"
 
+// Bounds checks of our own (compute-sanitizer is not available on the GPU pool): a library built with
+// -DCCGPU_CHECKS traps (device assert -> the next CUDA call fails) when a kernel is about to index outside an
+// array; scripts/gpu_checks.sh runs the parity suite and the soak cases through such a build.
+#ifdef CCGPU_CHECKS
+#include <cassert>
+#define CC_CHECK(cond) assert(cond)
+#else
+#define CC_CHECK(cond) ((void)0)
+#endif
+
 namespace ccgpu {
 
 constexpr uint32_t NO_ID = 0xFFFFFFFFu;
@@ -420,6 +430,7 @@ classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__res
         const int32_t p = par[k];
         // a partner that has another partner (undotted barcode of odd length): which strand leads, and
         // whether the reference survives, depends on file order (DCS_maker.py:231-247) - outside the domain
+        CC_CHECK(p < (int32_t)n_fam);
         if (p >= 0 && __ldg(&partner[p]) != (int32_t)c) atomicAdd(one_sided, 1u);
         const bool p_big = p >= 0 && __ldg(&fam_size[p]) >= 2;
         const bool dcs = big && p_big && c < (uint32_t)p;
@@ -483,6 +494,7 @@ classify_scan_kernel(const uint32_t *__restrict__ fam_size, const int32_t *__res
     for (int k = 0; k < CLS_ITEMS; k++) {
         const uint32_t c = base + k;
         o_dcs[k] = -1; o_corr[k] = -1; o_x[k] = -1;
+        CC_CHECK(r_dcs <= n_fam && r_corr <= n_fam && r_x <= n_fam);
         if ((f_dcs >> k) & 1u) { dcs_list[r_dcs] = c; o_dcs[k] = (int32_t)r_dcs++; }
         if ((f_corr >> k) & 1u) { corr_list[r_corr] = c; o_corr[k] = (int32_t)r_corr++; }
         if ((f_x >> k) & 1u) { dcssc_list[r_x] = c; o_x[k] = (int32_t)r_x++; }

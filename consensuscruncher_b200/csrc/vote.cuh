@@ -523,6 +523,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
             row = s_row[i];
         }
         uint8_t *out = out_rows + (uint64_t)row * stride;
+        CC_CHECK(row < n_rows || n == 0);
 
         if (n != 0) {
             uint32_t hi = 0, ferr = 0;                     // OR of the family's quality words; its error bits
@@ -749,6 +750,7 @@ rescue16_kernel(RowSources src, const uint32_t *__restrict__ corr_list, const in
     if (row >= n_rows) return;
     uint32_t c = corr_list[row];
     uint32_t p = (uint32_t)partner[c];
+    CC_CHECK((int32_t)p >= 0 && (src.fam_size[p] < 2 || src.sscs_row[p] >= 0));
     const uint8_t *mine = src.payload + (uint64_t)src.tmpl[c] * src.stride;
     const uint8_t *other = src.fam_size[p] >= 2 ? src.sscs_rows + (uint64_t)src.sscs_row[p] * src.stride
                                                 : src.payload + (uint64_t)src.tmpl[p] * src.stride;
@@ -769,6 +771,7 @@ duplex16_kernel(RowSources src, const uint32_t *__restrict__ lead_list, const in
     if (row >= n_rows) return;
     uint32_t c = lead_list[row];
     uint32_t p = (uint32_t)partner[c];
+    CC_CHECK((int32_t)p >= 0);
     auto row_of = [&](uint32_t x) -> const uint8_t * {
         if (!after_sc || src.fam_size[x] >= 2) return src.sscs_rows + (uint64_t)src.sscs_row[x] * src.stride;
         return src.corr_rows + (uint64_t)src.corr_row[x] * src.stride;
