@@ -271,17 +271,54 @@ std::vector<uint8_t> header_bytes(const ccp_bam *b, bool coordinate)
 // then the 0xFF00-byte blocks of all files are deflated by one pool, then files and indexes are written.
 bool write_bams(const ccp_bam *b, std::vector<FileJob> &jobs, int threads, std::string &err)
 {
+    // records are encoded in pieces of 16 k by the whole pool (one task per file would leave the pool waiting for
+    // the largest file), then every file's pieces are stitched behind its header
+    const bool timing = getenv("CCP_TIMING") != nullptr;
+    auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "write_bams %-26s %.3f s\n", what, std::chrono::duration<double>(now - t_start).count());
+        t_start = now;
+    };
+    constexpr size_t PIECE = 16384;
+    struct Piece { uint32_t file; size_t first, last; std::vector<uint8_t> bytes; std::vector<uint64_t> off; std::string err; };
+    std::vector<Piece> pieces;
+    for (size_t j = 0; j < jobs.size(); j++)
+        for (size_t a = 0; a < jobs[j].recs.size(); a += PIECE)
+            pieces.push_back(Piece{(uint32_t)j, a, std::min(a + PIECE, jobs[j].recs.size()), {}, {}, {}});
+    parallel_for(pieces.size(), threads, [&](size_t x) {
+        Piece &pc = pieces[x];
+        const FileJob &f = jobs[pc.file];
+        pc.off.resize(pc.last - pc.first);
+        for (size_t i = pc.first; i < pc.last && pc.err.empty(); i++) {
+            pc.off[i - pc.first] = pc.bytes.size();
+            encode_record(*f.recs[i], pc.bytes, pc.err);
+        }
+    });
+    lap("encode");
+    std::vector<size_t> first_piece(jobs.size() + 1, pieces.size());
+    for (size_t x = pieces.size(); x-- > 0;) first_piece[pieces[x].file] = x;
+    for (size_t j = jobs.size(); j-- > 0;) first_piece[j] = std::min(first_piece[j], first_piece[j + 1]);
     parallel_for(jobs.size(), threads, [&](size_t j) {
         FileJob &f = jobs[j];
         f.stream = header_bytes(b, f.coordinate);
         f.rec_off.resize(f.recs.size() + 1);
-        for (size_t i = 0; i < f.recs.size() && f.err.empty(); i++) {
-            f.rec_off[i] = f.stream.size();
-            encode_record(*f.recs[i], f.stream, f.err);
+        size_t total = f.stream.size();
+        for (size_t x = first_piece[j]; x < first_piece[j + 1]; x++) total += pieces[x].bytes.size();
+        f.stream.reserve(total);
+        for (size_t x = first_piece[j]; x < first_piece[j + 1] && f.err.empty(); x++) {
+            Piece &pc = pieces[x];
+            if (!pc.err.empty()) { f.err = pc.err; break; }
+            const uint64_t at = f.stream.size();
+            for (size_t i = pc.first; i < pc.last; i++) f.rec_off[i] = at + pc.off[i - pc.first];
+            f.stream.insert(f.stream.end(), pc.bytes.begin(), pc.bytes.end());
+            std::vector<uint8_t>().swap(pc.bytes);
         }
         f.rec_off[f.recs.size()] = f.stream.size();
         f.comp.resize((f.stream.size() + BGZF_BLOCK - 1) / BGZF_BLOCK);
     });
+    lap("stitch");
     std::vector<std::pair<uint32_t, uint32_t>> blocks;       // (file, block) over all files
     for (size_t j = 0; j < jobs.size(); j++) {
         if (!jobs[j].err.empty()) { err = jobs[j].err; return false; }
@@ -294,6 +331,7 @@ bool write_bams(const ccp_bam *b, std::vector<FileJob> &jobs, int threads, std::
         if (!deflate_block(f.stream.data() + a, len, 6, f.comp[blocks[x].second])) ok = false;
     });
     if (!ok) { err = "deflate failed"; return false; }
+    lap("deflate");
     parallel_for(jobs.size(), threads, [&](size_t j) {
         FileJob &f = jobs[j];
         FILE *fh = fopen(f.path.c_str(), "wb");

@@ -523,7 +523,7 @@ vote_small_kernel(const uint8_t *__restrict__ payload, uint32_t stride, uint32_t
             row = s_row[i];
         }
         uint8_t *out = out_rows + (uint64_t)row * stride;
-        CC_CHECK(row < n_rows || n == 0);
+        CC_CHECK(n == 0 || row_list != nullptr || row < n_rows);       // (with a row list, n_rows counts the list)
 
         if (n != 0) {
             uint32_t hi = 0, ferr = 0;                     // OR of the family's quality words; its error bits
