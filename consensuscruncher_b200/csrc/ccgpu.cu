@@ -178,6 +178,9 @@ int ensure(cc_ctx *ctx, DevBuf &b, size_t bytes)
     if (bytes == 0) bytes = 256;
     if (b.cap >= bytes) return CC_OK;
     if (b.p) {
+        // a buffer that has to grow grows by a quarter more than asked, so that a stream of slowly growing
+        // batches (region chunks of one sample) does not pay the synchronise + free + allocate every time
+        bytes += bytes / 4;
         CK(cudaStreamSynchronize(ctx->stream));
         CK(cudaFree(b.p));
         ctx->dev_bytes -= b.cap;
@@ -762,7 +765,7 @@ RowSources sources(cc_ctx *ctx)
     return s;
 }
 
-inline uint32_t row_groups(const cc_ctx *ctx) { return (ctx->lpad + 15) / 16; }   // threads per row, 16 positions each
+inline uint32_t row_groups(const cc_ctx *ctx) { return ((ctx->lpad + 15) / 16 + DUPLEX_CHUNKS - 1) / DUPLEX_CHUNKS; }   // threads per row
 
 // One pool holds every duplex row: [0, n_dcs) the SSCS-SSCS pairs (DCS_maker's first run; the
 // second run reproduces them unchanged), [n_dcs, n_dcs + n_extra) the pairs of the second run

@@ -739,6 +739,22 @@ __device__ __forceinline__ void agree_lane(const uint8_t *__restrict__ r1, const
     for (uint32_t x = half + lpad + lane * 4; x < stride; x += lanes * 4) *reinterpret_cast<uint32_t *>(out + x) = 0;
 }
 
+// threads of the row kernels below take DUPLEX_CHUNKS chunks of 16 positions each (`lanes` = threads per row)
+#ifndef DUPLEX_CHUNKS_CFG
+#define DUPLEX_CHUNKS_CFG 1
+#endif
+constexpr uint32_t DUPLEX_CHUNKS = DUPLEX_CHUNKS_CFG;
+
+template <bool SC>
+__device__ __forceinline__ void agree_chunks(const uint8_t *__restrict__ r1, const uint8_t *__restrict__ r2, uint8_t *__restrict__ out,
+                                             uint32_t lpad, uint32_t stride, uint32_t lane)
+{
+    const uint32_t chunks = (lpad + 15) / 16;
+#pragma unroll
+    for (uint32_t h = 0; h < DUPLEX_CHUNKS; h++)
+        if (DUPLEX_CHUNKS * lane + h < chunks) agree_lane<SC>(r1, r2, out, lpad, stride, DUPLEX_CHUNKS * lane + h, chunks);
+}
+
 // singleton rescue: row r <-> singleton family corr_list[r]; partner SSCS consensus if the
 // partner family has one, else the partner singleton's original read
 __global__ void __launch_bounds__(256)
@@ -754,7 +770,7 @@ rescue16_kernel(RowSources src, const uint32_t *__restrict__ corr_list, const in
     const uint8_t *mine = src.payload + (uint64_t)src.tmpl[c] * src.stride;
     const uint8_t *other = src.fam_size[p] >= 2 ? src.sscs_rows + (uint64_t)src.sscs_row[p] * src.stride
                                                 : src.payload + (uint64_t)src.tmpl[p] * src.stride;
-    agree_lane<true>(mine, other, out_rows + (uint64_t)row * src.stride, lpad, src.stride, lane, lanes);
+    agree_chunks<true>(mine, other, out_rows + (uint64_t)row * src.stride, lpad, src.stride, lane);
 }
 
 // DCS (after_sc = 0: both rows are SSCS consensus) or DCS over SSCS + corrected singletons
@@ -776,7 +792,7 @@ duplex16_kernel(RowSources src, const uint32_t *__restrict__ lead_list, const in
         if (!after_sc || src.fam_size[x] >= 2) return src.sscs_rows + (uint64_t)src.sscs_row[x] * src.stride;
         return src.corr_rows + (uint64_t)src.corr_row[x] * src.stride;
     };
-    agree_lane<false>(row_of(c), row_of(p), out_rows + (uint64_t)row * src.stride, lpad, src.stride, lane, lanes);
+    agree_chunks<false>(row_of(c), row_of(p), out_rows + (uint64_t)row * src.stride, lpad, src.stride, lane);
     if (lane == 0) {
         o_mapq[row] = (uint8_t)pair_mode(fam_mapq[c], fam_mapq[p], false);
         o_tlen[row] = (int32_t)pair_mode((uint32_t)fam_tlen[c], (uint32_t)fam_tlen[p], false);
