@@ -157,6 +157,8 @@ def build_parser(config_path=None):
     p.add_argument("--cleanup", choices=["True", "False"], help="remove intermediate files")
     p.add_argument("--device", type=int, default=0, help="first CUDA device")
     p.add_argument("--gpus", type=int, default=1, help="GPUs that take the region chunks in turn (devices --device ...)")
+    p.add_argument("--compression", type=int, default=None, choices=range(0, 10), metavar="0-9",
+                   help="zlib level of the output BAMs (default 6, like samtools; lower is faster, same records)")
     p.add_argument("--chunk-reads", type=int, default=20_000_000,
                    help="reads per chunk of consecutive bed regions (bounds the device memory a sample needs)")
     p.set_defaults(**defaults)
@@ -192,6 +194,8 @@ def main(argv=None):
             cons_p.error("no -b/--bedfile given and hg19_cytoBand.txt is not installed; "
                          "pass -b FILE or -b False")
     from .engine import GpuError
+    if args.compression is not None:
+        os.environ["CCP_DEFLATE_LEVEL"] = str(args.compression)
     try:
         run_consensus(args.bam, args.c_output, cutoff=float(args.cutoff), scorrect=str(args.scorrect) != "False",
                       bedfile=bedfile, bdelim=args.bdelim, cleanup=str(args.cleanup) == "True", device=args.device,

@@ -325,10 +325,14 @@ bool write_bams(const ccp_bam *b, std::vector<FileJob> &jobs, int threads, std::
         for (size_t k = 0; k < jobs[j].comp.size(); k++) blocks.emplace_back((uint32_t)j, (uint32_t)k);
     }
     std::atomic<bool> ok{true};
+    // zlib level of the output BAMs: 6 like samtools / pysam unless CCP_DEFLATE_LEVEL says otherwise (the records
+    // are the same; at level 6 the deflate is most of the command's wall time once the GPU has done its part)
+    int level = 6;
+    if (const char *e = getenv("CCP_DEFLATE_LEVEL")) { int v = atoi(e); if (v >= 0 && v <= 9) level = v; }
     parallel_for(blocks.size(), threads, [&](size_t x) {
         FileJob &f = jobs[blocks[x].first];
         size_t a = (size_t)blocks[x].second * BGZF_BLOCK, len = std::min(BGZF_BLOCK, f.stream.size() - a);
-        if (!deflate_block(f.stream.data() + a, len, 6, f.comp[blocks[x].second])) ok = false;
+        if (!deflate_block(f.stream.data() + a, len, level, f.comp[blocks[x].second])) ok = false;
     });
     if (!ok) { err = "deflate failed"; return false; }
     lap("deflate");
