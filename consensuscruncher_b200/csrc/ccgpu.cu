@@ -577,7 +577,8 @@ int do_join_index(cc_ctx *ctx)
         // (the barcode swap's symmetry was established before the tiles were grouped)
         LAUNCH(tile_join_kernel, (unsigned)std::min<uint64_t>(blocks_for(bound, 256), 148 * 32), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), ctr + CT_NFAM, ctx->dup_bc, ctx->n_bc,
                ptr<GroupSlot>(ctx->gtable), ptr<uint32_t>(ctx->gt_state), ptr<uint32_t>(ctx->key_a), ptr<uint32_t>(ctx->key_b),
-               ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<int32_t>(ctx->partner), ctr + CT_ASYM);
+               ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), ptr<int32_t>(ctx->partner), ctr + CT_ASYM,
+               ptr<uint16_t>(ctx->fam_flag));
         TRY(phase_end(ctx, CC_PH_JOIN));
         return do_classify(ctx);
     }

@@ -117,7 +117,9 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t *
     const uint64_t base = tile * GT_TILE;
     const uint32_t here = (uint32_t)min((uint64_t)GT_TILE, n - base);
 
-    for (int k = tid; k < (int)GT_HT; k += GT_THREADS) ht[k] = GT_EMPTY;
+    static_assert(GT_HT == 4 * GT_THREADS || GT_HT % (4 * GT_THREADS) == 0, "the shared table is cleared 16 bytes at a time");
+    for (int k = tid; k < (int)GT_HT / 4; k += GT_THREADS)
+        reinterpret_cast<uint4 *>(ht)[k] = make_uint4(GT_EMPTY, GT_EMPTY, GT_EMPTY, GT_EMPTY);
     if (tid == 0) { n_reps = 0; n_edge = 0; }
     if (tid < GT_TILE / 32) { bm[tid] = 0; bm_reads[tid] = 0; bm_sscs[tid] = 0; }
     uint32_t h[GT_PER];
@@ -213,9 +215,18 @@ tile_local_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t *
             rank[k] = 1 + (atomicAdd(&members[lrep[k]], 1u) & ~GT_MIXED);
             // every member is compared with its representative: no difference anywhere = uniform mode fields
             if (key_b[li].z != key_b[lrep[k]].z || key_b[li].w != key_b[lrep[k]].w) atomicOr(&members[lrep[k]], GT_MIXED);
-        } else {
-            rep_list[atomicAdd(&n_reps, 1u)] = (uint16_t)li;
         }
+    }
+    // the representatives queue up: one addition to the shared counter per warp, not per representative
+#pragma unroll
+    for (int k = 0; k < GT_PER; k++) {
+        const uint32_t li = k * GT_THREADS + tid;
+        const bool is_rep = li < here && lrep[k] == li;
+        const uint32_t reps_here = __ballot_sync(0xffffffffu, is_rep);
+        uint32_t at = 0;
+        if ((tid & 31) == 0 && reps_here) at = atomicAdd(&n_reps, (uint32_t)__popc(reps_here));
+        at = __shfl_sync(0xffffffffu, at, 0);
+        if (is_rep) rep_list[at + __popc(reps_here & ((1u << (tid & 31)) - 1u))] = (uint16_t)li;
     }
     __syncthreads();
 
@@ -464,46 +475,60 @@ tile_family_kernel(const uint4 *__restrict__ fields, uint64_t n, const uint32_t 
     small_hist[threadIdx.x] = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    // grid-stride over words (a warp per word): a few CTAs per SM, so the shared histogram is flushed rarely
+    // grid-stride over words, a warp takes FW words at a time and issues all their loads before it uses any:
+    // the kernel is bound by the latency of the founders' two gathers (counter word, template record), not by bytes
+    constexpr int FW = 4;
     const uint64_t words = (n + 31) / 32;
-    for (uint64_t w = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += ((uint64_t)gridDim.x * blockDim.x) >> 5) {
-        const uint32_t word = __ldg(&bitmap[w]);
-        if (word == 0) continue;
-        const bool founder = (word >> lane) & 1u;
-        const uint64_t i = w * 32 + lane;
-        uint32_t cnt = 0, size = 0;
-        if (founder) { cnt = founder_cnt[i]; size = (~cnt) >> 1; }
-        uint32_t incl = size;                                     // starts of the word's families: prefix of their sizes
+    const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t w0 = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * FW; w0 < words; w0 += warps * FW) {
+        uint32_t word[FW], cnt[FW];
+        uint4 meta[FW];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
+        for (int k = 0; k < FW; k++) word[k] = w0 + k < words ? __ldg(&bitmap[w0 + k]) : 0u;
+#pragma unroll
+        for (int k = 0; k < FW; k++) {
+            const bool founder = (word[k] >> lane) & 1u;
+            const uint64_t i = (w0 + k) * 32 + lane;
+            cnt[k] = founder ? founder_cnt[i] : 0xFFFFFFFFu;
+            meta[k] = founder ? __ldg(&fields[2 * i + 1]) : make_uint4(0, 0, 0, 0);
         }
-        const uint32_t big = __ballot_sync(0xffffffffu, size >= 2);
-        if (!founder) continue;
-        const uint32_t c = __ldg(&word_rank[w]) + __popc(word & ((1u << lane) - 1u));
-        const uint32_t start = __ldg(&word_start[w]) + incl - size;
-        int32_t row = -1;                                          // families of two or more reads own a consensus row
-        if (size >= 2) {
-            row = (int32_t)(__ldg(&word_sscs_start[w]) + __popc(big & ((1u << lane) - 1u)));
-            sscs_list[row] = c;
+#pragma unroll
+        for (int k = 0; k < FW; k++) {
+            if (word[k] == 0) continue;
+            const uint64_t w = w0 + k, i = w * 32 + lane;
+            const bool founder = (word[k] >> lane) & 1u;
+            const uint32_t size = (~cnt[k]) >> 1;
+            uint32_t incl = size;                                 // starts of the word's families: prefix of their sizes
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            const uint32_t big = __ballot_sync(0xffffffffu, size >= 2);
+            if (!founder) continue;
+            const uint32_t c = __ldg(&word_rank[w]) + __popc(word[k] & ((1u << lane) - 1u));
+            const uint32_t start = __ldg(&word_start[w]) + incl - size;
+            int32_t row = -1;                                      // families of two or more reads own a consensus row
+            if (size >= 2) {
+                row = (int32_t)(__ldg(&word_sscs_start[w]) + __popc(big & ((1u << lane) - 1u)));
+                sscs_list[row] = c;
+            }
+            sscs_row[c] = row;
+            CC_CHECK(c < n && start < n && (uint64_t)start + size <= n && i < n);
+            tmpl[c] = (uint32_t)i;
+            fam_size[c] = size;
+            fam_start[c] = start;
+            cursor[c] = start;
+            is_sscs[c] = size >= 2 ? ((cnt[k] & 1u) ? 1 : 3) : 0;  // bit 0: has a consensus row, bit 1: mode fields differ
+            fam_tlen[c] = (int32_t)meta[k].z;
+            fam_flag[c] = (uint16_t)(meta[k].w & 0xFFFF);
+            fam_mapq[c] = (uint8_t)((meta[k].w >> 16) & 0xFF);
+            fam_rg[c] = (uint8_t)(meta[k].w >> 24);
+            partner[c] = -1;
+            const uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
+            if (bin < 256) atomicAdd(&small_hist[bin], 1u);
+            else atomicAdd(&hist[bin], 1ull);
         }
-        sscs_row[c] = row;
-        CC_CHECK(c < n && start < n && (uint64_t)start + size <= n && i < n);
-        tmpl[c] = (uint32_t)i;
-        fam_size[c] = size;
-        fam_start[c] = start;
-        cursor[c] = start;
-        is_sscs[c] = size >= 2 ? ((cnt & 1u) ? 1 : 3) : 0;       // bit 0: has a consensus row, bit 1: mode fields differ
-        const uint4 b = __ldg(&fields[2 * i + 1]);
-        fam_tlen[c] = (int32_t)b.z;
-        fam_flag[c] = (uint16_t)(b.w & 0xFFFF);
-        fam_mapq[c] = (uint8_t)((b.w >> 16) & 0xFF);
-        fam_rg[c] = (uint8_t)(b.w >> 24);
-        partner[c] = -1;
-        const uint32_t bin = size < hist_bins - 1 ? size : hist_bins - 1;
-        if (bin < 256) atomicAdd(&small_hist[bin], 1u);
-        else atomicAdd(&hist[bin], 1ull);
     }
     __syncthreads();
     const uint32_t v = small_hist[threadIdx.x];
@@ -581,14 +606,15 @@ tile_join_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__ 
                  const uint32_t *__restrict__ dup_bc, uint32_t n_bc, const GroupSlot *__restrict__ table,
                  const uint32_t *__restrict__ gtc, const uint32_t *__restrict__ link, const uint32_t *__restrict__ aux,
                  const uint32_t *__restrict__ bitmap, const uint32_t *__restrict__ word_rank,
-                 int32_t *__restrict__ partner, const uint32_t *__restrict__ asym)
+                 int32_t *__restrict__ partner, const uint32_t *__restrict__ asym, const uint16_t *__restrict__ fam_flag)
 {
     const uint32_t n_fam = *n_fam_ptr;              // the family count lives on the device: a grid-stride loop up to it
     const bool symmetric = !*asym;
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n_fam; c += gridDim.x * blockDim.x) {
+    // the read number is part of the family key, so the family's flag (a coalesced 2-byte load) tells R1 from R2
+    // without a trip to the template's record
+    if (symmetric && !(fam_flag[c] & 0x40u)) continue;   // an R2 family hears from its R1 partner (partner[] starts at -1)
     const uint32_t first = tmpl[c];
-    const uint4 meta = __ldg(&fields[2 * (uint64_t)first + 1]);
-    if (symmetric && !(meta.w & 0x40u)) continue;   // an R2 family hears from its R1 partner (partner[] starts at -1)
     int32_t found = -1;
     if (__ldg(&link[first]) & LINK_LOCAL) {
         const uint32_t p = __ldg(&aux[first]);
