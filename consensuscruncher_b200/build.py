@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libccgpu.so")
 SOURCES = ["ccgpu.cu"]
-HEADERS = ["kernels.cuh", "radix_onesweep.cuh", "scan.cuh", "vote.cuh", "group_hash.cuh", "group_tile.cuh", os.path.join("..", "..", "include", "ccgpu.h")]
+HEADERS = ["kernels.cuh", "radix_onesweep.cuh", "scan.cuh", "vote.cuh", "group_hash.cuh", "group_tile.cuh", "group_pair.cuh", os.path.join("..", "..", "include", "ccgpu.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC", "-cudart", "static"]

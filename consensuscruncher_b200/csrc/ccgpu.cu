@@ -20,6 +20,7 @@
 #include "vote.cuh"
 #include "group_hash.cuh"
 #include "group_tile.cuh"
+#include "group_pair.cuh"
 
 using namespace ccgpu;
 
@@ -84,7 +85,7 @@ NcclApi &nccl_api()
 }
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
-           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_COUNT = 40 };
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_UNMIRRORED = 34, CT_COUNT = 40 };
 
 }  // namespace
 
@@ -123,8 +124,9 @@ struct cc_ctx {
     DevBuf cursor;                              // tile grouping: next free place of every family's segment
     DevBuf word_reads, word_start;              // ... per bitmap word: reads in the families founded there, and their prefix
     DevBuf gt_state;                            // ... device-side scalars + the contig stretch table (group_tile.cuh)
-    enum GroupMode { GROUP_TILE, GROUP_HASH, GROUP_SORT };
-    GroupMode group_mode = GROUP_TILE;
+    enum GroupMode { GROUP_PAIR, GROUP_TILE, GROUP_HASH, GROUP_SORT };
+    GroupMode group_mode = GROUP_PAIR;
+    bool pair_join = false;                     // the loaded batch was grouped pair by pair (group_pair.cuh)
     bool tile_join = false;
     uint64_t fam_bound = 0;                     // grids / buffers of family-level work cover this many families: the count itself
                                                 // (paths that learn it while grouping) or n (tile path: it stays on the device
@@ -477,6 +479,75 @@ int do_group_tile(cc_ctx *ctx)
     return CC_OK;
 }
 
+// Grouping pair by pair (group_pair.cuh): the default.  Leaves what the read-level paths leave.
+int do_group_pair(cc_ctx *ctx)
+{
+    const uint64_t n = ctx->n, np = n / 2;
+    uint32_t *ctr = ptr<uint32_t>(ctx->counters);
+    TRY(ensure(ctx, ctx->key_a, n * 4)); TRY(ensure(ctx, ctx->key_b, n * 4));
+    TRY(ensure(ctx, ctx->val_a, n * 4)); TRY(ensure(ctx, ctx->val_b, n * 4));
+    uint32_t *plink = ptr<uint32_t>(ctx->key_a), *paux = ptr<uint32_t>(ctx->key_b);
+    uint32_t *pstash = ptr<uint32_t>(ctx->val_b);           // group / family words; dead once the family records are written
+    uint32_t *edge_list = ptr<uint32_t>(ctx->val_a);        // dead before pair_place writes `perm` there
+    uint64_t slots = 1024;
+    while (slots < np + np / 4) slots <<= 1;                // the most the device may use: every pair a listed family
+    TRY(ensure(ctx, ctx->gtable, slots * sizeof(GroupSlot)));
+    GroupSlot *table = ptr<GroupSlot>(ctx->gtable);
+    const uint64_t words = (np + 31) / 32, tiles = pg_tiles(np);
+    TRY(ensure(ctx, ctx->bitmap, words * 4)); TRY(ensure(ctx, ctx->word_rank, words * 4));
+    TRY(ensure(ctx, ctx->word_reads, words * 4)); TRY(ensure(ctx, ctx->word_start, words * 4));
+    TRY(ensure(ctx, ctx->tmpl, n * 4)); TRY(ensure(ctx, ctx->fam_start, n * 4)); TRY(ensure(ctx, ctx->fam_size, n * 4));
+    TRY(ensure(ctx, ctx->cursor, np * 4 + 4)); TRY(ensure(ctx, ctx->is_sscs, n + 4)); TRY(ensure(ctx, ctx->fam_mapq, n + 4));
+    TRY(ensure(ctx, ctx->fam_rg, n + 4)); TRY(ensure(ctx, ctx->fam_flag, n * 2 + 4)); TRY(ensure(ctx, ctx->fam_tlen, n * 4));
+    TRY(ensure(ctx, ctx->partner, n * 4));
+    TRY(ensure(ctx, ctx->sscs_list, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->sscs_row, n * 4));
+    const uint64_t ws_tiles = (words + WS_TILE - 1) / WS_TILE;
+    TRY(ensure(ctx, ctx->scan_status, (2 * ws_tiles + 2) * sizeof(unsigned long long)));
+    TRY(ensure(ctx, ctx->gt_state, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t)));
+    uint32_t *gpc = ptr<uint32_t>(ctx->gt_state), *stretch = gpc + GTC_COUNT;
+    uint32_t *word_pairs = ptr<uint32_t>(ctx->word_reads), *word_sscs = ptr<uint32_t>(ctx->word_start);
+
+    TRY(phase_begin(ctx, CC_PH_HASH));
+    CK(cudaMemsetAsync(gpc, 0, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t), ctx->stream));
+    LAUNCH(pair_local_kernel<0>, (unsigned)tiles, PG_THREADS, ctx->fields, np, ctx->dup_bc, ctx->n_bc, gpc, stretch, ctr + CT_FAULTS,
+           ctr + CT_UNMIRRORED, plink, paux, pstash, edge_list, ptr<uint32_t>(ctx->bitmap), word_pairs, word_sscs);
+    // input out of order (flag raised on the device): the same tiles again, every family through the table
+    LAUNCH(pair_redo_kernel, 1, 1, gpc);
+    LAUNCH(pair_local_kernel<1>, (unsigned)std::min<uint64_t>(tiles, 148 * 8), PG_THREADS, ctx->fields, np, ctx->dup_bc, ctx->n_bc, gpc,
+           stretch, ctr + CT_FAULTS, ctr + CT_UNMIRRORED, plink, paux, pstash, edge_list, ptr<uint32_t>(ctx->bitmap), word_pairs, word_sscs);
+    LAUNCH(pair_table_prepare_kernel, 148 * 4, 256, gpc, table, slots);
+    LAUNCH(pair_edge_insert_kernel, 148 * 8, 256, ctx->fields, edge_list, gpc, table, pstash, paux, ctr + CT_FAULTS);
+    TRY(phase_end(ctx, CC_PH_HASH));
+
+    TRY(phase_begin(ctx, CC_PH_SEGMENT));
+    LAUNCH(pair_edge_mark_kernel, 148 * 8, 256, edge_list, gpc, table, paux, pstash, ptr<uint32_t>(ctx->bitmap), word_pairs, word_sscs);
+    CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * ws_tiles + 2) * sizeof(unsigned long long), ctx->stream));
+    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    // word_pairs -> segment starts (in pairs), word_sscs -> consensus row pairs, both in place; the totals count read families
+    LAUNCH(word_scan_kernel, (unsigned)ws_tiles, WS_THREADS, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), word_pairs,
+           word_sscs, words, ptr<unsigned long long>(ctx->scan_status), ctr + CT_TICKET0 + ctx->next_ticket++, ctr + CT_NFAM,
+           ctr + CT_NSSCS, 2u);
+    LAUNCH(pair_family_kernel, (unsigned)std::min<uint64_t>(blocks_for(np, 256), 148 * 16), 256, ctx->fields, np, pstash,
+           ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), word_pairs, word_sscs, ptr<uint32_t>(ctx->tmpl),
+           ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->cursor), ptr<uint8_t>(ctx->is_sscs),
+           ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
+           ptr<unsigned long long>(ctx->hist), (uint32_t)CC_HIST_BINS, ctr + CT_NMID, ptr<uint32_t>(ctx->sscs_list),
+           ptr<int32_t>(ctx->sscs_row));
+    ctx->perm = ptr<uint32_t>(ctx->val_a);
+    ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family, materialised when somebody fetches it
+    ctx->sorted_keys = ctx->spare_keys = nullptr;
+    LAUNCH(pair_place_kernel, (unsigned)tiles, PG_THREADS, np, plink, paux, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
+           ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->cursor), ctx->perm);
+    ctx->n_fam = 0;                                          // known after do_lists
+    ctx->fam_bound = n;
+    ctx->read_fam_ready = false;
+    ctx->gtable_mask = slots - 1;
+    ctx->pair_join = true;
+    TRY(phase_end(ctx, CC_PH_SEGMENT));
+    ctx->grouped = true;
+    return CC_OK;
+}
+
 int do_group(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
@@ -486,6 +557,7 @@ int do_group(cc_ctx *ctx)
     ctx->next_ticket = 0;
     ctx->gtable_mask = 0;
     ctx->tile_join = false;
+    ctx->pair_join = false;
     TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
     // [16 stage counters | CC_HIST_BINS family-size bins]: one buffer, so that cc_stats_allreduce is one collective
     TRY(ensure(ctx, ctx->stats, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long)));
@@ -495,6 +567,7 @@ int do_group(cc_ctx *ctx)
     CK(cudaMemsetAsync(ctx->stats.p, 0, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long), ctx->stream));
     memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
     if (n == 0) { ctx->grouped = true; return CC_OK; }
+    if (ctx->group_mode == cc_ctx::GROUP_PAIR) return do_group_pair(ctx);
     if (ctx->group_mode == cc_ctx::GROUP_TILE) return do_group_tile(ctx);
     if (ctx->group_mode == cc_ctx::GROUP_HASH) return do_group_hash(ctx);
 
@@ -573,6 +646,14 @@ int do_join_index(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->dcssc_list, bound * 4));
     if (bound == 0) return CC_OK;
     TRY(phase_begin(ctx, CC_PH_JOIN));
+    if (ctx->gtable_mask && ctx->pair_join) {
+        LAUNCH(pair_join_kernel, (unsigned)std::min<uint64_t>(blocks_for(bound / 2 + 1, 256), 148 * 32), 256, ctx->fields,
+               ptr<uint32_t>(ctx->tmpl), ctr + CT_NFAM, ctx->dup_bc, ctx->n_bc, ptr<GroupSlot>(ctx->gtable), ptr<uint32_t>(ctx->gt_state),
+               ptr<uint32_t>(ctx->key_a), ptr<uint32_t>(ctx->key_b), ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
+               ptr<int32_t>(ctx->partner));
+        TRY(phase_end(ctx, CC_PH_JOIN));
+        return do_classify(ctx);
+    }
     if (ctx->gtable_mask && ctx->tile_join) {
         // (the barcode swap's symmetry was established before the tiles were grouped)
         LAUNCH(tile_join_kernel, (unsigned)std::min<uint64_t>(blocks_for(bound, 256), 148 * 32), 256, ctx->fields, ptr<uint32_t>(ctx->tmpl), ctr + CT_NFAM, ctx->dup_bc, ctx->n_bc,
@@ -627,9 +708,23 @@ int do_classify(cc_ctx *ctx)
     return CC_OK;
 }
 
+int do_join_index(cc_ctx *ctx);
+
 int do_lists(cc_ctx *ctx, bool with_join)
 {
     TRY(read_counters(ctx));
+    if (ctx->pair_join && (ctx->host_ctr[CT_UNMIRRORED] || ctx->host_ctr[CT_FAULTS])) {
+        // The pair view does not hold for this batch (mates that do not mirror each other, or pair families that
+        // share the reads of one mate only): group it read by read, which reproduces the reference's families
+        // for such input - and, for the second kind, reports the pairs through the usual domain error.
+        const cc_ctx::GroupMode asked = ctx->group_mode;
+        ctx->group_mode = cc_ctx::GROUP_TILE;
+        int rc = do_group(ctx);
+        if (rc == CC_OK && with_join) rc = do_join_index(ctx);
+        ctx->group_mode = asked;
+        TRY(rc);
+        TRY(read_counters(ctx));
+    }
     ctx->n_fam = ctx->host_ctr[CT_NFAM];                 // (before the checks: the family arrays stay fetchable after a fault)
     if (ctx->host_ctr[CT_FAULTS])
         return fail(ctx, CC_ERR_DOMAIN, "a read pair does not found/join its two families together "
@@ -844,8 +939,9 @@ cc_ctx *cc_create(int device, const cc_params *params)
         return nullptr;
     }
     cc_ctx *ctx = new cc_ctx();
-    if (const char *g = getenv("CCGPU_GROUP"))         // "sort": radix-sort grouping, "hash": one table trip per read
-        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "hash") ? cc_ctx::GROUP_HASH : cc_ctx::GROUP_TILE;
+    if (const char *g = getenv("CCGPU_GROUP"))         // "tile": read by read in tiles, "hash": one table trip per read, "sort": radix sort
+        ctx->group_mode = !strcmp(g, "sort") ? cc_ctx::GROUP_SORT : !strcmp(g, "hash") ? cc_ctx::GROUP_HASH
+                        : !strcmp(g, "tile") ? cc_ctx::GROUP_TILE : cc_ctx::GROUP_PAIR;
     ctx->device = device;
     if (params) ctx->params = *params;
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {

@@ -379,7 +379,7 @@ constexpr int WS_THREADS = 256, WS_ITEMS = 8, WS_TILE = WS_THREADS * WS_ITEMS;
 __global__ void __launch_bounds__(WS_THREADS)
 word_scan_kernel(const uint32_t *__restrict__ bitmap, uint32_t *__restrict__ word_rank, uint32_t *word_reads,
                  uint32_t *word_sscs, uint64_t words, unsigned long long *status, uint32_t *ticket,
-                 uint32_t *__restrict__ n_fam, uint32_t *__restrict__ n_sscs)
+                 uint32_t *__restrict__ n_fam, uint32_t *__restrict__ n_sscs, uint32_t scale = 1)
 {
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_warp[WS_THREADS / 32][3];
@@ -432,7 +432,7 @@ word_scan_kernel(const uint32_t *__restrict__ bitmap, uint32_t *__restrict__ wor
         lookback_pairs<2>(status, tile, tot, excl, lane);
         if (lane == 0) {
             s_excl[0] = excl[0]; s_excl[1] = excl[1]; s_excl[2] = excl[2];
-            if (tile == gridDim.x - 1) { *n_fam = excl[0] + tot[0]; *n_sscs = excl[2] + tot[2]; }
+            if (tile == gridDim.x - 1) { *n_fam = scale * (excl[0] + tot[0]); *n_sscs = scale * (excl[2] + tot[2]); }   // (scale 2: the words count pair families)
         }
     }
     __syncthreads();

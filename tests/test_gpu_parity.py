@@ -358,11 +358,27 @@ def test_inputs_out_of_order_and_pairs_across_contigs(engine):
     helpers.assert_same_result(engine.consensus(deep), oracle.run(deep, 0.7, True))
 
 
-@pytest.mark.parametrize("mode", ["hash", "sort"])
+def test_mates_that_do_not_mirror_each_other_are_grouped_read_by_read(engine):
+    """The default grouping works on pairs and needs mates that carry each other's coordinates; a batch where they
+    do not (here: the second mates of some pairs name a shifted mate position, consistently per family) is
+    detected on the device and grouped read by read - same result as the oracle either way."""
+    packed = synth.generate(seed=73, n_molecules=4000, L=40, n_tid=2, region=(0, 30000), fam_mean=3.0).to_packed()
+    f = packed.fields
+    odd = np.arange(packed.n) % 2 == 1
+    sel = odd & (f["mpos"] % 5 == 2)
+    assert sel.sum() > 100
+    f["mpos"][sel] += 7
+    engine.set_params(cutoff=0.7, scorrect=True)
+    res = engine.consensus(packed)
+    helpers.assert_same_result(res, oracle.run(packed, 0.7, True))
+
+
+@pytest.mark.parametrize("mode", ["tile", "hash", "sort"])
 def test_other_grouping_paths_give_the_same_result(monkeypatch, mode):
     # CCGPU_GROUP=sort selects the radix-sort grouping (hash keys, stable onesweep sort, exact boundaries),
-    # CCGPU_GROUP=hash the table with one trip per read (group_hash.cuh); the default groups tile by tile
-    # (group_tile.cuh).  Same families, same numbering, same everything.
+    # CCGPU_GROUP=hash the table with one trip per read (group_hash.cuh), CCGPU_GROUP=tile the read-by-read
+    # tile grouping (group_tile.cuh); the default groups pair by pair (group_pair.cuh).  Same families, same
+    # numbering, same everything.
     monkeypatch.setenv("CCGPU_GROUP", mode)
     cases = [synth.generate(seed=41, n_molecules=2500, L=128).to_packed(),
              synth.generate(seed=42, n_molecules=800, L=64, mapq_mixed=True, max_family=40, dist="const", fam_mean=20).to_packed(),
