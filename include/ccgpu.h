@@ -140,10 +140,10 @@ int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, 
 int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n,
                          uint32_t lpad, uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc);
 
-/* Family grouping by the exact family tuple: tile by tile in shared memory, with a small global table for the
- * families at tile edges (CCGPU_GROUP=hash in the environment at cc_create: one table trip per read;
- * CCGPU_GROUP=sort: key hash + stable radix sort + exact boundaries - same results); families in creation
- * order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
+/* Family grouping by the exact family tuple: pair by pair (both mates' families at once) and tile by tile in
+ * shared memory, with a small global table for the families at tile edges (CCGPU_GROUP in the environment at
+ * cc_create selects the other paths - tile: read by read in tiles, hash: one table trip per read, sort: key hash
+ * + stable radix sort + exact boundaries - same results); families in creation order, sizes, size histogram.  Replaces read_dict / tag_dict / csn_pair_dict
  * construction (consensus_helper.py:438-475) and Counter(tag_dict.values())
  * (SSCS_maker.py:361). */
 int cc_group(cc_ctx *ctx);
