@@ -134,6 +134,12 @@ struct cc_ctx {
     uint64_t gtable_mask = 0;                   // non-zero while gtable describes the loaded batch
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
+    bool dcssc_row_ready = true;                // CC_DCSSC_ROW holds ranks until somebody asks for it (materialise)
+    bool segments_ready = false;                // vstart / vsize / big_list / mid_list were written by the grouping, no vote has touched them
+    // counters read back while later kernels run (cc_run): a side stream, "counters final" / "copy done" events, pinned words
+    cudaStream_t side = nullptr;
+    cudaEvent_t snap_src[2] = {nullptr, nullptr}, snap_done[2] = {nullptr, nullptr};
+    uint32_t *pin_ctr = nullptr;                // [3][CT_COUNT]: two snapshots, read_counters
     uint32_t host_ctr[CT_COUNT];
     // bookkeeping
     bool profile = false;
@@ -300,8 +306,10 @@ int scan_popcounts(cc_ctx *ctx, const uint32_t *words, uint32_t *out, uint64_t n
 
 int read_counters(cc_ctx *ctx)
 {
-    CK(cudaMemcpyAsync(ctx->host_ctr, ctx->counters.p, sizeof(ctx->host_ctr), cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t *pinned = ctx->pin_ctr + 2 * CT_COUNT;          // (slots 0 and 1 belong to the side stream's snapshots)
+    CK(cudaMemcpyAsync(pinned, ctx->counters.p, sizeof(ctx->host_ctr), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    memcpy(ctx->host_ctr, pinned, sizeof(ctx->host_ctr));
     if (ctx->host_ctr[CT_ERR])
         return fail(ctx, CC_ERR_BASE, "a base other than A/C/G/T carries Q>=30 inside a family "
                                       "(the reference raises IndexError/ValueError, SSCS_maker.py:119-122)");
@@ -501,6 +509,9 @@ int do_group_pair(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->fam_rg, n + 4)); TRY(ensure(ctx, ctx->fam_flag, n * 2 + 4)); TRY(ensure(ctx, ctx->fam_tlen, n * 4));
     TRY(ensure(ctx, ctx->partner, n * 4));
     TRY(ensure(ctx, ctx->sscs_list, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->sscs_row, n * 4));
+    // the vote's per-row segments and its two lists of larger families are written with the family records
+    TRY(ensure(ctx, ctx->vstart, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->vsize, (n / 2 + 2) * 4));
+    TRY(ensure(ctx, ctx->big_list, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->mid_list, (n / 16 + 4) * 4));
     const uint64_t ws_tiles = (words + WS_TILE - 1) / WS_TILE;
     TRY(ensure(ctx, ctx->scan_status, (2 * ws_tiles + 2) * sizeof(unsigned long long)));
     TRY(ensure(ctx, ctx->gt_state, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t)));
@@ -532,7 +543,9 @@ int do_group_pair(cc_ctx *ctx)
            ptr<uint32_t>(ctx->fam_size), ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->cursor), ptr<uint8_t>(ctx->is_sscs),
            ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
            ptr<unsigned long long>(ctx->hist), (uint32_t)CC_HIST_BINS, ctr + CT_NMID, ptr<uint32_t>(ctx->sscs_list),
-           ptr<int32_t>(ctx->sscs_row));
+           ptr<int32_t>(ctx->sscs_row), ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->big_list),
+           ctr + CT_NBIG, ctx->lpad <= 512 ? VOTE_SMALL_MAX : 0u, ptr<uint32_t>(ctx->mid_list), ctr + CT_NMIDLIST);
+    ctx->segments_ready = true;
     ctx->perm = ptr<uint32_t>(ctx->val_a);
     ctx->spare_vals = ptr<uint32_t>(ctx->val_b);           // read -> family, materialised when somebody fetches it
     ctx->sorted_keys = ctx->spare_keys = nullptr;
@@ -558,6 +571,7 @@ int do_group(cc_ctx *ctx)
     ctx->gtable_mask = 0;
     ctx->tile_join = false;
     ctx->pair_join = false;
+    ctx->segments_ready = false;
     TRY(ensure(ctx, ctx->counters, CT_COUNT * sizeof(uint32_t)));
     // [16 stage counters | CC_HIST_BINS family-size bins]: one buffer, so that cc_stats_allreduce is one collective
     TRY(ensure(ctx, ctx->stats, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long)));
@@ -710,9 +724,35 @@ int do_classify(cc_ctx *ctx)
 
 int do_join_index(cc_ctx *ctx);
 
+// Counters as they stand at this point of the stream, copied to pinned memory by the side stream while the
+// main stream carries on; snapshot_wait hands them to host_ctr.
+int snapshot_begin(cc_ctx *ctx, int k)
+{
+    CK(cudaEventRecord(ctx->snap_src[k], ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->side, ctx->snap_src[k], 0));
+    CK(cudaMemcpyAsync(ctx->pin_ctr + k * CT_COUNT, ctx->counters.p, CT_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->side));
+    CK(cudaEventRecord(ctx->snap_done[k], ctx->side));
+    return CC_OK;
+}
+
+int snapshot_wait(cc_ctx *ctx, int k)
+{
+    CK(cudaEventSynchronize(ctx->snap_done[k]));
+    memcpy(ctx->host_ctr, ctx->pin_ctr + k * CT_COUNT, sizeof(ctx->host_ctr));
+    return CC_OK;
+}
+
+int finish_lists(cc_ctx *ctx, bool with_join);
+
 int do_lists(cc_ctx *ctx, bool with_join)
 {
     TRY(read_counters(ctx));
+    return finish_lists(ctx, with_join);
+}
+
+// host_ctr holds the counters: fall back / fail / take the row counts
+int finish_lists(cc_ctx *ctx, bool with_join)
+{
     if (ctx->pair_join && (ctx->host_ctr[CT_UNMIRRORED] || ctx->host_ctr[CT_FAULTS])) {
         // The pair view does not hold for this batch (mates that do not mirror each other, or pair families that
         // share the reads of one mate only): group it read by read, which reproduces the reference's families
@@ -739,8 +779,7 @@ int do_lists(cc_ctx *ctx, bool with_join)
         ctx->n_corr = ctx->host_ctr[CT_NCORR];
         ctx->n_extra = ctx->host_ctr[CT_NDCSSC];
         ctx->n_dcssc = ctx->params.scorrect ? ctx->n_dcs + ctx->n_extra : 0;
-        if (ctx->n_fam)
-            LAUNCH(dcssc_row_finish_kernel, blocks_for(ctx->n_fam, 256), 256, ptr<int32_t>(ctx->dcssc_row), ctx->n_fam, ctx->n_dcs);
+        ctx->dcssc_row_ready = false;                        // the rows of the second pass follow the n_dcs shared ones: added on demand
     }
     ctx->listed = true;
     return CC_OK;
@@ -814,7 +853,10 @@ int do_vote(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->mid_list, ((size_t)ctx->host_ctr[CT_NMID] + 1) * 4));
     if (!ctx->thr_valid) TRY(upload_thresholds(ctx));
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
-    if (rows) {
+    if (rows && !ctx->segments_ready) {
+        // (a second vote of one batch comes here too: the first one marked rows in vsize and appended to big_list)
+        CK(cudaMemsetAsync(ctr + CT_NBIG, 0, 4, ctx->stream));
+        CK(cudaMemsetAsync(ctr + CT_NMIDLIST, 0, 4, ctx->stream));
         TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
         LAUNCH(vote_segments_kernel, blocks_for(rows, 256), 256, ptr<uint32_t>(ctx->sscs_list),
                ptr<uint32_t>(ctx->fam_start), ptr<uint32_t>(ctx->fam_size), ptr<uint8_t>(ctx->is_sscs), rows,
@@ -824,6 +866,7 @@ int do_vote(cc_ctx *ctx)
                ptr<uint32_t>(ctx->mid_list), ctr + CT_NMIDLIST);
         TRY(phase_end(ctx, CC_PH_VOTE_AUX));
     }
+    ctx->segments_ready = false;
     TRY(phase_begin(ctx, CC_PH_VOTE));
     if (rows && ctx->lpad <= 512) {
         const uint32_t lanes = (ctx->lpad + 15) / 16;
@@ -950,6 +993,16 @@ cc_ctx *cc_create(int device, const cc_params *params)
         return nullptr;
     }
     ctx->stream = ctx->own_stream;
+    bool ok = cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaMallocHost(&ctx->pin_ctr, 3 * CT_COUNT * sizeof(uint32_t)) == cudaSuccess;
+    for (int k = 0; k < 2 && ok; k++)
+        ok = cudaEventCreateWithFlags(&ctx->snap_src[k], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->snap_done[k], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+        g_create_error = "cudaStreamCreate / cudaMallocHost / cudaEventCreate failed";
+        cc_destroy(ctx);
+        return nullptr;
+    }
     return ctx;
 }
 
@@ -971,6 +1024,12 @@ void cc_destroy(cc_ctx *ctx)
     for (auto &t : ctx->phase)
         for (cudaEvent_t ev : t.ev) cudaEventDestroy(ev);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
+    for (int k = 0; k < 2; k++) {
+        if (ctx->snap_src[k]) cudaEventDestroy(ctx->snap_src[k]);
+        if (ctx->snap_done[k]) cudaEventDestroy(ctx->snap_done[k]);
+    }
+    if (ctx->pin_ctr) cudaFreeHost(ctx->pin_ctr);
+    if (ctx->side) cudaStreamDestroy(ctx->side);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -1166,9 +1225,30 @@ int cc_run(cc_ctx *ctx)
     if (!ctx->have_reads) return fail(ctx, CC_ERR_ARG, "cc_run before cc_load_reads");
     CK(cudaSetDevice(ctx->device));
     TRY(do_group(ctx));
-    TRY(do_join_index(ctx));
-    TRY(do_lists(ctx, true));
-    TRY(do_vote(ctx));
+    if (ctx->pair_join && ctx->n) {
+        // Everything the vote's launch needs (consensus rows, families of 16+ reads, the grouping's verdict on the
+        // input) is final before the join: the host reads it while the join and the classification run, queues the
+        // vote behind them, and reads the duplex counts while the vote runs.
+        TRY(snapshot_begin(ctx, 0));
+        TRY(do_join_index(ctx));
+        TRY(snapshot_begin(ctx, 1));
+        TRY(snapshot_wait(ctx, 0));
+        if (ctx->host_ctr[CT_UNMIRRORED] || ctx->host_ctr[CT_FAULTS]) {
+            TRY(do_lists(ctx, true));                        // regroups read by read, or reports the pairs
+            TRY(do_vote(ctx));
+        } else {
+            ctx->n_fam = ctx->host_ctr[CT_NFAM];
+            ctx->n_sscs = ctx->host_ctr[CT_NSSCS];
+            TRY(do_vote(ctx));
+            TRY(snapshot_wait(ctx, 1));
+            const int rc = finish_lists(ctx, true);
+            if (rc != CC_OK) { ctx->voted = false; return rc; }    // (a partnership that is not mutual: as if the vote had not run)
+        }
+    } else {
+        TRY(do_join_index(ctx));
+        TRY(do_lists(ctx, true));
+        TRY(do_vote(ctx));
+    }
     if (ctx->params.scorrect) TRY(do_rescue(ctx));
     TRY(do_duplex(ctx, false));
     ctx->joined = true;
@@ -1258,6 +1338,10 @@ uint64_t cc_array_bytes(cc_ctx *ctx, int what)
 
 static int materialise(cc_ctx *ctx, int what)
 {
+    if (what == CC_DCSSC_ROW && !ctx->dcssc_row_ready && ctx->n_fam) {
+        LAUNCH(dcssc_row_finish_kernel, blocks_for(ctx->n_fam, 256), 256, ptr<int32_t>(ctx->dcssc_row), ctx->n_fam, ctx->n_dcs);
+        ctx->dcssc_row_ready = true;
+    }
     if (what == CC_READ_FAM && !ctx->read_fam_ready && ctx->n_fam) {
         LAUNCH(read_fam_kernel, blocks_for((uint64_t)ctx->n_fam * 32, 256), 256, ptr<uint32_t>(ctx->fam_start),
                ptr<uint32_t>(ctx->fam_size), ctx->perm, ctx->n_fam, ctx->spare_vals);

@@ -394,7 +394,9 @@ pair_family_kernel(const uint4 *__restrict__ fields, uint64_t n_pairs, const uin
                    uint32_t *__restrict__ pcursor, uint8_t *__restrict__ is_sscs, uint8_t *__restrict__ fam_mapq,
                    uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
                    unsigned long long *__restrict__ hist, uint32_t hist_bins, uint32_t *__restrict__ n_mid,
-                   uint32_t *__restrict__ sscs_list, int32_t *__restrict__ sscs_row)
+                   uint32_t *__restrict__ sscs_list, int32_t *__restrict__ sscs_row, uint32_t *__restrict__ vstart,
+                   uint32_t *__restrict__ vsize, uint32_t *__restrict__ big_list, uint32_t *__restrict__ n_big,
+                   uint32_t small_max, uint32_t *__restrict__ mid_list, uint32_t *__restrict__ n_midlist)
 {
     __shared__ uint32_t small_hist[256];
     small_hist[threadIdx.x] = 0;
@@ -438,6 +440,11 @@ pair_family_kernel(const uint4 *__restrict__ fields, uint64_t n_pairs, const uin
                 const uint32_t r = 2u * (__ldg(&word_sscs_start[w]) + __popc(big & ((1u << lane) - 1u)));
                 rows = make_int2((int)r, (int)r + 1);
                 *reinterpret_cast<uint2 *>(sscs_list + r) = make_uint2(2 * P, 2 * P + 1);
+                // what the vote reads per consensus row (vote_segments_kernel does the same for the other groupings)
+                *reinterpret_cast<uint2 *>(vstart + r) = make_uint2(2 * sp, 2 * sp + size);
+                *reinterpret_cast<uint2 *>(vsize + r) = make_uint2(size | ((st[k] & 1u) << 31), size | ((st[k] & 2u) << 30));
+                if (size > small_max) *reinterpret_cast<uint2 *>(big_list + atomicAdd(n_big, 2u)) = make_uint2(r, r + 1);
+                else if (size > 15) *reinterpret_cast<uint2 *>(mid_list + atomicAdd(n_midlist, 2u)) = make_uint2(r, r + 1);
             }
             *reinterpret_cast<int2 *>(sscs_row + 2 * P) = rows;
             *reinterpret_cast<uint2 *>(tmpl + 2 * P) = make_uint2((uint32_t)(2 * p), (uint32_t)(2 * p + 1));
