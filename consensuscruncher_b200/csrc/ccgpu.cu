@@ -135,6 +135,7 @@ struct cc_ctx {
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
     bool dcssc_row_ready = true;                // CC_DCSSC_ROW holds ranks until somebody asks for it (materialise)
+    bool stats_clean = false;                   // the 16 stage counters are zero (no classification has added to them)
     bool segments_ready = false;                // vstart / vsize / big_list / mid_list were written by the grouping, no vote has touched them
     // counters read back while later kernels run (cc_run): a side stream, "counters final" / "copy done" events, pinned words
     cudaStream_t side = nullptr;
@@ -255,12 +256,24 @@ int collect_phases(cc_ctx *ctx)
 }
 
 // ---- prefix-sum helpers ---------------------------------------------------------------
+// Every chained scan draws its tile numbers from a counter of its own ("ticket"), zeroed with the other counters
+// when a batch is grouped.  A batch whose later stages are run again and again (cc_set_params + the stage calls)
+// uses the pool up: the scans queued so far are complete by the time anything queued now runs, so the pool is
+// zeroed in stream order and handed out again.
+int ticket_room(cc_ctx *ctx)
+{
+    if (ctx->next_ticket < CT_NMIDLIST - CT_TICKET0) return CC_OK;
+    CK(cudaMemsetAsync(ptr<uint32_t>(ctx->counters) + CT_TICKET0, 0, (CT_NMIDLIST - CT_TICKET0) * sizeof(uint32_t), ctx->stream));
+    ctx->next_ticket = 0;
+    return CC_OK;
+}
+
 int scan_prepare(cc_ctx *ctx, uint64_t n, uint32_t **ticket)
 {
     uint64_t tiles = scan_tiles(n);
     TRY(ensure(ctx, ctx->scan_status, (tiles + 1) * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (tiles + 1) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    TRY(ticket_room(ctx));
     *ticket = ptr<uint32_t>(ctx->counters) + CT_TICKET0 + ctx->next_ticket++;
     return CC_OK;
 }
@@ -460,7 +473,7 @@ int do_group_tile(cc_ctx *ctx)
     LAUNCH(edge_mark_kernel, 148 * 8, 256, edge_list, gtc, table, aux, stash, ptr<uint32_t>(ctx->bitmap),
            ptr<uint32_t>(ctx->word_reads), word_sscs);
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * ws_tiles + 2) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    TRY(ticket_room(ctx));
     LAUNCH(word_scan_kernel, (unsigned)ws_tiles, WS_THREADS, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank),
            ptr<uint32_t>(ctx->word_reads), word_sscs, words, ptr<unsigned long long>(ctx->scan_status),
            ctr + CT_TICKET0 + ctx->next_ticket++, ctr + CT_NFAM, ctr + CT_NSSCS);
@@ -533,7 +546,7 @@ int do_group_pair(cc_ctx *ctx)
     TRY(phase_begin(ctx, CC_PH_SEGMENT));
     LAUNCH(pair_edge_mark_kernel, 148 * 8, 256, edge_list, gpc, table, paux, pstash, ptr<uint32_t>(ctx->bitmap), word_pairs, word_sscs);
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * ws_tiles + 2) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    TRY(ticket_room(ctx));
     // word_pairs -> segment starts (in pairs), word_sscs -> consensus row pairs, both in place; the totals count read families
     LAUNCH(word_scan_kernel, (unsigned)ws_tiles, WS_THREADS, ptr<uint32_t>(ctx->bitmap), ptr<uint32_t>(ctx->word_rank), word_pairs,
            word_sscs, words, ptr<unsigned long long>(ctx->scan_status), ctr + CT_TICKET0 + ctx->next_ticket++, ctr + CT_NFAM,
@@ -579,6 +592,7 @@ int do_group(cc_ctx *ctx)
     ctx->hist.cap = 0;
     CK(cudaMemsetAsync(ctx->counters.p, 0, CT_COUNT * sizeof(uint32_t), ctx->stream));
     CK(cudaMemsetAsync(ctx->stats.p, 0, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long), ctx->stream));
+    ctx->stats_clean = true;
     memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
     if (n == 0) { ctx->grouped = true; return CC_OK; }
     if (ctx->group_mode == cc_ctx::GROUP_PAIR) return do_group_pair(ctx);
@@ -711,7 +725,10 @@ int do_classify(cc_ctx *ctx)
     const uint64_t tiles = ((uint64_t)nf + CLS_TILE - 1) / CLS_TILE;
     TRY(ensure(ctx, ctx->scan_status, (2 * tiles + 2) * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ctx->scan_status.p, 0, (2 * tiles + 2) * sizeof(unsigned long long), ctx->stream));
-    if (ctx->next_ticket >= CT_NMIDLIST - CT_TICKET0) return fail(ctx, CC_ERR_ARG, "scan ticket pool exhausted");
+    if (!ctx->stats_clean)      // cc_dcs_join again on one batch (after cc_set_params): the stage counters are counted afresh
+        CK(cudaMemsetAsync(ctx->stats.p, 0, 16 * sizeof(unsigned long long), ctx->stream));
+    ctx->stats_clean = false;
+    TRY(ticket_room(ctx));
     uint32_t *ticket = ctr + CT_TICKET0 + ctx->next_ticket++;
     LAUNCH(classify_scan_kernel, (unsigned)tiles, CLS_THREADS, ptr<uint32_t>(ctx->fam_size), ptr<int32_t>(ctx->partner), ctr + CT_NFAM,
            (int)ctx->params.scorrect, ptr<unsigned long long>(ctx->scan_status), ticket, ptr<uint32_t>(ctx->dcs_list),

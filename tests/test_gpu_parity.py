@@ -86,6 +86,28 @@ def test_stagewise_calls_equal_one_shot(engine):
     helpers.assert_same_result(engine.result(), one)
 
 
+@pytest.mark.parametrize("mode", ["pair", "tile"])
+def test_voting_a_batch_again_with_another_cutoff(mode, monkeypatch):
+    """cc_set_params + cc_sscs_vote on a batch that was voted already: the lists of 16+ and 128+ read families and
+    the rows queued for the exact kernel (quality bytes >= 128) are made afresh, not appended to."""
+    from consensuscruncher_b200.engine import GpuConsensus
+    monkeypatch.setenv("CCGPU_GROUP", mode)
+    s = synth.generate(seed=43, n_molecules=160, L=64, dist="lognormal", fam_mean=40.0, max_family=400, p_n=0.0)
+    s.qual[::7, 3] = 200
+    packed = s.to_packed()
+    with GpuConsensus(0, cutoff=0.7, scorrect=True) as eng:
+        eng.load(packed)
+        eng.group()
+        assert (eng.fetch("fam_size") > 127).any() and ((eng.fetch("fam_size") > 15) & (eng.fetch("fam_size") < 128)).any()
+        expected = {c: oracle.run(packed, c, True) for c in (0.7, 0.9, 0.51)}
+        for cutoff in (0.7, 0.9, 0.7, 0.51) * 6:              # (more joins than the pool of scan tickets holds)
+            eng.set_params(cutoff=cutoff, scorrect=True)
+            eng.sscs_vote()
+            eng.dcs_join()
+            eng.sc_rescue()
+            helpers.assert_same_result(eng.result(), expected[cutoff])
+
+
 def test_empty_and_tiny_batches(engine):
     engine.set_params(cutoff=0.7, scorrect=True)
     empty = pack.pack_reads([])
