@@ -163,8 +163,12 @@ int cc_dcs_join(cc_ctx *ctx);
  * second DCS_maker run (ConsensusCruncher.py:247-270).  Needs cc_dcs_join first. */
 int cc_sc_rescue(cc_ctx *ctx);
 
-/* cc_group, cc_sscs_vote, cc_dcs_join and (if params.scorrect) cc_sc_rescue in one call
- * with one host synchronisation for the row counts (the family count stays on the device) and one at the end. */
+/* cc_group, cc_sscs_vote, cc_dcs_join and (if params.scorrect) cc_sc_rescue in one call.  The host needs the
+ * row counts to size the output rows: it reads them from pinned memory while later kernels run (a side stream
+ * copies the counters once the grouping has placed the reads and again after the classification), so the call
+ * waits for the device once, at its end.
+ * The stage calls may be repeated on a loaded batch (cc_set_params with another cutoff, then cc_sscs_vote,
+ * cc_dcs_join, cc_sc_rescue again): rows, lists and CC_STATS are made afresh every time. */
 int cc_run(cc_ctx *ctx);
 
 /* Whole path from host buffers to host results: cc_load_reads + cc_run; afterwards
