@@ -63,7 +63,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-contexts", type=int, default=2, help="contexts the end-to-end leg rotates over")
-    ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4", "planes"],
+    ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4", "planes", "classes"],
                     help="host row format of the end-to-end leg: 8-bit qualities (cc_run_host), 4-bit quality "
                          "codes (cc_run_host_q4), or both with the compact one reported when the batch allows it")
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"],
@@ -476,6 +476,26 @@ def device_compact(batch):
     return pairs, planes, qbits, qual_table, base_table
 
 
+def device_classes(pairs):
+    """Input of `cc_run_host_classes` from device_compact's pair records (pack.to_classes is the host statement):
+    (pairs16 i32[n/2][4], classes i32[C][8]) or None."""
+    import torch
+    t1, t2 = pairs[:, 6].to(torch.int64), pairs[:, 7].to(torch.int64)
+    if not bool(((t2 == -t1) & (t1.abs() <= 32767)).all()):
+        return None
+    keys = pairs[:, [1, 2, 4, 8, 9]].contiguous()           # cig, tid, mtid, flags, meta
+    classes, inverse = torch.unique(keys, dim=0, return_inverse=True)
+    if classes.shape[0] > 65536:
+        return None
+    out = torch.empty((pairs.shape[0], 4), dtype=torch.int32, device=pairs.device)
+    out[:, 0], out[:, 1], out[:, 2] = pairs[:, 0], pairs[:, 3], pairs[:, 5]
+    w = (t1 & 0xFFFF) | (inverse.to(torch.int64) << 16)
+    out[:, 3] = torch.where(w >= 2 ** 31, w - 2 ** 32, w).to(torch.int32)
+    table = torch.zeros((classes.shape[0], 8), dtype=torch.int32, device=pairs.device)
+    table[:, 0:5] = classes
+    return out, table
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -601,23 +621,35 @@ def main():
             torch.cuda.synchronize(dev)
             q4 = None
         # Most compact (cc_run_host_compact): 40-byte pair records + 2-bit bases + few-bit quality codes
-        planes = device_compact(batch) if args.e2e_format in ("auto", "planes") else None
-        if args.e2e_format == "planes" and planes is None:
-            raise SystemExit("--e2e-format planes: the batch does not fit the compact format")
-        h_pairs = h_planes = None
+        planes = device_compact(batch) if args.e2e_format in ("auto", "planes", "classes") else None
+        if args.e2e_format in ("planes", "classes") and planes is None:
+            raise SystemExit("--e2e-format %s: the batch does not fit the compact format" % args.e2e_format)
+        h_pairs = h_planes = h_pairs16 = h_classes = None
         if planes is not None:
             h_pairs = torch.empty(planes[0].shape, dtype=torch.int32, pin_memory=True)
             h_planes = torch.empty(planes[1].shape, dtype=torch.uint8, pin_memory=True)
             h_pairs.copy_(planes[0]); h_planes.copy_(planes[1])
             p_qbits, p_qual, p_base = planes[2], planes[3].contiguous(), planes[4].contiguous()
+            # Shorter still (cc_run_host_classes): 16-byte pair records + a table of what many pairs share
+            short = device_classes(planes[0]) if args.e2e_format in ("auto", "classes") else None
+            if args.e2e_format == "classes" and short is None:
+                raise SystemExit("--e2e-format classes: the batch does not fit the short pair records")
+            if short is not None:
+                h_pairs16 = torch.empty(short[0].shape, dtype=torch.int32, pin_memory=True)
+                h_classes = torch.empty(short[1].shape, dtype=torch.int32, pin_memory=True)
+                h_pairs16.copy_(short[0]); h_classes.copy_(short[1])
             torch.cuda.synchronize(dev)
-            planes = None
+            planes = short = None
         fmt = {"name": "q8"}
         import ctypes
 
         def e2e_step(which, step_no):
             e = engines[which]
-            if fmt["name"] == "planes":
+            if fmt["name"] == "classes":
+                e._check(e.lib.cc_run_host_classes(e.ctx, h_pairs16.data_ptr(), h_classes.data_ptr(), h_classes.shape[0],
+                                                   h_planes.data_ptr(), n_reads, batch.lpad, h_planes.shape[1], p_qbits,
+                                                   p_qual.data_ptr(), p_base.data_ptr(), h_dup.data_ptr(), batch.n_bc))
+            elif fmt["name"] == "planes":
                 e._check(e.lib.cc_run_host_compact(e.ctx, h_pairs.data_ptr(), h_planes.data_ptr(), n_reads, batch.lpad,
                                                    h_planes.shape[1], p_qbits, p_qual.data_ptr(), p_base.data_ptr(),
                                                    h_dup.data_ptr(), batch.n_bc))
@@ -671,7 +703,9 @@ def main():
             t = torch.tensor([wall], dtype=torch.float64, device=dev)
             if world > 1:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            if name == "planes":
+            if name == "classes":
+                h2d = (h_pairs16.numel() + h_classes.numel()) * 4 + h_planes.numel() + h_dup.numel() * h_dup.element_size()
+            elif name == "planes":
                 h2d = h_pairs.numel() * 4 + h_planes.numel() + h_dup.numel() * h_dup.element_size()
             else:
                 payload_bytes = h_q4.numel() if name == "q4" else h_payload.numel()
@@ -685,11 +719,17 @@ def main():
             legs["q8"] = measure("q8")
         if h_q4 is not None:
             legs["q4"] = measure("q4")
-        if h_planes is not None:
+        if h_planes is not None and args.e2e_format != "classes":
             legs["planes"] = measure("planes")
-        best = "planes" if "planes" in legs else "q4" if "q4" in legs else "q8"
+        if h_pairs16 is not None:
+            legs["classes"] = measure("classes")
+        best = "classes" if "classes" in legs else "planes" if "planes" in legs else "q4" if "q4" in legs else "q8"
         e2e = dict(legs[best])
         e2e["input_format"] = {
+            "classes": "cc_run_host_classes: 16-byte pair records + %d classes + rows of 2-bit bases and %d-bit quality "
+                       "codes (%d bytes per read)" % (h_classes.shape[0] if h_classes is not None else 0,
+                                                      p_qbits if h_planes is not None else 0,
+                                                      8 + (h_planes.shape[1] if h_planes is not None else 0)),
             "planes": "cc_run_host_compact: 40-byte pair records + rows of 2-bit bases and %d-bit quality codes "
                       "(%d bytes per read)" % (p_qbits if h_planes is not None else 0,
                                                20 + (h_planes.shape[1] if h_planes is not None else 0)),
@@ -697,8 +737,10 @@ def main():
             "q8": "cc_run_host: rows with 8-bit qualities"}[best]
         if best != "q8" and "q8" in legs:
             e2e["q8_rows"] = {k: legs["q8"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
-        if best == "planes" and "q4" in legs:
+        if best in ("planes", "classes") and "q4" in legs:
             e2e["q4_rows"] = {k: legs["q4"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
+        if best == "classes" and "planes" in legs:
+            e2e["pair40_rows"] = {k: legs["planes"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}
         e2e["pipeline"] = ("%d contexts take turns: read-back of batch k overlaps upload of batch k+1; "
                            "host wall clock" % n_ctx)
         e2e["numa"] = numa
@@ -723,7 +765,7 @@ def main():
     if which or (args.sweep == "auto" and world == 1):
         # release the replica batch and the end-to-end leg's pinned buffers first
         batch = None
-        h_fields = h_payload = h_dup = h_q4 = h_outs = h_pairs = h_planes = None
+        h_fields = h_payload = h_dup = h_q4 = h_outs = h_pairs = h_planes = h_pairs16 = h_classes = None
         import gc
         gc.collect()
         torch.cuda.empty_cache()

@@ -85,7 +85,7 @@ NcclApi &nccl_api()
 }
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
-           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_UNMIRRORED = 34, CT_COUNT = 40 };
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_UNMIRRORED = 34, CT_BADCLASS = 35, CT_COUNT = 40 };
 
 }  // namespace
 
@@ -100,7 +100,7 @@ struct cc_ctx {
     const uint32_t *dup_bc = nullptr;
     uint64_t n = 0;
     uint32_t lpad = 0, stride = 0, n_bc = 0;
-    DevBuf in_fields, in_payload, in_dup, in_q4, in_pairs;
+    DevBuf in_fields, in_payload, in_dup, in_q4, in_pairs, in_classes;
     // grouping scratch
     DevBuf key_a, key_b, val_a, val_b, head, radix_counts, scan_status, counters, hist, stats;
     uint32_t *perm = nullptr, *sorted_keys = nullptr, *spare_keys = nullptr, *spare_vals = nullptr;
@@ -135,6 +135,7 @@ struct cc_ctx {
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
     bool dcssc_row_ready = true;                // CC_DCSSC_ROW holds ranks until somebody asks for it (materialise)
+    bool by_classes = false;                    // loaded through cc_load_reads_classes: in_classes ends with a "bad class index" word
     bool stats_clean = false;                   // the 16 stage counters are zero (no classification has added to them)
     bool segments_ready = false;                // vstart / vsize / big_list / mid_list were written by the grouping, no vote has touched them
     // counters read back while later kernels run (cc_run): a side stream, "counters final" / "copy done" events, pinned words
@@ -323,6 +324,8 @@ int read_counters(cc_ctx *ctx)
     CK(cudaMemcpyAsync(pinned, ctx->counters.p, sizeof(ctx->host_ctr), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     memcpy(ctx->host_ctr, pinned, sizeof(ctx->host_ctr));
+    if (ctx->host_ctr[CT_BADCLASS])
+        return fail(ctx, CC_ERR_ARG, "cc_load_reads_classes: a pair record names a class beyond n_classes");
     if (ctx->host_ctr[CT_ERR])
         return fail(ctx, CC_ERR_BASE, "a base other than A/C/G/T carries Q>=30 inside a family "
                                       "(the reference raises IndexError/ValueError, SSCS_maker.py:119-122)");
@@ -591,6 +594,9 @@ int do_group(cc_ctx *ctx)
     ctx->hist.p = ptr<unsigned long long>(ctx->stats) + 16;                // a view, never released on its own
     ctx->hist.cap = 0;
     CK(cudaMemsetAsync(ctx->counters.p, 0, CT_COUNT * sizeof(uint32_t), ctx->stream));
+    if (ctx->by_classes)        // what the expansion of the short pair records found (the word behind the class table)
+        CK(cudaMemcpyAsync(ptr<uint32_t>(ctx->counters) + CT_BADCLASS, ptr<uint8_t>(ctx->in_classes) + ctx->in_classes.cap - 4, 4,
+                           cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaMemsetAsync(ctx->stats.p, 0, (16 + (size_t)CC_HIST_BINS) * sizeof(unsigned long long), ctx->stream));
     ctx->stats_clean = true;
     memset(ctx->host_ctr, 0, sizeof(ctx->host_ctr));
@@ -1028,7 +1034,7 @@ void cc_destroy(cc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->in_pairs, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
+    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->in_pairs, &ctx->in_classes, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
                      &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->stats,
                      &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
                      &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
@@ -1095,6 +1101,7 @@ int cc_load_reads(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, 
     ctx->dup_bc = ptr<uint32_t>(ctx->in_dup);
     ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
     ctx->have_reads = true;
+    ctx->by_classes = false;
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
     return CC_OK;
 }
@@ -1129,31 +1136,48 @@ int cc_load_reads_q4(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payloa
     ctx->dup_bc = ptr<uint32_t>(ctx->in_dup);
     ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
     ctx->have_reads = true;
+    ctx->by_classes = false;
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
     return CC_OK;
 }
 
-int cc_load_reads_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes, uint64_t n, uint32_t lpad,
-                          uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
-                          const uint32_t *dup_bc, uint32_t n_bc)
+// cc_load_reads_compact / cc_load_reads_classes: pair records (40-byte ones, or 16-byte ones + a class table) and
+// rows in bit planes, both expanded on the device into the layout every kernel reads
+static int load_planes(cc_ctx *ctx, const char *who, const void *pairs, size_t pair_bytes, const cc_pair_class *classes,
+                       uint32_t n_classes, const uint8_t *planes, uint64_t n, uint32_t lpad, uint32_t stride_c, uint32_t qbits,
+                       const uint8_t qual_table[16], const uint8_t base_table[16], const uint32_t *dup_bc, uint32_t n_bc)
 {
     if (!ctx || !qual_table || !base_table) return CC_ERR_ARG;
     CK(cudaSetDevice(ctx->device));
-    if (qbits < 1 || qbits > 4) return fail(ctx, CC_ERR_ARG, "cc_load_reads_compact: qbits must be 1..4");
+    if (qbits < 1 || qbits > 4) return fail(ctx, CC_ERR_ARG, (std::string(who) + ": qbits must be 1..4").c_str());
     if (lpad == 0 || lpad % 32 || stride_c % 16 || stride_c < lpad / 4 + lpad * qbits / 8)
-        return fail(ctx, CC_ERR_ARG, "need lpad % 32 == 0, stride_c % 16 == 0, stride_c >= lpad/4 + lpad*qbits/8");
+        return fail(ctx, CC_ERR_ARG, (std::string(who) + ": need lpad % 32 == 0, stride_c % 16 == 0, stride_c >= lpad/4 + lpad*qbits/8").c_str());
+    const bool by_classes = pair_bytes == sizeof(cc_pair16);
+    if (by_classes && n && (!classes || n_classes == 0 || n_classes > 65536))
+        return fail(ctx, CC_ERR_ARG, (std::string(who) + ": need 1..65536 classes").c_str());
     const uint32_t stride = (lpad / 2 + lpad + 63) / 64 * 64;           // the standard row the kernels read
     TRY(check_geometry(ctx, pairs, planes, n, lpad, stride));
     TRY(ensure(ctx, ctx->in_fields, n * sizeof(cc_fields)));
-    TRY(ensure(ctx, ctx->in_pairs, (n / 2) * sizeof(cc_pair)));
+    TRY(ensure(ctx, ctx->in_pairs, (n / 2) * pair_bytes));
+    if (by_classes) TRY(ensure(ctx, ctx->in_classes, (size_t)n_classes * sizeof(cc_pair_class) + 64));
     TRY(ensure(ctx, ctx->in_q4, n * (size_t)stride_c));
     TRY(ensure(ctx, ctx->in_payload, n * (size_t)stride));
     TRY(ensure(ctx, ctx->in_dup, (size_t)n_bc * 4));
     TRY(phase_begin(ctx, CC_PH_H2D));
+    ctx->by_classes = false;
     if (n) {
-        CK(cudaMemcpyAsync(ctx->in_pairs.p, pairs, (n / 2) * sizeof(cc_pair), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->in_pairs.p, pairs, (n / 2) * pair_bytes, cudaMemcpyHostToDevice, ctx->stream));
         CK(cudaMemcpyAsync(ctx->in_q4.p, planes, n * (size_t)stride_c, cudaMemcpyHostToDevice, ctx->stream));
-        LAUNCH(expand_pairs_kernel, blocks_for(n / 2, 256), 256, ptr<uint2>(ctx->in_pairs), n / 2, ptr<uint4>(ctx->in_fields));
+        if (by_classes) {
+            uint32_t *bad = reinterpret_cast<uint32_t *>(ptr<uint8_t>(ctx->in_classes) + ctx->in_classes.cap - 4);
+            CK(cudaMemcpyAsync(ctx->in_classes.p, classes, (size_t)n_classes * sizeof(cc_pair_class), cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemsetAsync(bad, 0, 4, ctx->stream));
+            LAUNCH(expand_pairs16_kernel, blocks_for(n / 2, 256), 256, ptr<uint4>(ctx->in_pairs), ptr<uint4>(ctx->in_classes), n_classes,
+                   n / 2, ptr<uint4>(ctx->in_fields), bad);
+            ctx->by_classes = true;
+        } else {
+            LAUNCH(expand_pairs_kernel, blocks_for(n / 2, 256), 256, ptr<uint2>(ctx->in_pairs), n / 2, ptr<uint4>(ctx->in_fields));
+        }
         CodeTable table;
         memcpy(table.qual, qual_table, 16);
         memcpy(table.base, base_table, 16);
@@ -1177,6 +1201,22 @@ int cc_load_reads_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *plan
     return CC_OK;
 }
 
+int cc_load_reads_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes, uint64_t n, uint32_t lpad,
+                          uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
+                          const uint32_t *dup_bc, uint32_t n_bc)
+{
+    return load_planes(ctx, "cc_load_reads_compact", pairs, sizeof(cc_pair), nullptr, 0, planes, n, lpad, stride_c, qbits,
+                       qual_table, base_table, dup_bc, n_bc);
+}
+
+int cc_load_reads_classes(cc_ctx *ctx, const cc_pair16 *pairs, const cc_pair_class *classes, uint32_t n_classes,
+                          const uint8_t *planes, uint64_t n, uint32_t lpad, uint32_t stride_c, uint32_t qbits,
+                          const uint8_t qual_table[16], const uint8_t base_table[16], const uint32_t *dup_bc, uint32_t n_bc)
+{
+    return load_planes(ctx, "cc_load_reads_classes", pairs, sizeof(cc_pair16), classes, n_classes, planes, n, lpad, stride_c,
+                       qbits, qual_table, base_table, dup_bc, n_bc);
+}
+
 int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *payload, uint64_t n, uint32_t lpad,
                          uint32_t stride, const uint32_t *dup_bc, uint32_t n_bc)
 {
@@ -1190,6 +1230,7 @@ int cc_load_reads_device(cc_ctx *ctx, const cc_fields *fields, const uint8_t *pa
     ctx->dup_bc = dup_bc;
     ctx->n = n; ctx->lpad = lpad; ctx->stride = stride; ctx->n_bc = n_bc;
     ctx->have_reads = true;
+    ctx->by_classes = false;
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = false;
     return CC_OK;
 }
@@ -1295,6 +1336,14 @@ int cc_run_host_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes
                         const uint32_t *dup_bc, uint32_t n_bc)
 {
     TRY(cc_load_reads_compact(ctx, pairs, planes, n, lpad, stride_c, qbits, qual_table, base_table, dup_bc, n_bc));
+    return cc_run(ctx);
+}
+
+int cc_run_host_classes(cc_ctx *ctx, const cc_pair16 *pairs, const cc_pair_class *classes, uint32_t n_classes,
+                        const uint8_t *planes, uint64_t n, uint32_t lpad, uint32_t stride_c, uint32_t qbits,
+                        const uint8_t qual_table[16], const uint8_t base_table[16], const uint32_t *dup_bc, uint32_t n_bc)
+{
+    TRY(cc_load_reads_classes(ctx, pairs, classes, n_classes, planes, n, lpad, stride_c, qbits, qual_table, base_table, dup_bc, n_bc));
     return cc_run(ctx);
 }
 

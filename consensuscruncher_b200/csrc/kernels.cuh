@@ -831,6 +831,38 @@ expand_pairs_kernel(const uint2 *__restrict__ pairs, uint64_t n_pairs, uint4 *__
     fields[4 * k + 3] = make_uint4(b.x, b.y, d.y, m2);
 }
 
+// Short pair records (cc_load_reads_classes): what many pairs have in common - cigar pair, contigs, flags, MAPQs,
+// read groups - sits once in a class table; a pair keeps its barcode, its two positions, the first mate's TLEN
+// (the second mate's is its negative) and the number of its class.  16 bytes describe both 32-byte field records.
+struct PairClass {
+    uint32_t cig;
+    int32_t tid, mtid;
+    uint32_t flags;                    // flag1 | flag2 << 16
+    uint32_t meta;                     // mapq1 | mapq2 << 8 | rg1 << 16 | rg2 << 24
+    uint32_t reserved[3];
+};
+static_assert(sizeof(PairClass) == 32, "cc_pair_class is 32 bytes");
+
+__global__ void __launch_bounds__(256)
+expand_pairs16_kernel(const uint4 *__restrict__ pairs, const uint4 *__restrict__ classes, uint32_t n_classes,
+                      uint64_t n_pairs, uint4 *__restrict__ fields, uint32_t *__restrict__ bad_class)
+{
+    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_pairs) return;
+    const uint4 p = pairs[k];                       // bc, pos, mpos, tlen1 (i16) | cls << 16
+    uint32_t cls = p.w >> 16;
+    if (cls >= n_classes) { atomicAdd(bad_class, 1u); cls = 0; }
+    const uint4 c0 = __ldg(&classes[2 * cls]);      // cig, tid, mtid, flags
+    const uint32_t meta = __ldg(&classes[2 * cls + 1]).x;
+    const int32_t tlen1 = (int32_t)(int16_t)(p.w & 0xFFFFu);
+    const uint32_t m1 = (c0.w & 0xFFFFu) | ((meta & 0xFFu) << 16) | (((meta >> 16) & 0xFFu) << 24);
+    const uint32_t m2 = (c0.w >> 16) | (((meta >> 8) & 0xFFu) << 16) | ((meta >> 24) << 24);
+    fields[4 * k] = make_uint4(p.x, c0.x, c0.y, p.y);
+    fields[4 * k + 1] = make_uint4(c0.z, p.z, (uint32_t)tlen1, m1);
+    fields[4 * k + 2] = make_uint4(p.x, c0.x, c0.z, p.z);
+    fields[4 * k + 3] = make_uint4(c0.y, p.y, (uint32_t)(-tlen1), m2);
+}
+
 // Rows in bit planes: lpad/4 bytes of 2-bit bases (A,C,G,T = 0..3, position p at bits 2p..2p+1) followed by
 // lpad * QBITS / 8 bytes of QBITS-bit codes (position p at bit p * QBITS, little endian).  A code names
 // a quality and, where base_of[code] != 0xFF, the literal 4-bit base code of the position (N, a pad, an

@@ -37,7 +37,7 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
            "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4",
-           "cc_load_reads_compact", "cc_run_host_compact", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
+           "cc_load_reads_compact", "cc_run_host_compact", "cc_load_reads_classes", "cc_run_host_classes", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
 COMM_ID_BYTES = 128
 
 
@@ -102,6 +102,8 @@ def load_library(path=None):
     L.cc_device_bytes.argtypes = [vp]
     L.cc_load_reads_compact.argtypes = [vp, vp, vp, u64, u32, u32, u32, vp, vp, vp, u32]
     L.cc_run_host_compact.argtypes = [vp, vp, vp, u64, u32, u32, u32, vp, vp, vp, u32]
+    L.cc_load_reads_classes.argtypes = [vp, vp, vp, u32, vp, u64, u32, u32, u32, vp, vp, vp, u32]
+    L.cc_run_host_classes.argtypes = [vp, vp, vp, u32, vp, u64, u32, u32, u32, vp, vp, vp, u32]
     L.cc_fetch_many.argtypes = [vp, u32, vp, vp, vp]
     L.cc_comm_unique_id.argtypes = [vp]
     L.cc_comm_init.argtypes = [vp, vp, i32, i32]
@@ -208,6 +210,23 @@ class GpuConsensus:
                                                    planes.shape[1], int(qbits), qual_table.ctypes.data,
                                                    base_table.ctypes.data, dup.ctypes.data, len(dup)))
 
+    def load_classes(self, packed: PackedReads, compact=None):
+        """16-byte pair records + class table + bit-plane rows -> device (cc_load_reads_classes); raises if the
+        batch does not fit (see pack.to_classes)."""
+        from .pack import row_geometry, to_classes, to_compact
+        compact = compact or to_compact(packed)
+        short = to_classes(compact[0]) if compact is not None else None
+        if short is None:
+            raise GpuError("the batch does not fit the short pair records: use load_compact() or load()")
+        pairs, classes = short
+        _, planes, qbits, qual_table, base_table = compact
+        dup = np.ascontiguousarray(packed.dup_bc, dtype=np.uint32)
+        self._keep = (pairs, classes, planes, dup, qual_table, base_table)
+        self.lpad, self.stride = packed.lpad, row_geometry(packed.lpad)[1]
+        self._check(self.lib.cc_load_reads_classes(self.ctx, pairs.ctypes.data, classes.ctypes.data, len(classes),
+                                                   planes.ctypes.data, packed.n, packed.lpad, planes.shape[1], int(qbits),
+                                                   qual_table.ctypes.data, base_table.ctypes.data, dup.ctypes.data, len(dup)))
+
     def load_device(self, fields_ptr, payload_ptr, n, lpad, stride, dup_ptr, n_bc):
         """Adopt buffers that already live in device memory (cc_load_reads_device)."""
         self.lpad, self.stride = int(lpad), int(stride)
@@ -272,14 +291,19 @@ class GpuConsensus:
         """The whole path on one batch: host SoA in, family-level results out.
         compact=True sends the rows with 4-bit quality codes (cc_load_reads_q4)."""
         q4 = None
-        if compact in ("auto", "planes"):      # the most compact rows the batch's qualities allow
-            from .pack import to_compact, to_q4
+        if compact in ("auto", "planes", "classes"):      # the most compact form the batch allows
+            from .pack import to_classes, to_compact, to_q4
             planes = to_compact(packed)
             if planes is not None:
-                self.load_compact(packed, planes)
+                if compact != "planes" and to_classes(planes[0]) is not None:
+                    self.load_classes(packed, planes)
+                elif compact == "classes":
+                    raise GpuError("the batch does not fit the short pair records")
+                else:
+                    self.load_compact(packed, planes)
                 self.run()
                 return self.result()
-            if compact == "planes":
+            if compact in ("planes", "classes"):
                 raise GpuError("the batch does not fit the compact format")
             q4 = to_q4(packed)
             compact = q4 is not None

@@ -311,6 +311,51 @@ def to_compact(packed):
     return pairs, planes, qbits, qual_table, base_table
 
 
+PAIR16_DT = np.dtype([("bc", "<u4"), ("pos", "<i4"), ("mpos", "<i4"), ("tlen1", "<i2"), ("cls", "<u2")])   # cc_pair16
+CLASS_DT = np.dtype([("cig", "<u4"), ("tid", "<i4"), ("mtid", "<i4"), ("flag1", "<u2"), ("flag2", "<u2"),
+                     ("mapq1", "u1"), ("mapq2", "u1"), ("rg1", "u1"), ("rg2", "u1"), ("reserved", "<u4", (3,))])  # cc_pair_class
+assert PAIR16_DT.itemsize == 16 and CLASS_DT.itemsize == 32
+_CLASS_KEYS = ("cig", "tid", "mtid", "flag1", "flag2", "mapq1", "mapq2", "rg1", "rg2")
+
+
+def to_classes(pairs):
+    """Input of `cc_load_reads_classes` from cc_pair records: (pairs16, classes), or None when the batch does
+    not fit - a pair whose TLENs are not each other's negatives or do not fit 16 bits, more than 65 536
+    distinct (cigar pair, contigs, flags, MAPQs, read groups) combinations."""
+    if not ((pairs["tlen2"] == -pairs["tlen1"]) & (np.abs(pairs["tlen1"]) <= 32767)).all():
+        return None
+    # classes by a 64-bit mix of their fields (np.unique on one integer column), then checked field by field
+    h = np.zeros(len(pairs), np.uint64)
+    for nm in _CLASS_KEYS:
+        h = (h ^ pairs[nm].astype(np.int64).astype(np.uint64)) * np.uint64(0x9E3779B97F4A7C15)
+        h ^= h >> np.uint64(29)
+    _, first, inverse = np.unique(h, return_index=True, return_inverse=True)
+    if len(first) > 65536:
+        return None
+    classes = np.zeros(len(first), CLASS_DT)
+    for nm in _CLASS_KEYS:
+        classes[nm] = pairs[nm][first]
+        if not (classes[nm][inverse] == pairs[nm]).all():
+            return None                                       # two classes under one hash value: not worth a second try
+    out = np.zeros(len(pairs), PAIR16_DT)
+    for nm in ("bc", "pos", "mpos", "tlen1"):
+        out[nm] = pairs[nm]
+    out["cls"] = inverse
+    return out, classes
+
+
+def from_classes(pairs16, classes):
+    """cc_pair records of short pair records (the host statement of expand_pairs16_kernel)."""
+    out = np.zeros(len(pairs16), PAIR_DT)
+    c = classes[pairs16["cls"]]
+    for nm in ("bc", "pos", "mpos", "tlen1"):
+        out[nm] = pairs16[nm]
+    out["tlen2"] = -pairs16["tlen1"].astype(np.int32)
+    for nm in _CLASS_KEYS:
+        out[nm] = c[nm]
+    return out
+
+
 def from_compact(pairs, planes, qbits, qual_table, base_table, lpad):
     """Inverse of `to_compact`: (fields, standard payload rows) - what the device expands to."""
     n = 2 * pairs.shape[0]

@@ -217,6 +217,33 @@ int cc_run_host_compact(cc_ctx *ctx, const cc_pair *pairs, const uint8_t *planes
                         uint32_t stride_c, uint32_t qbits, const uint8_t qual_table[16], const uint8_t base_table[16],
                         const uint32_t *dup_bc, uint32_t n_bc);
 
+/* cc_load_reads_compact with 16-byte pair records: what many pairs have in common sits once in a class table
+ * (at most 65 536 classes), a pair keeps its barcode, its two positions, the first-seen mate's TLEN and the
+ * number of its class; the second mate's TLEN is the negative of the first's.  A batch with a pair whose TLENs
+ * are not each other's negatives, with |TLEN| > 32767 or with more classes must use cc_load_reads_compact.
+ * planes / qbits / tables as there.  A class index >= n_classes makes the run return CC_ERR_ARG.
+ * At lpad = 128 with 7 codes: 8 + 80 = 88 bytes per read against 224.  Same reference code as
+ * cc_load_reads (read_bam, consensus_helper.py:376-436). */
+typedef struct {
+    uint32_t bc;
+    int32_t pos, mpos;                 /* of the first-seen mate (read 2k)                   */
+    int16_t tlen1;                     /* TLEN of read 2k; read 2k+1 has -tlen1              */
+    uint16_t cls;                      /* index into the class table                         */
+} cc_pair16;
+typedef struct {
+    uint32_t cig;
+    int32_t tid, mtid;                 /* of the first-seen mate                             */
+    uint16_t flag1, flag2;
+    uint8_t mapq1, mapq2, rg1, rg2;
+    uint32_t reserved[3];              /* 32-byte records                                    */
+} cc_pair_class;
+int cc_load_reads_classes(cc_ctx *ctx, const cc_pair16 *pairs, const cc_pair_class *classes, uint32_t n_classes,
+                          const uint8_t *planes, uint64_t n, uint32_t lpad, uint32_t stride_c, uint32_t qbits,
+                          const uint8_t qual_table[16], const uint8_t base_table[16], const uint32_t *dup_bc, uint32_t n_bc);
+int cc_run_host_classes(cc_ctx *ctx, const cc_pair16 *pairs, const cc_pair_class *classes, uint32_t n_classes,
+                        const uint8_t *planes, uint64_t n, uint32_t lpad, uint32_t stride_c, uint32_t qbits,
+                        const uint8_t qual_table[16], const uint8_t base_table[16], const uint32_t *dup_bc, uint32_t n_bc);
+
 /* counts[CC_N_*] after the stage that produces them (synchronises). */
 int cc_counts(cc_ctx *ctx, uint64_t counts[8]);
 

@@ -175,3 +175,23 @@ def test_compact_upload_gives_the_same_result(engine, kw):
     got = engine.consensus(packed, compact="planes")
     helpers.assert_same_result(got, oracle.run(packed, 0.7, True))
     helpers.assert_same_result(got, engine.consensus(packed))
+    # cc_load_reads_classes: 16-byte pair records + class table
+    assert pack.to_classes(pack.to_compact(packed)[0]) is not None
+    helpers.assert_same_result(engine.consensus(packed, compact="classes"), got)
+
+
+def test_short_pair_records_with_a_class_out_of_range_are_refused(engine):
+    from consensuscruncher_b200 import pack, synth
+    from consensuscruncher_b200.engine import GpuError
+    packed = synth.generate(seed=85, n_molecules=400, L=64).to_packed()
+    compact = pack.to_compact(packed)
+    pairs, classes = pack.to_classes(compact[0])
+    pairs["cls"][7] = len(classes)
+    engine.set_params(cutoff=0.7, scorrect=True)
+    dup = np.ascontiguousarray(packed.dup_bc, dtype=np.uint32)
+    _, planes, qbits, qt, bt = compact
+    rc = engine.lib.cc_run_host_classes(engine.ctx, pairs.ctypes.data, classes.ctypes.data, len(classes), planes.ctypes.data,
+                                        packed.n, packed.lpad, planes.shape[1], int(qbits), qt.ctypes.data, bt.ctypes.data,
+                                        dup.ctypes.data, len(dup))
+    assert rc == -2 and b"class" in engine.lib.cc_last_error(engine.ctx)          # CC_ERR_ARG
+    helpers.assert_same_result(engine.consensus(packed, compact="classes"), oracle.run(packed, 0.7, True))

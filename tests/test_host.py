@@ -216,6 +216,30 @@ def test_compact_upload_format_round_trips():
     assert pack.to_pairs(packed.fields) is None and pack.to_compact(packed) is None
 
 
+def test_short_pair_records_round_trip():
+    """pack.to_classes (input of cc_load_reads_classes): 16-byte pair records + a class table give back the very
+    same cc_pair records; batches that do not fit are refused."""
+    for kw in (dict(seed=5, n_molecules=300, L=100), dict(seed=6, n_molecules=200, L=33, n_tid=3),
+               dict(seed=7, n_molecules=150, L=150, mapq_mixed=True)):
+        pairs = pack.to_pairs(synth.generate(**kw).to_packed().fields)
+        short = pack.to_classes(pairs)
+        assert short is not None
+        p16, classes = short
+        assert p16.dtype.itemsize == 16 and classes.dtype.itemsize == 32 and len(p16) == len(pairs)
+        assert 0 < len(classes) <= len(pairs) and int(p16["cls"].max()) == len(classes) - 1
+        assert pack.from_classes(p16, classes).tobytes() == pairs.tobytes()
+    odd = pairs.copy()
+    odd["tlen2"][3] += 1                                   # TLENs that are not each other's negatives
+    assert pack.to_classes(odd) is None
+    far = pairs.copy()
+    far["tlen1"][5], far["tlen2"][5] = 40000, -40000       # does not fit 16 bits
+    assert pack.to_classes(far) is None
+    many = np.zeros(70000, pack.PAIR_DT)
+    many["cig"] = np.arange(70000)                          # more classes than a u16 names
+    assert pack.to_classes(many) is None
+    assert pack.to_classes(many[:65536]) is not None
+
+
 @pytest.mark.parametrize("wl,total", [("c3", 60_000), ("c4", 120_000)])
 def test_cytoband_sharded_dataset_is_the_same_whoever_makes_it(wl, total):
     """workloads.py: band b's reads depend on (seed, b) only, ranks own disjoint bands, and the generator's own
@@ -242,3 +266,23 @@ def test_cytoband_sharded_dataset_is_the_same_whoever_makes_it(wl, total):
             tid, lo, hi = pl.regions[b]
             keep |= (f[:, 2] == tid) & (f[:, 3] >= lo) & (f[:, 3] < hi) & (f[:, 5] >= lo) & (f[:, 5] < hi)
         assert np.array_equal(f[keep], fp)
+
+
+def test_bench_builds_the_compact_forms_like_pack_does():
+    """bench.py makes the inputs of cc_run_host_compact / cc_run_host_classes with torch (on the device, when there is
+    one); pack.to_compact / pack.to_classes are the host statements: same bytes."""
+    torch = pytest.importorskip("torch")
+    import types
+    import bench
+    p = synth.generate(seed=5, n_molecules=1500, L=100, n_tid=3, mapq_mixed=True).to_packed()
+    f = torch.from_numpy(np.ascontiguousarray(p.fields).view(np.int32).reshape(-1, 8).copy())
+    b = types.SimpleNamespace(fields=f, payload=torch.from_numpy(p.payload.copy()), lpad=p.lpad)
+    pairs_t, planes_t, qbits, qt, bt = bench.device_compact(b)
+    pairs, planes, qbits_h, qt_h, bt_h = pack.to_compact(p)
+    assert pairs_t.numpy().tobytes() == pairs.tobytes() and np.array_equal(planes_t.numpy(), planes)
+    assert qbits == qbits_h and np.array_equal(qt.numpy(), qt_h) and np.array_equal(bt.numpy(), bt_h)
+    p16_t, classes_t = bench.device_classes(pairs_t)
+    p16 = p16_t.numpy().view(pack.PAIR16_DT).reshape(-1)
+    classes = classes_t.numpy().view(pack.CLASS_DT).reshape(-1)
+    assert len(classes) == len(pack.to_classes(pairs)[1])
+    assert pack.from_classes(p16, classes).tobytes() == pairs.tobytes()
