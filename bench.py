@@ -63,6 +63,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-contexts", type=int, default=2, help="contexts the end-to-end leg rotates over")
+    ap.add_argument("--e2e-output", default="auto", choices=["auto", "rows", "planes"],
+                    help="end-to-end leg: read the consensus rows back as they are, or in bit planes (cc_pack_rows) when they fit")
     ap.add_argument("--e2e-format", default="auto", choices=["auto", "q8", "q4", "planes", "classes"],
                     help="host row format of the end-to-end leg: 8-bit qualities (cc_run_host), 4-bit quality "
                          "codes (cc_run_host_q4), or both with the compact one reported when the batch allows it")
@@ -640,8 +642,11 @@ def main():
                 h_pairs16.copy_(short[0]); h_classes.copy_(short[1])
             torch.cuda.synchronize(dev)
             planes = short = None
-        fmt = {"name": "q8"}
+        fmt = {"name": "q8", "out": "rows"}
         import ctypes
+        plane_of = {"sscs_rows": "sscs_planes", "corr_rows": "corr_planes", "dcssc_rows": "dcssc_planes"}
+        pk_qbits, pk_stride = ctypes.c_uint32(0), ctypes.c_uint32(0)
+        pk_qual, pk_base = (ctypes.c_uint8 * 16)(), (ctypes.c_uint8 * 16)()
 
         def e2e_step(which, step_no):
             e = engines[which]
@@ -661,8 +666,12 @@ def main():
                                            batch.stride, h_dup.data_ptr(), batch.n_bc))
             total = 0
             whats, dsts, sizes = [], [], []
+            in_planes = False
+            if fmt["out"] == "planes":          # rows once more in bit planes on the device: half the bytes to read back
+                e._check(e.lib.cc_pack_rows(e.ctx, ctypes.byref(pk_qbits), ctypes.byref(pk_stride), pk_qual, pk_base))
+                in_planes = pk_qbits.value > 0
             for nm in out_names:
-                what = ARRAYS[nm][0]
+                what = ARRAYS[plane_of[nm] if in_planes and nm in plane_of else nm][0]
                 nbytes = e.lib.cc_array_bytes(e.ctx, what)
                 if nbytes == 0:
                     continue
@@ -690,8 +699,8 @@ def main():
 
         e2e_steps = max(4, min(args.steps, 8)) // n_ctx * n_ctx or n_ctx
 
-        def measure(name):
-            fmt["name"] = name
+        def measure(name, out="rows"):
+            fmt["name"], fmt["out"] = name, out
             run_steps(2 * n_ctx)               # warm-up: allocations, pinning of the result buffers
             barrier()
             t0 = time.perf_counter()
@@ -724,7 +733,18 @@ def main():
         if h_pairs16 is not None:
             legs["classes"] = measure("classes")
         best = "classes" if "classes" in legs else "planes" if "planes" in legs else "q4" if "q4" in legs else "q8"
+        rows_back = None
+        if best in ("classes", "planes") and args.e2e_output in ("auto", "planes"):
+            packed_leg = measure(best, "planes")
+            if pk_qbits.value > 0:              # (more than 16 quality / base combinations in the results: rows as they are)
+                rows_back = {k: legs[best][k] for k in ("value", "ms_per_step", "d2h_bytes_per_step")}
+                legs[best] = packed_leg
         e2e = dict(legs[best])
+        e2e["output_format"] = ("cc_pack_rows: consensus rows read back as 2-bit bases + %d-bit (quality, literal base) codes, "
+                                "%d bytes per row instead of %d" % (pk_qbits.value, pk_stride.value, batch.stride)
+                                if rows_back else "rows as the kernels write them (%d bytes each)" % batch.stride)
+        if rows_back:
+            e2e["plain_rows_back"] = rows_back
         e2e["input_format"] = {
             "classes": "cc_run_host_classes: 16-byte pair records + %d classes + rows of 2-bit bases and %d-bit quality "
                        "codes (%d bytes per read)" % (h_classes.shape[0] if h_classes is not None else 0,

@@ -135,6 +135,11 @@ struct cc_ctx {
     bool have_reads = false, grouped = false, listed = false, voted = false, joined = false, rescued = false;
     bool read_fam_ready = false;
     bool dcssc_row_ready = true;                // CC_DCSSC_ROW holds ranks until somebody asks for it (materialise)
+    // cc_pack_rows: the produced rows once more, in bit planes
+    DevBuf planes_sscs, planes_corr, planes_dcs, alphabet;
+    bool packed = false;
+    uint32_t pack_qbits = 0, pack_stride = 0;
+    uint8_t pack_qual[16] = {}, pack_base[16] = {};
     bool by_classes = false;                    // loaded through cc_load_reads_classes: in_classes ends with a "bad class index" word
     bool stats_clean = false;                   // the 16 stage counters are zero (no classification has added to them)
     bool segments_ready = false;                // vstart / vsize / big_list / mid_list were written by the grouping, no vote has touched them
@@ -580,6 +585,7 @@ int do_group_pair(cc_ctx *ctx)
 int do_group(cc_ctx *ctx)
 {
     const uint64_t n = ctx->n;
+    ctx->packed = false;
     ctx->grouped = ctx->listed = ctx->voted = ctx->joined = ctx->rescued = ctx->read_fam_ready = false;
     ctx->n_fam = ctx->n_sscs = ctx->n_dcs = ctx->n_corr = ctx->n_dcssc = ctx->n_extra = 0;
     ctx->fam_bound = 0;
@@ -870,6 +876,7 @@ int launch_vote_pair(cc_ctx *ctx, uint32_t rows)
 int do_vote(cc_ctx *ctx)
 {
     const uint32_t rows = ctx->n_sscs;
+    ctx->packed = false;
     TRY(ensure(ctx, ctx->sscs_rows, (size_t)rows * ctx->stride));
     TRY(ensure(ctx, ctx->vstart, (size_t)rows * 4)); TRY(ensure(ctx, ctx->vsize, (size_t)rows * 4));
     TRY(ensure(ctx, ctx->big_list, (size_t)rows * 4));
@@ -937,6 +944,7 @@ int do_duplex(cc_ctx *ctx, bool after_sc)
     const uint32_t total = ctx->n_dcs + ctx->n_extra;
     const uint32_t rows = after_sc ? ctx->n_extra : ctx->n_dcs;
     const uint32_t first = after_sc ? ctx->n_dcs : 0;
+    ctx->packed = false;
     TRY(ensure(ctx, ctx->dcs_rows, (size_t)total * ctx->stride));
     TRY(ensure(ctx, ctx->dcs_mapq, total)); TRY(ensure(ctx, ctx->dcs_rg, total));
     TRY(ensure(ctx, ctx->dcs_flag, (size_t)total * 2)); TRY(ensure(ctx, ctx->dcs_tlen, (size_t)total * 4));
@@ -958,6 +966,7 @@ int do_duplex(cc_ctx *ctx, bool after_sc)
 int do_rescue(cc_ctx *ctx)
 {
     const uint32_t rows = ctx->n_corr;
+    ctx->packed = false;
     TRY(ensure(ctx, ctx->corr_rows, (size_t)rows * ctx->stride));
     TRY(phase_begin(ctx, CC_PH_RESCUE));
     if (rows) {
@@ -1034,7 +1043,7 @@ void cc_destroy(cc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->in_pairs, &ctx->in_classes, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
+    DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->in_pairs, &ctx->in_classes, &ctx->planes_sscs, &ctx->planes_corr, &ctx->planes_dcs, &ctx->alphabet, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
                      &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->stats,
                      &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
                      &ctx->fam_flag, &ctx->fam_tlen, &ctx->fam_rg, &ctx->partner, &ctx->table, &ctx->f_dcs, &ctx->f_corr,
@@ -1065,7 +1074,7 @@ int cc_set_params(cc_ctx *ctx, const cc_params *params)
     // the row lists, consensus rows and joins of the loaded batch were made with the old parameters:
     // later stages must not hand them out as current (the grouping does not depend on either value)
     if (params->cutoff != ctx->params.cutoff || (params->scorrect != 0) != (ctx->params.scorrect != 0))
-        ctx->voted = ctx->joined = ctx->rescued = false;
+        ctx->voted = ctx->joined = ctx->rescued = ctx->packed = false;
     ctx->params = *params;
     ctx->thr_valid = false;
     return CC_OK;
@@ -1388,6 +1397,10 @@ static const void *array_ptr(cc_ctx *ctx, int what, uint64_t *bytes)
     case CC_DCSSC_FLAG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 2ull; return ctx->dcs_flag.p;
     case CC_DCSSC_TLEN: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc * 4ull; return ctx->dcs_tlen.p;
     case CC_DCSSC_RG: if (!ctx->rescued) return nullptr; *bytes = ctx->n_dcssc; return ctx->dcs_rg.p;
+    case CC_SSCS_PLANES: if (!ctx->packed) return nullptr; *bytes = (uint64_t)ctx->n_sscs * ctx->pack_stride; return ctx->planes_sscs.p;
+    case CC_CORR_PLANES: if (!ctx->packed || !ctx->rescued) return nullptr; *bytes = (uint64_t)ctx->n_corr * ctx->pack_stride; return ctx->planes_corr.p;
+    case CC_DCS_PLANES: if (!ctx->packed || !ctx->joined) return nullptr; *bytes = (uint64_t)ctx->n_dcs * ctx->pack_stride; return ctx->planes_dcs.p;
+    case CC_DCSSC_PLANES: if (!ctx->packed || !ctx->rescued) return nullptr; *bytes = (uint64_t)ctx->n_dcssc * ctx->pack_stride; return ctx->planes_dcs.p;
     case CC_STATS: *bytes = 16 * 8; return ctx->stats.p;
     case CC_FAM_HIST: *bytes = CC_HIST_BINS * 8ull; return ctx->hist.p;
     default: return nullptr;
@@ -1424,6 +1437,66 @@ const void *cc_device_ptr(cc_ctx *ctx, int what)
     if (!p || bytes == 0) return nullptr;
     if (cudaSetDevice(ctx->device) != cudaSuccess || materialise(ctx, what) != CC_OK) return nullptr;
     return p;
+}
+
+int cc_pack_rows(cc_ctx *ctx, uint32_t *qbits, uint32_t *stride_c, uint8_t qual_table[16], uint8_t base_table[16])
+{
+    if (!ctx || !qbits || !stride_c || !qual_table || !base_table) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->voted) return fail(ctx, CC_ERR_ARG, "cc_pack_rows before cc_sscs_vote");
+    *qbits = 0; *stride_c = 0;
+    memset(qual_table, 0, 16); memset(base_table, 0xFF, 16);
+    struct Part { DevBuf *src; DevBuf *dst; uint64_t rows; };
+    const Part parts[3] = {{&ctx->sscs_rows, &ctx->planes_sscs, ctx->n_sscs},
+                           {&ctx->corr_rows, &ctx->planes_corr, ctx->rescued ? ctx->n_corr : 0},
+                           {&ctx->dcs_rows, &ctx->planes_dcs, ctx->rescued ? ctx->n_dcssc : ctx->joined ? ctx->n_dcs : 0}};
+    const uint32_t lpad = ctx->lpad, lanes = lpad / 16;
+    if (!ctx->packed) {
+        // which (quality, literal base) combinations occur: 65 536 presence bits (+ the pack kernels' "does not fit" word)
+        TRY(ensure(ctx, ctx->alphabet, (ALPHA_WORDS + 1) * sizeof(uint32_t)));
+        uint32_t *seen = ptr<uint32_t>(ctx->alphabet);
+        CK(cudaMemsetAsync(seen, 0, (ALPHA_WORDS + 1) * sizeof(uint32_t), ctx->stream));
+        for (const Part &p : parts)
+            if (p.rows)
+                LAUNCH(row_alphabet_kernel, (unsigned)std::min<uint64_t>(blocks_for(p.rows * lanes, 256), 148 * 8), 256,
+                       ptr<uint8_t>(*p.src), ctx->stride, lpad, p.rows, seen);
+        std::vector<uint32_t> host(ALPHA_WORDS);
+        CK(cudaMemcpyAsync(host.data(), seen, ALPHA_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        RowKeys keys;
+        memset(&keys, 0, sizeof(keys));
+        uint32_t found = 0;
+        for (uint32_t w = 0; w < ALPHA_WORDS; w++)
+            for (uint32_t bits = host[w]; bits; bits &= bits - 1) {
+                if (found < 16) keys.key[found] = (uint16_t)(w * 32 + (uint32_t)__builtin_ctz(bits));
+                found++;
+            }
+        if (found > 16) return CC_OK;                         // *qbits == 0: the rows do not fit, fetch them as they are
+        keys.count = found;
+        uint32_t qb = 1;
+        while ((1u << qb) < found) qb++;
+        ctx->pack_qbits = qb;
+        ctx->pack_stride = (lpad / 4 + lpad * qb / 8 + 15) / 16 * 16;
+        memset(ctx->pack_qual, 0, 16); memset(ctx->pack_base, 0xFF, 16);
+        for (uint32_t k = 0; k < found; k++) { ctx->pack_qual[k] = (uint8_t)(keys.key[k] >> 8); ctx->pack_base[k] = (uint8_t)(keys.key[k] & 0xFF); }
+        for (const Part &p : parts) {
+            if (!p.rows) continue;
+            TRY(ensure(ctx, *p.dst, p.rows * ctx->pack_stride));
+            const unsigned grid = blocks_for(p.rows * lanes, 256);
+            const uint8_t *in = ptr<uint8_t>(*p.src);
+            uint8_t *out = ptr<uint8_t>(*p.dst);
+            switch (qb) {
+            case 1: LAUNCH(pack_rows_kernel<1>, grid, 256, in, ctx->stride, lpad, p.rows, out, ctx->pack_stride, keys, seen + ALPHA_WORDS); break;
+            case 2: LAUNCH(pack_rows_kernel<2>, grid, 256, in, ctx->stride, lpad, p.rows, out, ctx->pack_stride, keys, seen + ALPHA_WORDS); break;
+            case 3: LAUNCH(pack_rows_kernel<3>, grid, 256, in, ctx->stride, lpad, p.rows, out, ctx->pack_stride, keys, seen + ALPHA_WORDS); break;
+            default: LAUNCH(pack_rows_kernel<4>, grid, 256, in, ctx->stride, lpad, p.rows, out, ctx->pack_stride, keys, seen + ALPHA_WORDS); break;
+            }
+        }
+        ctx->packed = true;
+    }
+    *qbits = ctx->pack_qbits; *stride_c = ctx->pack_stride;
+    memcpy(qual_table, ctx->pack_qual, 16); memcpy(base_table, ctx->pack_base, 16);
+    return CC_OK;
 }
 
 int cc_fetch(cc_ctx *ctx, int what, void *host_dst, uint64_t bytes)

@@ -831,6 +831,95 @@ expand_pairs_kernel(const uint2 *__restrict__ pairs, uint64_t n_pairs, uint4 *__
     fields[4 * k + 3] = make_uint4(b.x, b.y, d.y, m2);
 }
 
+// ---- result rows in bit planes (cc_pack_rows) ---------------------------------------------------------
+// The inverse of expand_planes_kernel for the rows the path produces.  A position's key is
+// quality << 8 | literal, literal = 0xFF for a plain A/C/G/T and the 4-bit base code otherwise (N, the padding
+// after the read's end).  row_alphabet_kernel marks the keys that occur (65 536 bits); with at most 16 of them
+// pack_rows_kernel writes 2-bit bases + QBITS-bit codes in the layout of cc_load_reads_compact's planes.
+constexpr int ALPHA_WORDS = 65536 / 32;
+
+__device__ __forceinline__ uint32_t row_key(uint32_t nib, uint32_t q)
+{
+    const bool plain = nib == 1u || nib == 2u || nib == 4u || nib == 8u;
+    return (q << 8) | (plain ? 0xFFu : nib);
+}
+
+__global__ void __launch_bounds__(256)
+row_alphabet_kernel(const uint8_t *__restrict__ rows, uint32_t stride, uint32_t lpad, uint64_t n_rows, uint32_t *__restrict__ seen)
+{
+    __shared__ uint32_t s_seen[ALPHA_WORDS];
+    for (int k = threadIdx.x; k < ALPHA_WORDS; k += blockDim.x) s_seen[k] = 0;
+    __syncthreads();
+    const uint32_t lanes = lpad / 16, half = lpad / 2;
+    const uint64_t total = n_rows * lanes;
+    for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t row = t / lanes;
+        const uint32_t lane = (uint32_t)(t % lanes);
+        const uint8_t *src = rows + row * stride;
+        const uint2 b = *reinterpret_cast<const uint2 *>(src + lane * 8);
+        const uint4 q = *reinterpret_cast<const uint4 *>(src + half + lane * 16);
+        const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+        uint32_t last = 0xFFFFFFFFu;
+#pragma unroll
+        for (int p = 0; p < 16; p++) {
+            const uint32_t nib = ((p < 8 ? b.x : b.y) >> (4 * (p & 7))) & 15u;
+            const uint32_t key = row_key(nib, (qw[p >> 2] >> (8 * (p & 3))) & 0xFFu);
+            if (key == last) continue;                                  // runs of one key are the rule
+            last = key;
+            if (!((s_seen[key >> 5] >> (key & 31)) & 1u)) atomicOr(&s_seen[key >> 5], 1u << (key & 31));
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < ALPHA_WORDS; k += blockDim.x)
+        if (s_seen[k]) atomicOr(&seen[k], s_seen[k]);
+}
+
+struct RowKeys { uint16_t key[16]; uint32_t count; };
+
+template <int QBITS>
+__global__ void __launch_bounds__(256)
+pack_rows_kernel(const uint8_t *__restrict__ rows, uint32_t stride, uint32_t lpad, uint64_t n_rows,
+                 uint8_t *__restrict__ out, uint32_t stride_c, RowKeys keys, uint32_t *__restrict__ misfit)
+{
+    __shared__ uint8_t s_code[17][256];                 // [literal, 16 = plain A/C/G/T][quality] -> code, 0xFF = none
+    for (int k = threadIdx.x; k < 17 * 256 / 4; k += blockDim.x) reinterpret_cast<uint32_t *>(&s_code[0][0])[k] = 0xFFFFFFFFu;
+    __syncthreads();
+    if (threadIdx.x < keys.count) {
+        const uint32_t key = keys.key[threadIdx.x], lit = key & 0xFFu;
+        s_code[lit == 0xFFu ? 16 : (lit & 15u)][key >> 8] = (uint8_t)threadIdx.x;
+    }
+    __syncthreads();
+    const uint32_t lanes = lpad / 16, half = lpad / 2;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t row = t / lanes;
+    const uint32_t lane = (uint32_t)(t % lanes);
+    if (row >= n_rows) return;
+    const uint8_t *src = rows + row * stride;
+    uint8_t *dst = out + row * stride_c;
+    const uint2 b = *reinterpret_cast<const uint2 *>(src + lane * 8);
+    const uint4 q = *reinterpret_cast<const uint4 *>(src + half + lane * 16);
+    const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+    uint32_t b2 = 0;
+    unsigned long long codes = 0;
+    bool bad = false;
+#pragma unroll
+    for (int p = 0; p < 16; p++) {
+        const uint32_t nib = ((p < 8 ? b.x : b.y) >> (4 * (p & 7))) & 15u;
+        const uint32_t qv = (qw[p >> 2] >> (8 * (p & 3))) & 0xFFu;
+        const bool plain = nib == 1u || nib == 2u || nib == 4u || nib == 8u;
+        const uint32_t code = s_code[plain ? 16 : nib][qv];
+        bad |= code == 0xFFu;
+        if (plain) b2 |= (uint32_t)(__ffs(nib) - 1) << (2 * p);
+        codes |= (unsigned long long)(code & ((1u << QBITS) - 1u)) << (p * QBITS);
+    }
+    if (bad) atomicAdd(misfit, 1u);
+    *reinterpret_cast<uint32_t *>(dst + lane * 4) = b2;
+    uint16_t *qdst = reinterpret_cast<uint16_t *>(dst + lpad / 4 + lane * 2 * QBITS);
+#pragma unroll
+    for (int k = 0; k < QBITS; k++) qdst[k] = (uint16_t)(codes >> (16 * k));
+    for (uint32_t x = lpad / 4 + lpad * QBITS / 8 + lane * 4; x < stride_c; x += lanes * 4) *reinterpret_cast<uint32_t *>(dst + x) = 0;
+}
+
 // Short pair records (cc_load_reads_classes): what many pairs have in common - cigar pair, contigs, flags, MAPQs,
 // read groups - sits once in a class table; a pair keeps its barcode, its two positions, the first mate's TLEN
 // (the second mate's is its negative) and the number of its class.  16 bytes describe both 32-byte field records.

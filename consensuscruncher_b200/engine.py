@@ -27,6 +27,7 @@ ARRAYS = {
     "dcs_tlen": (18, np.int32), "dcs_rg": (19, np.uint8), "dcssc_mapq": (20, np.uint8),
     "dcssc_flag": (21, np.uint16), "dcssc_tlen": (22, np.int32), "dcssc_rg": (23, np.uint8),
     "stats": (24, np.int64), "fam_hist": (25, np.uint64),
+    "sscs_planes": (26, np.uint8), "corr_planes": (27, np.uint8), "dcs_planes": (28, np.uint8), "dcssc_planes": (29, np.uint8),
 }
 PHASES = ("h2d", "hash", "sort", "segment", "join", "classify", "vote", "rescue", "dcs", "dcs_sc", "vote_aux")
 CC_ERR_BASE, CC_ERR_DOMAIN = -4, -5
@@ -37,7 +38,7 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
            "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4",
-           "cc_load_reads_compact", "cc_run_host_compact", "cc_load_reads_classes", "cc_run_host_classes", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
+           "cc_load_reads_compact", "cc_run_host_compact", "cc_load_reads_classes", "cc_run_host_classes", "cc_pack_rows", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
 COMM_ID_BYTES = 128
 
 
@@ -105,6 +106,7 @@ def load_library(path=None):
     L.cc_load_reads_classes.argtypes = [vp, vp, vp, u32, vp, u64, u32, u32, u32, vp, vp, vp, u32]
     L.cc_run_host_classes.argtypes = [vp, vp, vp, u32, vp, u64, u32, u32, u32, vp, vp, vp, u32]
     L.cc_fetch_many.argtypes = [vp, u32, vp, vp, vp]
+    L.cc_pack_rows.argtypes = [vp, vp, vp, vp, vp]
     L.cc_comm_unique_id.argtypes = [vp]
     L.cc_comm_init.argtypes = [vp, vp, i32, i32]
     L.cc_stats_allreduce.argtypes = [vp]
@@ -127,6 +129,7 @@ class GpuConsensus:
         self.device = int(device)
         self.lpad = self.stride = 0
         self._keep = None
+        self.packing = None
 
     # -- plumbing ----------------------------------------------------------
     def close(self):
@@ -267,6 +270,8 @@ class GpuConsensus:
             self._check(self.lib.cc_fetch(self.ctx, what, out.ctypes.data, nbytes))
         if name.endswith("_rows"):
             out = out.reshape(-1, self.stride)
+        if name.endswith("_planes") and self.packing:
+            out = out.reshape(-1, self.packing[1])
         return out
 
     def device_ptr(self, name):
@@ -280,11 +285,33 @@ class GpuConsensus:
         outs = [np.zeros(sizes[j] // np.dtype(ARRAYS[nm][1]).itemsize, ARRAYS[nm][1]) for j, nm in enumerate(names)]
         dsts = (ctypes.c_void_p * k)(*[o.ctypes.data if o.size else None for o in outs])
         self._check(self.lib.cc_fetch_many(self.ctx, k, whats, dsts, sizes))
-        return {nm: (o.reshape(-1, self.stride) if nm.endswith("_rows") else o) for nm, o in zip(names, outs)}
+        shape = lambda nm, o: (o.reshape(-1, self.stride) if nm.endswith("_rows") else
+                               o.reshape(-1, self.packing[1]) if nm.endswith("_planes") and self.packing else o)
+        return {nm: shape(nm, o) for nm, o in zip(names, outs)}
 
-    def result(self) -> ConsensusResult:
+    def pack_rows(self):
+        """cc_pack_rows: the produced rows once more in bit planes.  (qbits, stride_c, qual_table, base_table), or
+        None when the rows hold more than 16 (quality, literal base) combinations."""
+        qbits, stride_c = ctypes.c_uint32(0), ctypes.c_uint32(0)
+        qt, bt = np.zeros(16, np.uint8), np.zeros(16, np.uint8)
+        self._check(self.lib.cc_pack_rows(self.ctx, ctypes.byref(qbits), ctypes.byref(stride_c), qt.ctypes.data, bt.ctypes.data))
+        self.packing = (qbits.value, stride_c.value, qt, bt) if qbits.value else None
+        return self.packing
+
+    def result(self, planes=False) -> ConsensusResult:
+        """Every result array.  planes=True reads the rows back in bit planes (half the bytes) when they fit and
+        expands them on the host - same result."""
         from .result import ALL_ARRAYS
-        arrays = self.fetch_many(list(ALL_ARRAYS))
+        names = list(ALL_ARRAYS)
+        if planes and self.pack_rows():
+            from .pack import planes_to_rows
+            qbits, _, qt, bt = self.packing
+            row_names = [nm for nm in names if nm.endswith("_rows")]
+            arrays = self.fetch_many([nm for nm in names if nm not in row_names] + [nm[:-4] + "planes" for nm in row_names])
+            for nm in row_names:
+                arrays[nm] = planes_to_rows(arrays.pop(nm[:-4] + "planes"), qbits, qt, bt, self.lpad)
+        else:
+            arrays = self.fetch_many(names)
         return ConsensusResult(self.lpad, self.stride, bool(self.params.scorrect), **arrays)
 
     def consensus(self, packed: PackedReads, compact=False) -> ConsensusResult:

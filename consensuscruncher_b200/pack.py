@@ -369,6 +369,13 @@ def from_compact(pairs, planes, qbits, qual_table, base_table, lpad):
     a["flag"], b["flag"] = pairs["flag1"], pairs["flag2"]
     a["mapq"], b["mapq"] = pairs["mapq1"], pairs["mapq2"]
     a["rg"], b["rg"] = pairs["rg1"], pairs["rg2"]
+    return f, planes_to_rows(planes, qbits, qual_table, base_table, lpad)
+
+
+def planes_to_rows(planes, qbits, qual_table, base_table, lpad):
+    """Standard payload rows from rows in bit planes (the host statement of expand_planes_kernel; also how a host
+    reads the CC_*_PLANES arrays of cc_pack_rows)."""
+    n = planes.shape[0]
     half = lpad // 2
     _, stride = row_geometry(lpad)
     bp = planes[:, :lpad // 4]
@@ -382,7 +389,7 @@ def from_compact(pairs, planes, qbits, qual_table, base_table, lpad):
     out = np.zeros((n, stride), np.uint8)
     out[:, :half] = base[:, 0::2] | (base[:, 1::2] << 4)
     out[:, half:half + lpad] = qual_table[codes]
-    return f, out
+    return out
 
 
 def from_q4(payload4, table, lpad):

@@ -96,7 +96,9 @@ enum cc_array {
     CC_DCS_MAPQ = 16, CC_DCS_FLAG = 17, CC_DCS_TLEN = 18, CC_DCS_RG = 19,         /* per DCS row   */
     CC_DCSSC_MAPQ = 20, CC_DCSSC_FLAG = 21, CC_DCSSC_TLEN = 22, CC_DCSSC_RG = 23, /* per DCS-SC row */
     CC_STATS = 24,       /* [i64 x 16] see cc_stat                                    */
-    CC_FAM_HIST = 25     /* [u64 x CC_HIST_BINS] families per size (last bin: >= CC_HIST_BINS-1) */
+    CC_FAM_HIST = 25,    /* [u64 x CC_HIST_BINS] families per size (last bin: >= CC_HIST_BINS-1) */
+    /* the four row arrays once more in bit planes, after cc_pack_rows: [u8 x rows x stride_c] */
+    CC_SSCS_PLANES = 26, CC_CORR_PLANES = 27, CC_DCS_PLANES = 28, CC_DCSSC_PLANES = 29
 };
 
 #define CC_HIST_BINS 65536
@@ -252,6 +254,15 @@ int cc_fetch(cc_ctx *ctx, int what, void *host_dst, uint64_t bytes);
 /* Several result arrays at once: every copy is issued before the one wait (cc_fetch waits per array).
  * what[k] / host_dst[k] / bytes[k] as for cc_fetch; arrays of size 0 are skipped. */
 int cc_fetch_many(cc_ctx *ctx, uint32_t count, const int *what, void *const *host_dst, const uint64_t *bytes);
+/* Result rows in bit planes, for a host that pays for every byte it reads back.  Finds the (quality, literal
+ * base) combinations that occur in the rows produced so far; with at most 16 of them every row is written once
+ * more in the layout of cc_load_reads_compact's `planes` - lpad/4 bytes of 2-bit bases, lpad*qbits/8 bytes of
+ * codes, stride_c bytes per row; qual_table[code] / base_table[code] as there (0xff: take the 2-bit base; 15: N;
+ * 0: the padding after the read's end) - and CC_*_PLANES can be fetched instead of CC_*_ROWS (96 instead of 192
+ * bytes per row at lpad = 128).  *qbits == 0 on return: more than 16 combinations, fetch the rows as they are.
+ * Consensus qualities are 60, 0 or a lone supporter's own quality (SSCS_maker.py:139-153, DCS_maker.py:107-119),
+ * so binned input gives few of them.  Synchronises; a later stage call or cc_set_params discards the planes. */
+int cc_pack_rows(cc_ctx *ctx, uint32_t *qbits, uint32_t *stride_c, uint8_t qual_table[16], uint8_t base_table[16]);
 /* Size in bytes of result array `what` (0 if not produced yet). */
 uint64_t cc_array_bytes(cc_ctx *ctx, int what);
 /* Device address of result array `what` (NULL if not produced yet); valid until the next load. */

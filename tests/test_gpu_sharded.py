@@ -195,3 +195,37 @@ def test_short_pair_records_with_a_class_out_of_range_are_refused(engine):
                                         dup.ctypes.data, len(dup))
     assert rc == -2 and b"class" in engine.lib.cc_last_error(engine.ctx)          # CC_ERR_ARG
     helpers.assert_same_result(engine.consensus(packed, compact="classes"), oracle.run(packed, 0.7, True))
+
+
+@pytest.mark.parametrize("kw,scorrect", [(dict(seed=91, n_molecules=1500, L=128), True), (dict(seed=92, n_molecules=900, L=33, n_tid=3), True),
+                                         (dict(seed=93, n_molecules=600, L=250, mapq_mixed=True), False),
+                                         (dict(seed=94, n_molecules=40, L=100, dist="const", fam_mean=200), True)])
+def test_rows_read_back_in_bit_planes_are_the_same_rows(engine, kw, scorrect):
+    """cc_pack_rows: 2-bit bases + few-bit (quality, literal base) codes for every produced row; expanded on the
+    host they are the rows cc_fetch returns."""
+    from consensuscruncher_b200 import synth
+    packed = synth.generate(**kw).to_packed()
+    engine.set_params(cutoff=0.7, scorrect=scorrect)
+    engine.run_host(packed)
+    plain = engine.result()
+    helpers.assert_same_result(plain, oracle.run(packed, 0.7, scorrect))
+    via = engine.result(planes=True)
+    assert engine.packing is not None and 1 <= engine.packing[0] <= 4
+    helpers.assert_same_result(via, plain)
+    assert engine.fetch("sscs_planes").shape == (plain.sscs_rows.shape[0], engine.packing[1])
+    assert engine.packing[1] * 2 <= engine.stride + 32
+    engine.set_params(cutoff=0.9, scorrect=scorrect)          # another cutoff: the planes of the old rows are gone
+    assert engine.lib.cc_array_bytes(engine.ctx, 26) == 0
+
+
+def test_rows_with_many_distinct_qualities_stay_as_they_are(engine):
+    from consensuscruncher_b200 import synth
+    s = synth.generate(seed=95, n_molecules=800, L=100)
+    packed = s.to_packed()
+    half = packed.lpad // 2
+    q = packed.payload[:, half:half + 100]
+    q[...] = np.where(q > 2, np.random.default_rng(8).integers(3, 42, q.shape).astype(np.uint8), q)
+    engine.set_params(cutoff=0.7, scorrect=True)
+    engine.run_host(packed)
+    assert engine.pack_rows() is None and engine.lib.cc_array_bytes(engine.ctx, 26) == 0
+    helpers.assert_same_result(engine.result(planes=True), oracle.run(packed, 0.7, True))
