@@ -1591,6 +1591,30 @@ int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2,
     return CC_OK;
 }
 
+int cc_join_records(cc_ctx *ctx, const cc_fields *records, uint64_t n, const uint32_t *dup_bc, uint32_t n_bc, int32_t *partner)
+{
+    if (!ctx || (n && (!records || !partner)) || (n_bc && !dup_bc)) return CC_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) return CC_OK;
+    if (n >= (1ull << 31)) return fail(ctx, CC_ERR_TOO_LARGE, "cc_join_records: at most 2^31 - 1 records");
+    uint64_t slots = 64;
+    while (slots < 2 * n) slots <<= 1;
+    // staged: records, then the barcode table; the hash table; the answer
+    TRY(ensure(ctx, ctx->tmp_a, n * sizeof(cc_fields) + (size_t)n_bc * 4 + 256));
+    TRY(ensure(ctx, ctx->tmp_b, slots * 8));
+    TRY(ensure(ctx, ctx->tmp_c, n * 4));
+    uint32_t *d_dup = reinterpret_cast<uint32_t *>(ptr<uint8_t>(ctx->tmp_a) + n * sizeof(cc_fields));
+    CK(cudaMemcpyAsync(ctx->tmp_a.p, records, n * sizeof(cc_fields), cudaMemcpyHostToDevice, ctx->stream));
+    if (n_bc) CK(cudaMemcpyAsync(d_dup, dup_bc, (size_t)n_bc * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(ctx->tmp_b.p, 0, slots * 8, ctx->stream));
+    LAUNCH(record_build_kernel, blocks_for(n, 256), 256, ptr<uint4>(ctx->tmp_a), (uint32_t)n, ptr<unsigned long long>(ctx->tmp_b), slots - 1);
+    LAUNCH(record_probe_kernel, blocks_for(n, 256), 256, ptr<uint4>(ctx->tmp_a), (uint32_t)n, d_dup, n_bc,
+           ptr<unsigned long long>(ctx->tmp_b), slots - 1, ptr<int32_t>(ctx->tmp_c));
+    CK(cudaMemcpyAsync(partner, ctx->tmp_c.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return CC_OK;
+}
+
 int cc_sort_coordinates(cc_ctx *ctx, const int32_t *tid, const int32_t *pos, const uint16_t *flag, uint64_t n,
                         uint32_t *order)
 {

@@ -328,6 +328,49 @@ join_probe_kernel(const uint4 *__restrict__ fields, const uint32_t *__restrict__
     if (symmetric && found >= 0) partner[found] = (int32_t)c;
 }
 
+// ---- cc_join_records: the same join over records that stand for themselves ----------------------------
+// (the stand-alone DCS_maker / singleton_correction stage commands: one record per tag, so there are no
+// families to build first).  Every record goes into the table and every record probes; of several records
+// with the complementary key the one with the smallest index answers.
+__global__ void __launch_bounds__(256)
+record_build_kernel(const uint4 *__restrict__ fields, uint32_t n, unsigned long long *__restrict__ table, uint64_t mask)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    uint64_t h = rec_hash(load_rec(fields, c));
+    unsigned long long entry = ((h >> 32) << 32) | (unsigned long long)(c + 1);
+    uint64_t slot = (h * 0xD6E8FEB86659FD93ull >> 20) & mask;
+    while (atomicCAS(&table[slot], 0ull, entry) != 0ull) slot = (slot + 1) & mask;
+}
+
+__global__ void __launch_bounds__(256)
+record_probe_kernel(const uint4 *__restrict__ fields, uint32_t n, const uint32_t *__restrict__ dup_bc, uint32_t n_bc,
+                    const unsigned long long *__restrict__ table, uint64_t mask, int32_t *__restrict__ partner)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    Rec q = load_rec(fields, c);
+    uint32_t found = 0xFFFFFFFFu;
+    uint32_t d = q.a.x < n_bc ? __ldg(&dup_bc[q.a.x]) : NO_ID;
+    if (d != NO_ID) {
+        q.a.x = d;                 // barcode halves swapped
+        q.b.w ^= 0x40u;            // R1 <-> R2
+        uint64_t h = rec_hash(q);
+        uint32_t tag = (uint32_t)(h >> 32);
+        uint64_t slot = (h * 0xD6E8FEB86659FD93ull >> 20) & mask;
+        for (;;) {
+            unsigned long long e = table[slot];
+            if (e == 0ull) break;
+            if ((uint32_t)(e >> 32) == tag) {
+                uint32_t o = (uint32_t)e - 1u;
+                if (o < found && same_tag(load_rec(fields, o), q)) found = o;
+            }
+            slot = (slot + 1) & mask;
+        }
+    }
+    partner[c] = found == 0xFFFFFFFFu ? -1 : (int32_t)found;
+}
+
 // ---- classification of families into output classes ----------------------------------------
 // DCS_maker.py:233-253 (lead strand makes the DCS, the other is skipped, no partner ->
 // SSCS singleton); singleton_correction.py:258-283; second DCS pass over the merge of

@@ -38,7 +38,7 @@ SYMBOLS = ("cc_create", "cc_destroy", "cc_last_error", "cc_set_params", "cc_set_
            "cc_run_host", "cc_counts", "cc_fetch", "cc_array_bytes", "cc_device_ptr", "cc_consensus_maker",
            "cc_duplex_consensus", "cc_profile", "cc_phase_ms", "cc_kernel_launches", "cc_device_bytes",
            "cc_consensus_maker_static", "cc_sort_coordinates", "cc_load_reads_q4", "cc_run_host_q4",
-           "cc_load_reads_compact", "cc_run_host_compact", "cc_load_reads_classes", "cc_run_host_classes", "cc_pack_rows", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
+           "cc_load_reads_compact", "cc_run_host_compact", "cc_load_reads_classes", "cc_run_host_classes", "cc_pack_rows", "cc_join_records", "cc_fetch_many", "cc_comm_unique_id", "cc_comm_init", "cc_stats_allreduce", "cc_comm_destroy", "cc_comm_info")
 COMM_ID_BYTES = 128
 
 
@@ -107,6 +107,7 @@ def load_library(path=None):
     L.cc_run_host_classes.argtypes = [vp, vp, vp, u32, vp, u64, u32, u32, u32, vp, vp, vp, u32]
     L.cc_fetch_many.argtypes = [vp, u32, vp, vp, vp]
     L.cc_pack_rows.argtypes = [vp, vp, vp, vp, vp]
+    L.cc_join_records.argtypes = [vp, vp, u64, vp, u32, vp]
     L.cc_comm_unique_id.argtypes = [vp]
     L.cc_comm_init.argtypes = [vp, vp, i32, i32]
     L.cc_stats_allreduce.argtypes = [vp]
@@ -342,6 +343,16 @@ class GpuConsensus:
         return self.result()
 
     # -- stand-alone primitives ----------------------------------------------------
+    def join_records(self, fields, dup_bc):
+        """cc_join_records: index of the record with the complementary key, or -1, for every record."""
+        fields = np.ascontiguousarray(fields)
+        dup = np.ascontiguousarray(dup_bc, dtype=np.uint32)
+        out = np.full(len(fields), -1, np.int32)
+        if len(fields):
+            self._check(self.lib.cc_join_records(self.ctx, fields.ctypes.data, len(fields), dup.ctypes.data if len(dup) else None,
+                                                 len(dup), out.ctypes.data))
+        return out
+
     def consensus_maker_rows(self, rows, lpad, cutoff):
         rows = np.ascontiguousarray(rows, np.uint8)
         out = np.zeros(rows.shape[1], np.uint8)

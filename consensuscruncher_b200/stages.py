@@ -9,10 +9,12 @@ interface - same arguments, same files next to `--outfile` / `--singleton`:
   sc_main        singleton_correction.py --singleton [--bedfile]                     (singleton_correction.py:111-311)
 
 The SSCS stage is the GPU grouping + vote (cc_group, cc_sscs_vote).  The DCS and rescue
-stages read consensus BAMs in which every family is a single record, so their bookkeeping
-(which tag pairs with which, in which order, region by region) is replayed on the host with
-the reference's rules, and the per-base arithmetic of all pairs goes to the GPU in one batch
-(cc_duplex_consensus).  Mode ties take the first value, as everywhere in this package.
+stages read consensus BAMs in which every family is a single record: which tag pairs with
+which is the device's hash join over those records (cc_join_records, once per region, in place
+of `duplex_tag` strings and dictionary probes), the per-base arithmetic of all pairs goes to
+the GPU in one batch (cc_duplex_consensus), and the host keeps what is left of the reference's
+bookkeeping - the order of emission and what a region loop forgets between regions.  Mode ties
+take the first value, as everywhere in this package.
 """
 from __future__ import annotations
 
@@ -77,6 +79,7 @@ class _Families:
         self.members = OrderedDict()      # tag -> [reads]            (read_dict)
         self.size = {}                    # tag -> count              (tag_dict)
         self.names = OrderedDict()        # pair name -> [tags]       (csn_pair_dict)
+        self.key = {}                     # tag -> (barcode, cigar pair, first read): the tag as a tuple, for the device join
         self.total = self.unmapped_mate = self.multiple = 0
 
     def feed(self, reads, indices):
@@ -101,12 +104,32 @@ class _Families:
                 if tag not in self.members and tag not in self.size:
                     self.members[tag] = [x]
                     self.size[tag] = 1
+                    self.key[tag] = (barcode, cigar, x)
                     owned = self.names.setdefault(name, [])
                     if len(owned) < 2:
                         owned.append(tag)
                 elif tag in self.size and tag in self.members:
                     self.members[tag].append(x)
                     self.size[tag] += 1
+
+
+def _join(engine, groups):
+    """[(families, tags)] -> partner index of every tag within the concatenation of the tag lists, or -1:
+    the record whose key is the tag's with the barcode halves swapped and R1 <-> R2 (duplex_tag,
+    consensus_helper.py:605-648), found by the device (cc_join_records); of several, the first."""
+    n = sum(len(tags) for _, tags in groups)
+    fields = np.zeros(n, pack.FIELDS_DT)
+    bc_ids, cig_ids = {}, {}
+    k = 0
+    for fam, tags in groups:
+        for tag in tags:
+            barcode, cigar, r = fam.key[tag]
+            f = fields[k]
+            f["bc"] = bc_ids.setdefault(barcode, len(bc_ids))
+            f["cig"] = cig_ids.setdefault(cigar, len(cig_ids))
+            f["tid"], f["pos"], f["mtid"], f["mpos"], f["flag"] = r.tid, r.pos, r.mtid, r.mpos, r.flag
+            k += 1
+    return engine.join_records(fields, pack.build_dup_table(list(bc_ids)))
 
 
 def _pair_mode(a, b, is_flag=False):
@@ -190,28 +213,39 @@ def run_dcs(infile, outfile, bedfile=None, engine=None):
     single_path = base + (".sscs.sc.singleton.bam" if after_sc else ".sscs.singleton.bam")
     fam = _Families()
     index = _position_index(reads) if bedfile is not None else None
-    made = set()
+    made, made_before = set(), set()  # tags that led a DCS (in this region / in earlier regions)
     jobs, plan = [], []              # plan: ("dcs", job index, lead, partner) | ("single", read)
-    for region in _regions(bedfile, header):
-        fam.feed(reads, _visit(reads, region, index))
-        for name in list(fam.names):
-            for tag in fam.names[name]:
-                ds = keys.duplex_tag(tag)
-                if ds in made:
-                    continue
-                if tag not in fam.members:
-                    continue
-                if tag in fam.size and ds in fam.size and ds in fam.members:
-                    lead, other = fam.members[tag][0], fam.members[ds][0]
-                    plan.append(("dcs", len(jobs), lead, other))
-                    jobs.append((lead, other))
-                    made.add(tag)
-                else:
-                    plan.append(("single", fam.members[tag][0]))
-                del fam.members[tag]
-            del fam.names[name]
     eng, own = _get_engine(engine)
     try:
+        for region in _regions(bedfile, header):
+            fam.feed(reads, _visit(reads, region, index))
+            tags = list(fam.members)
+            where = {t: i for i, t in enumerate(tags)}
+            partner = _join(eng, [(fam, tags)])
+            for name in list(fam.names):
+                for tag in fam.names[name]:
+                    if tag not in fam.members:
+                        continue
+                    j = int(partner[where[tag]])
+                    if j >= 0:
+                        ds = tags[j]
+                    elif made_before:
+                        ds = keys.duplex_tag(tag)          # (not among this region's tags: only an earlier region can have made it)
+                    else:
+                        ds = None
+                    if ds is not None and (ds in made or ds in made_before):
+                        continue
+                    if j >= 0 and ds in fam.members:       # (a member has a size: DCS_maker.py:236)
+                        lead, other = fam.members[tag][0], fam.members[ds][0]
+                        plan.append(("dcs", len(jobs), lead, other))
+                        jobs.append((lead, other))
+                        made.add(tag)
+                    else:
+                        plan.append(("single", fam.members[tag][0]))
+                    del fam.members[tag]
+                del fam.names[name]
+            made_before |= made
+            made = set()
         results = _agree_batch(eng, jobs, sc=False)
     finally:
         if own:
@@ -252,39 +286,50 @@ def run_sc(singleton_path, bedfile=None, engine=None):
     jobs, plan = [], []              # ("sscs" | "singleton", job, read, qname) | ("uncorrected", read)
     pending = {}                     # singleton-by-singleton corrections waiting for their partner's turn
     counter = 0
-    for region in _regions(bedfile, header):
-        if region is not None and region[1] != last_chr:
-            # a new chromosome forgets the SSCS seen so far and the singleton sizes (singleton_correction.py:192-200)
-            s_fam.size = {}
-            kept_total = c_fam.total
-            c_fam = _Families()
-            c_fam.total = kept_total
-            last_chr = region[1]
-        s_fam.feed(singles, _visit(singles, region, s_index))
-        c_fam.feed(sscs, _visit(sscs, region, c_index))
-        for name in list(s_fam.names):
-            for tag in s_fam.names[name]:
-                counter += 1
-                ds = keys.duplex_tag(tag)
-                qname = name + ":1"
-                read = s_fam.members[tag][0]
-                if ds in c_fam.members:
-                    plan.append(("sscs", len(jobs), read, qname))
-                    jobs.append((read, c_fam.members[ds][0]))
-                    del c_fam.members[ds]
-                    del s_fam.members[tag]
-                elif ds in s_fam.members:
-                    plan.append(("singleton", len(jobs), read, qname))
-                    jobs.append((read, s_fam.members[ds][0]))
-                    pending[tag] = ds
-                    if ds in pending:
-                        del s_fam.members[tag], s_fam.members[ds], pending[tag], pending[ds]
-                else:
-                    plan.append(("uncorrected", read))
-                    del s_fam.members[tag]
-            del s_fam.names[name]
     eng, own = _get_engine(engine)
     try:
+        for region in _regions(bedfile, header):
+            if region is not None and region[1] != last_chr:
+                # a new chromosome forgets the SSCS seen so far and the singleton sizes (singleton_correction.py:192-200)
+                s_fam.size = {}
+                kept_total = c_fam.total
+                c_fam = _Families()
+                c_fam.total = kept_total
+                last_chr = region[1]
+            s_fam.feed(singles, _visit(singles, region, s_index))
+            c_fam.feed(sscs, _visit(sscs, region, c_index))
+            # the device's join: a singleton's partner among the SSCS first (they come first in the concatenation),
+            # else among the singletons; the second call answers for singletons whose SSCS partner is already taken
+            c_tags, s_tags = list(c_fam.members), list(s_fam.members)
+            nc = len(c_tags)
+            where = {t: i for i, t in enumerate(s_tags)}
+            both = _join(eng, [(c_fam, c_tags), (s_fam, s_tags)])
+            among_singles = _join(eng, [(s_fam, s_tags)])
+            for name in list(s_fam.names):
+                for tag in s_fam.names[name]:
+                    counter += 1
+                    qname = name + ":1"
+                    read = s_fam.members[tag][0]
+                    i = where[tag]
+                    jc, js = int(both[nc + i]), int(among_singles[i])
+                    by_sscs = c_tags[jc] if 0 <= jc < nc else None
+                    by_single = s_tags[js] if js >= 0 else None
+                    if by_sscs is not None and by_sscs in c_fam.members:
+                        plan.append(("sscs", len(jobs), read, qname))
+                        jobs.append((read, c_fam.members[by_sscs][0]))
+                        del c_fam.members[by_sscs]
+                        del s_fam.members[tag]
+                    elif by_single is not None and by_single in s_fam.members:
+                        ds = by_single
+                        plan.append(("singleton", len(jobs), read, qname))
+                        jobs.append((read, s_fam.members[ds][0]))
+                        pending[tag] = ds
+                        if ds in pending:
+                            del s_fam.members[tag], s_fam.members[ds], pending[tag], pending[ds]
+                    else:
+                        plan.append(("uncorrected", read))
+                        del s_fam.members[tag]
+                del s_fam.names[name]
         results = _agree_batch(eng, jobs, sc=True)
     finally:
         if own:

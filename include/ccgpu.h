@@ -278,6 +278,14 @@ int cc_consensus_maker(cc_ctx *ctx, const uint8_t *rows, uint32_t n, uint32_t lp
 int cc_duplex_consensus(cc_ctx *ctx, const uint8_t *rows1, const uint8_t *rows2, uint64_t n_pairs,
                         uint32_t lpad, uint32_t stride, int sc, uint8_t *out_rows);
 
+/* The duplex join over n records that stand for themselves (one record per tag, as in the SSCS and singleton
+ * files the stand-alone stage commands read): partner[i] = the record whose family key - barcode, cigar pair,
+ * contig / position of read and mate, strand and read-number bits - is record i's with the barcode halves swapped
+ * (dup_bc) and R1 <-> R2, or -1; of several such records the first.  Replaces duplex_tag
+ * (consensus_helper.py:605-648) and the dictionary probes of DCS_maker.py:229-247 and
+ * singleton_correction.py:253-270 in those commands.  Host buffers. */
+int cc_join_records(cc_ctx *ctx, const cc_fields *records, uint64_t n, const uint32_t *dup_bc, uint32_t n_bc, int32_t *partner);
+
 /* Coordinate sort of output records: the `samtools view -bu | samtools sort` of sort_index
  * (ConsensusCruncher.py:10-29) and, applied to concatenated inputs, `samtools merge`
  * (ConsensusCruncher.py:248,282).  order[k] = index of the record of rank k under the stable

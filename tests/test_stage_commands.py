@@ -57,3 +57,39 @@ def test_stage_chain_reproduces_reference_tree(tmp_path, name, engine):
         assert [r.key()[:12] for r in got] == exp, fname
     assert open(os.path.join(d, "s.stats.txt")).read() == g["stats"]
     assert open(os.path.join(d, "s.read_families.txt")).read() == g["read_families"]
+
+
+def test_record_join_equals_the_dictionary_probe(engine):
+    """cc_join_records against what the stage scripts do with strings: partner = the first record whose tuple is this
+    record's with the barcode swapped (through the table) and R1 <-> R2; records without one, records whose barcode
+    has no counterpart, several records under one key."""
+    import numpy as np
+    from consensuscruncher_b200 import pack
+    rng = np.random.default_rng(12)
+    n, n_bc = 20000, 37
+    f = np.zeros(n, pack.FIELDS_DT)
+    f["bc"] = rng.integers(0, n_bc, n)
+    f["cig"] = rng.integers(0, 3, n)
+    f["tid"] = rng.integers(0, 2, n)
+    f["pos"] = rng.integers(0, 40, n)
+    f["mtid"] = f["tid"]
+    f["mpos"] = f["pos"] + rng.integers(0, 3, n)
+    f["flag"] = rng.choice(np.array([99, 147, 83, 163], np.uint16), n)
+    f["tlen"], f["mapq"] = rng.integers(-9, 9, n), 60             # not part of the key
+    dup = rng.permutation(n_bc).astype(np.uint32)
+    dup[rng.random(n_bc) < 0.2] = pack.NO_ID
+    got = engine.join_records(f, dup)
+    key = lambda r, bc, bits: (int(bc), int(r["cig"]), int(r["tid"]), int(r["pos"]), int(r["mtid"]), int(r["mpos"]), bits)
+    bits = lambda r: (int(r["flag"]) >> 4 & 1, int(r["flag"]) >> 6 & 1)
+    first = {}
+    for i in range(n):
+        first.setdefault(key(f[i], f[i]["bc"], bits(f[i])), i)
+    exp = np.full(n, -1, np.int32)
+    for i in range(n):
+        d = dup[f[i]["bc"]]
+        if d != pack.NO_ID:
+            o, m = bits(f[i])
+            exp[i] = first.get(key(f[i], d, (o, m ^ 1)), -1)
+    assert (exp >= 0).sum() > 1000 and (exp < 0).sum() > 1000
+    assert np.array_equal(got, exp)
+    assert len(engine.join_records(f[:0], dup)) == 0
