@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Soak: many random small and medium batches through the GPU path against the oracle, each batch several times
 (members land in a family's segment in arrival order, so repeats exercise different interleavings of the atomics),
-every third one also with its pairs shuffled (the all-through-the-table grouping pass) and through the compact
-upload.  compute-sanitizer is closed on this pool (its wrapper refuses to run), so this - bit-exact agreement with
+every third one also with its pairs shuffled (the all-through-the-table grouping pass), through the most compact
+upload the batch fits and with the rows read back in bit planes.  compute-sanitizer is closed on this pool (its wrapper refuses to run), so this - bit-exact agreement with
 the CPU oracle over hundreds of cases and repeats, in every grouping mode (CCGPU_GROUP) - stands in for racecheck.
 python scripts/gpu_soak.py [first_seed] [count]"""
 import os, sys
@@ -33,6 +33,8 @@ with GpuConsensus(0) as eng:
         for rep in range(3):
             got = eng.consensus(packed, compact="auto" if rep == 2 else False)
             d = got.diff(exp)
+            if not d and rep == 1:                  # the same rows read back in bit planes (cc_pack_rows), when they fit
+                d = eng.result(planes=True).diff(exp)
             if d:
                 bad += 1
                 print("seed", seed, "rep", rep, "differs in", d)
