@@ -85,7 +85,7 @@ NcclApi &nccl_api()
 }
 
 enum Ctr { CT_NFAM = 0, CT_MIXED = 1, CT_NSSCS = 2, CT_NDCS = 3, CT_NCORR = 4, CT_NDCSSC = 5,
-           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_ASYM = 32, CT_ONESIDED = 33, CT_UNMIRRORED = 34, CT_BADCLASS = 35, CT_COUNT = 40 };
+           CT_FAULTS = 6, CT_ERR = 7, CT_TICKET0 = 8, CT_NMIDLIST = 28, CT_NMID = 29, CT_NBIG = 30, CT_NREDO = 31, CT_ASYM = 32, CT_ONESIDED = 33, CT_UNMIRRORED = 34, CT_BADCLASS = 35, CT_COUNT = 40 };
 
 }  // namespace
 
@@ -141,11 +141,13 @@ struct cc_ctx {
     uint32_t pack_qbits = 0, pack_stride = 0;
     uint8_t pack_qual[16] = {}, pack_base[16] = {};
     bool by_classes = false;                    // loaded through cc_load_reads_classes: in_classes ends with a "bad class index" word
+    uint64_t redo_off = 0;                      // big_list[redo_off ..]: rows the bulk vote kernel hands to the exact one
     bool stats_clean = false;                   // the 16 stage counters are zero (no classification has added to them)
     bool segments_ready = false;                // vstart / vsize / big_list / mid_list were written by the grouping, no vote has touched them
     // counters read back while later kernels run (cc_run): a side stream, "counters final" / "copy done" events, pinned words
     cudaStream_t side = nullptr;
     cudaEvent_t snap_src[2] = {nullptr, nullptr}, snap_done[2] = {nullptr, nullptr};
+    cudaEvent_t big_src = nullptr, big_done = nullptr;     // the vote of the largest families runs on the side stream
     uint32_t *pin_ctr = nullptr;                // [3][CT_COUNT]: two snapshots, read_counters
     uint32_t host_ctr[CT_COUNT];
     // bookkeeping
@@ -532,7 +534,7 @@ int do_group_pair(cc_ctx *ctx)
     TRY(ensure(ctx, ctx->sscs_list, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->sscs_row, n * 4));
     // the vote's per-row segments and its two lists of larger families are written with the family records
     TRY(ensure(ctx, ctx->vstart, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->vsize, (n / 2 + 2) * 4));
-    TRY(ensure(ctx, ctx->big_list, (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->mid_list, (n / 16 + 4) * 4));
+    TRY(ensure(ctx, ctx->big_list, 2 * (n / 2 + 2) * 4)); TRY(ensure(ctx, ctx->mid_list, (n / 16 + 4) * 4));
     const uint64_t ws_tiles = (words + WS_TILE - 1) / WS_TILE;
     TRY(ensure(ctx, ctx->scan_status, (2 * ws_tiles + 2) * sizeof(unsigned long long)));
     TRY(ensure(ctx, ctx->gt_state, (GTC_COUNT + STRETCH_SLOTS) * sizeof(uint32_t)));
@@ -856,7 +858,7 @@ int launch_vote_small(cc_ctx *ctx, uint32_t rows, uint32_t n_lo, uint32_t n_hi, 
         ptr<uint32_t>(ctx->sscs_list), row_list, rows, n_lo, n_hi, ptr<uint8_t>(ctx->thr_table),
         (1.0 >= ctx->params.cutoff) ? 1 : 0, ctx->thr_magic, ctx->fields, ptr<uint8_t>(ctx->sscs_rows),
         ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen), ptr<uint8_t>(ctx->fam_rg),
-        ptr<uint32_t>(ctx->counters) + CT_ERR, ptr<uint32_t>(ctx->big_list), ptr<uint32_t>(ctx->counters) + CT_NBIG);
+        ptr<uint32_t>(ctx->counters) + CT_ERR, ptr<uint32_t>(ctx->big_list) + ctx->redo_off, ptr<uint32_t>(ctx->counters) + CT_NREDO);
     ctx->launches++;
     CK(cudaGetLastError());
     return CC_OK;
@@ -879,13 +881,16 @@ int do_vote(cc_ctx *ctx)
     ctx->packed = false;
     TRY(ensure(ctx, ctx->sscs_rows, (size_t)rows * ctx->stride));
     TRY(ensure(ctx, ctx->vstart, (size_t)rows * 4)); TRY(ensure(ctx, ctx->vsize, (size_t)rows * 4));
-    TRY(ensure(ctx, ctx->big_list, (size_t)rows * 4));
+    // (two lists in one buffer: families of more than 127 reads, and behind them the rows the bulk kernel hands over;
+    //  the pair grouping has written the first one already - its buffer is sized for any count, so this never regrows it)
+    TRY(ensure(ctx, ctx->big_list, 2 * ((size_t)rows + 2) * 4));
+    ctx->redo_off = (size_t)rows + 2;
     TRY(ensure(ctx, ctx->mid_list, ((size_t)ctx->host_ctr[CT_NMID] + 1) * 4));
     if (!ctx->thr_valid) TRY(upload_thresholds(ctx));
     uint32_t *ctr = ptr<uint32_t>(ctx->counters);
     if (rows && !ctx->segments_ready) {
         // (a second vote of one batch comes here too: the first one marked rows in vsize and appended to big_list)
-        CK(cudaMemsetAsync(ctr + CT_NBIG, 0, 4, ctx->stream));
+        CK(cudaMemsetAsync(ctr + CT_NBIG, 0, 8, ctx->stream));       // and CT_NREDO behind it
         CK(cudaMemsetAsync(ctr + CT_NMIDLIST, 0, 4, ctx->stream));
         TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
         LAUNCH(vote_segments_kernel, blocks_for(rows, 256), 256, ptr<uint32_t>(ctx->sscs_list),
@@ -897,6 +902,21 @@ int do_vote(cc_ctx *ctx)
         TRY(phase_end(ctx, CC_PH_VOTE_AUX));
     }
     ctx->segments_ready = false;
+    if (rows) {
+        // The families of more than 127 reads (one CTA each, a 10^4-read family is a long chain of row loads) are
+        // voted on the side stream while the bulk kernel runs on this one: different families, different rows.
+        // What the bulk kernel hands over (rows with a quality byte >= 128) is a list of its own, voted after both.
+        CK(cudaEventRecord(ctx->big_src, ctx->stream));
+        CK(cudaStreamWaitEvent(ctx->side, ctx->big_src, 0));
+        vote_big_kernel<<<148 * 8, 256, 0, ctx->side>>>(
+            ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm, ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize),
+            ptr<uint32_t>(ctx->sscs_list), ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG, ctx->params.cutoff,
+            ptr<uint8_t>(ctx->sscs_rows), ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
+            ptr<uint8_t>(ctx->fam_rg), ctr + CT_ERR);
+        ctx->launches++;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ctx->big_done, ctx->side));
+    }
     TRY(phase_begin(ctx, CC_PH_VOTE));
     if (rows && ctx->lpad <= 512) {
         const uint32_t lanes = (ctx->lpad + 15) / 16;
@@ -909,9 +929,10 @@ int do_vote(cc_ctx *ctx)
     TRY(phase_end(ctx, CC_PH_VOTE));
     if (rows) {
         TRY(phase_begin(ctx, CC_PH_VOTE_AUX));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->big_done, 0));
         LAUNCH(vote_big_kernel, 148 * 8, 256, ctx->fields, ctx->payload, ctx->stride, ctx->lpad, ctx->perm,
                ptr<uint32_t>(ctx->vstart), ptr<uint32_t>(ctx->vsize), ptr<uint32_t>(ctx->sscs_list),
-               ptr<uint32_t>(ctx->big_list), ctr + CT_NBIG, ctx->params.cutoff, ptr<uint8_t>(ctx->sscs_rows),
+               ptr<uint32_t>(ctx->big_list) + ctx->redo_off, ctr + CT_NREDO, ctx->params.cutoff, ptr<uint8_t>(ctx->sscs_rows),
                ptr<uint8_t>(ctx->fam_mapq), ptr<uint16_t>(ctx->fam_flag), ptr<int32_t>(ctx->fam_tlen),
                ptr<uint8_t>(ctx->fam_rg), ctr + CT_ERR);
         TRY(phase_end(ctx, CC_PH_VOTE_AUX));
@@ -1030,6 +1051,8 @@ cc_ctx *cc_create(int device, const cc_params *params)
     for (int k = 0; k < 2 && ok; k++)
         ok = cudaEventCreateWithFlags(&ctx->snap_src[k], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&ctx->snap_done[k], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&ctx->big_src, cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&ctx->big_done, cudaEventDisableTiming) == cudaSuccess;
     if (!ok) {
         g_create_error = "cudaStreamCreate / cudaMallocHost / cudaEventCreate failed";
         cc_destroy(ctx);
@@ -1043,6 +1066,7 @@ void cc_destroy(cc_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->side) cudaStreamSynchronize(ctx->side);
     DevBuf *all[] = {&ctx->in_fields, &ctx->in_payload, &ctx->in_dup, &ctx->in_q4, &ctx->in_pairs, &ctx->in_classes, &ctx->planes_sscs, &ctx->planes_corr, &ctx->planes_dcs, &ctx->alphabet, &ctx->key_a, &ctx->key_b, &ctx->val_a, &ctx->val_b,
                      &ctx->head, &ctx->radix_counts, &ctx->scan_status, &ctx->counters, &ctx->stats,
                      &ctx->tmpl, &ctx->c2hs, &ctx->fam_start, &ctx->fam_size, &ctx->is_sscs, &ctx->fam_mapq,
@@ -1060,6 +1084,8 @@ void cc_destroy(cc_ctx *ctx)
         if (ctx->snap_src[k]) cudaEventDestroy(ctx->snap_src[k]);
         if (ctx->snap_done[k]) cudaEventDestroy(ctx->snap_done[k]);
     }
+    if (ctx->big_src) cudaEventDestroy(ctx->big_src);
+    if (ctx->big_done) cudaEventDestroy(ctx->big_done);
     if (ctx->pin_ctr) cudaFreeHost(ctx->pin_ctr);
     if (ctx->side) cudaStreamDestroy(ctx->side);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);

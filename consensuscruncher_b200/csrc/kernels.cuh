@@ -653,7 +653,7 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
                  uint32_t lpad, const uint32_t *__restrict__ perm, uint32_t start, uint32_t n, double cutoff,
                  uint8_t *__restrict__ out, uint32_t c, uint8_t *__restrict__ fam_mapq,
                  uint16_t *__restrict__ fam_flag, int32_t *__restrict__ fam_tlen, uint8_t *__restrict__ fam_rg,
-                 uint32_t *__restrict__ err_flag, uint32_t *scratch = nullptr)
+                 uint32_t *__restrict__ err_flag, uint32_t *scratch = nullptr, bool mixed = true)
 {
     const int lane = threadIdx.x & 31;
     const int warp = WARPS > 1 ? (int)(threadIdx.x >> 5) : 0;
@@ -676,15 +676,22 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
             // lanes fetch 32 member indices at once, then the warp walks the rows together
             uint32_t mine = (j0 + lane < n) ? perm[start + j0 + lane] : 0;
             uint32_t lim = min(32u, n - j0);
-            for (uint32_t jj = 0; jj < lim; jj++) {
-                uint32_t r = __shfl_sync(0xffffffffu, mine, jj);
-                if (active) {
+            // eight rows at a time: all their loads are issued before the first tally (a family of 10^4 reads is one
+            // CTA's work, so the latency of a row must not add up row by row); rows past the end tally nothing (q = 0)
+            for (uint32_t jj = 0; jj < lim; jj += 8) {
+                uint32_t s16[8], q[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const uint32_t r = __shfl_sync(0xffffffffu, mine, (jj + u) & 31);
+                    const bool on = active && jj + u < lim;
                     const uint8_t *src = payload + (uint64_t)r * stride;
-                    uint32_t s16 = *reinterpret_cast<const uint16_t *>(src + (p0 >> 1));
-                    uint32_t q = *reinterpret_cast<const uint32_t *>(src + half + p0);
-                    vote_row(acc, q, s16, err);
+                    s16[u] = on ? *reinterpret_cast<const uint16_t *>(src + (p0 >> 1)) : 0u;
+                    q[u] = on ? *reinterpret_cast<const uint32_t *>(src + half + p0) : 0u;
                 }
-                if (++since_flush == 255) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) vote_row(acc, q[u], s16[u], err);
+                since_flush += 8;
+                if (since_flush >= 248) {                      // byte counters hold 255
 #pragma unroll
                     for (int bi = 0; bi < 4; bi++) {
 #pragma unroll
@@ -755,6 +762,7 @@ vote_family_warp(const uint4 *__restrict__ fields, const uint8_t *__restrict__ p
     if (warp != 0) return;                                     // (after the last barrier)
     for (uint32_t x = half + lpad + lane * 4; x < stride; x += 128) *reinterpret_cast<uint32_t *>(out + x) = 0;
     if (err) atomicOr(err_flag, 1u);
+    if (!mixed) return;                                        // the grouping found one value per field: the template's, already written
 
     // ---- mode fields of the family (create_aligned_segment, consensus_helper.py:569-583)
     auto meta_of = [&](uint32_t j) { return __ldg(&fields[2 * (uint64_t)perm[start + j] + 1]); };

@@ -692,9 +692,10 @@ vote_big_kernel(const uint4 *__restrict__ fields, const uint8_t *__restrict__ pa
     const uint32_t total = *n_big;
     for (uint32_t i = blockIdx.x; i < total; i += gridDim.x) {
         const uint32_t row = big_list[i];
-        vote_family_warp<8>(fields, payload, stride, lpad, perm, vstart[row], vsize[row] & VSIZE_COUNT, cutoff,
+        const uint32_t size = vsize[row];
+        vote_family_warp<8>(fields, payload, stride, lpad, perm, vstart[row], size & VSIZE_COUNT, cutoff,
                             out_rows + (uint64_t)row * stride, sscs_list[row], fam_mapq, fam_flag, fam_tlen, fam_rg,
-                            err_flag, scratch);
+                            err_flag, scratch, (size & VSIZE_MIXED) != 0);
     }
 }
 
