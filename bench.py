@@ -633,7 +633,13 @@ def main():
             h_pairs.copy_(planes[0]); h_planes.copy_(planes[1])
             p_qbits, p_qual, p_base = planes[2], planes[3].contiguous(), planes[4].contiguous()
             # Shorter still (cc_run_host_classes): 16-byte pair records + a table of what many pairs share
-            short = device_classes(planes[0]) if args.e2e_format in ("auto", "classes") else None
+            short = None
+            if args.e2e_format in ("auto", "classes"):
+                try:
+                    short = device_classes(planes[0])
+                except RuntimeError:            # (no room for torch.unique's scratch next to the batch: the 40-byte records then)
+                    short = None
+                    torch.cuda.empty_cache()
             if args.e2e_format == "classes" and short is None:
                 raise SystemExit("--e2e-format classes: the batch does not fit the short pair records")
             if short is not None:
